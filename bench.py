@@ -1,0 +1,403 @@
+#!/usr/bin/env python
+"""Benchmark of the GSC hot path on B200 (contract: see the task statement / DESIGN.md section 6).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c2|c3] [--batch B]
+  python bench.py --impl reference ...     # the CPU oracle on the box's host cores
+
+A "step" is one pass of the hot path over one batch of synthetic network states:
+  c2  batch packer + GNN embedder + actor MLP inference  (B = 4096 states, N_max = 24, n ~ U{16..24})
+  c3  full DDPG update: packer, 5 forward + 3 backward passes, 2 fused Adam/soft-update launches
+      (N_max = n = 100, |E| = 150, replay minibatch of B states per GPU)
+For N > 1 every rank works on its own B states (weak scaling); c3 all-reduces the flat gradient
+buffers over NCCL, c2 has no collective.  One JSON line is printed by rank 0.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "graph-states/sec GNN+actor/critic fwd+bwd at 1/2/4/8 B200; % HBM roofline"
+UNIT = "graph-states/s"
+
+
+def measured_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured"
+    return 6650.0, "fallback"
+
+
+# ------------------------------------------------------------------------------------------------
+def make_workload(args, rank: int):
+    from gsc_b200 import synth
+    seed = 1234 + 1000 * rank
+    if args.workload == "c2":
+        B = args.batch or 4096
+        st = synth.make_states(B, 24, 16, 24, seed=seed)
+        return dict(kind="c2", B=B, n_max=24, cur=st)
+    B = args.batch or 1024
+    cur, nxt, actions, rewards, dones = synth.make_transitions(B, 100, 100, 100, seed=seed, fixed_links=150,
+                                                               num_topologies=32)
+    return dict(kind="c3", B=B, n_max=100, cur=cur, nxt=nxt, actions=actions, rewards=rewards, dones=dones)
+
+
+def workload_name(w):
+    if w["kind"] == "c2":
+        return f"c2: batch packer + GNN embedder + actor inference, B={w['B']}/GPU, N_max=24, n~U{{16..24}}, |E|=round(1.5n)"
+    return f"c3: full DDPG update (fwd+bwd+Adam+target), B={w['B']}/GPU, N_max=n=100, |E|=150"
+
+
+def algorithmic_bytes(w, Pa: int, Pc: int) -> float:
+    """SURVEY.md section 8d formulas with the actual n, e, A, B of this batch."""
+    st = w["cur"]
+    Nt, E, B, A = st.x.shape[0], st.edge_index.shape[1], st.num_graphs, st.action_dim
+    graph = 4.0 * Nt * 3 + 16.0 * E + 8.0 * Nt          # 4nF + 16e (two int64 per directed edge) + 8n (batch)
+    if w["kind"] == "c2":
+        return graph + 4.0 * A * B * 2 + 4.0 * Pa
+    return 2 * (graph + 4.0 * A * B) + (4.0 * A + 8) * B + 48.0 * (Pa + Pc)
+
+
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    FIELDS = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.proc = None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={index}", f"--query-gpu={self.FIELDS}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            out, _ = self.proc.communicate(timeout=5)
+        except Exception:
+            self.proc.kill()
+            out = ""
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in out.strip().splitlines():
+            parts = [p.strip() for p in line.split(",")]
+            if len(parts) < 6:
+                continue
+            try:
+                sm.append(float(parts[0])); mx.append(float(parts[1]))
+            except ValueError:
+                continue
+            for nme, val in zip(names, parts[2:6]):
+                if val.lower().startswith("active"):
+                    reasons.add(nme)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------
+def run_ours(args):
+    import torch.distributed as dist
+    from gsc_b200 import ddpg, ops
+    from gsc_b200.graph import GraphBatch
+    from gsc_b200.models import Actor, AgentSpec, QNetwork
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; gsc_b200 has no CPU fallback (use --impl reference for the CPU oracle)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    w = make_workload(args, rank)
+    B, n_max = w["B"], w["n_max"]
+    spec = AgentSpec(n_max)
+    torch.manual_seed(1234)
+    actor = Actor(spec).to(dev)
+    Pa = sum(p.numel() for p in actor.parameters())
+    Pc = 0
+    upd = None
+    if w["kind"] == "c3":
+        qf1 = QNetwork(spec).to(dev)
+        Pc = sum(p.numel() for p in qf1.parameters())
+        ta, tq = Actor(spec).to(dev), QNetwork(spec).to(dev)
+        ta.load_state_dict(actor.state_dict())
+        tq.load_state_dict(qf1.state_dict())
+        upd = ddpg.DDPGUpdater(actor, qf1, ta, tq, lr=1e-3, gamma=0.99, tau=1e-4,
+                               world_size=world)
+
+    def host_batch(st):
+        return GraphBatch.from_states(st, pin=True)
+
+    h_cur = host_batch(w["cur"])
+    host = {"cur": h_cur}
+    if w["kind"] == "c3":
+        host["nxt"] = host_batch(w["nxt"])
+        host["nxt"].edge_index, host["nxt"].batch, host["nxt"].mask = h_cur.edge_index, h_cur.batch, h_cur.mask
+        for k in ("actions", "rewards", "dones"):
+            host[k] = torch.from_numpy(w[k]).pin_memory()
+
+    def to_dev(hb, share=None):
+        mv = lambda t: t.to(dev, non_blocking=True)
+        if share is None:
+            return GraphBatch(mv(hb.x), mv(hb.edge_index), mv(hb.batch), mv(hb.mask), hb.num_graphs, hb.max_nodes)
+        return GraphBatch(mv(hb.x), share.edge_index, share.batch, share.mask, hb.num_graphs, hb.max_nodes)
+
+    def h2d_all():
+        d = {"cur": to_dev(host["cur"])}
+        if w["kind"] == "c3":
+            d["nxt"] = to_dev(host["nxt"], share=d["cur"])
+            for k in ("actions", "rewards", "dones"):
+                d[k] = host[k].to(dev, non_blocking=True)
+        return d
+
+    def fresh(gb):   # same device tensors, CSR not packed yet: the packer is part of every step
+        return GraphBatch(gb.x, gb.edge_index, gb.batch, gb.mask, gb.num_graphs, gb.max_nodes)
+
+    def step(d):
+        if w["kind"] == "c2":
+            return ddpg.predict(actor, fresh(d["cur"]))
+        cur, nxt = fresh(d["cur"]), fresh(d["nxt"])
+        return upd.update(cur, nxt, d["actions"], d["rewards"], d["dones"])
+
+    resident = h2d_all()
+    torch.cuda.synchronize()
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)     # > 126 MB L2
+    out_host = torch.empty((B, w["cur"].action_dim), dtype=torch.float32).pin_memory() if w["kind"] == "c2" else \
+        torch.empty(2, dtype=torch.float32).pin_memory()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident timing (value) ----
+    for _ in range(args.warmup):
+        flush.zero_()
+        step(resident)
+    barrier()
+    sampler = ClockSampler(local) if rank == 0 else None
+    ops.timer = {}
+    launches0 = ops.launch_count
+    evs = []
+    barrier()
+    t_wall0 = time.perf_counter()
+    for _ in range(args.steps):
+        flush.zero_()                                               # L2 flush, outside the event pair
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        step(resident)
+        e1.record()
+        evs.append((e0, e1))
+    barrier()
+    t_wall = time.perf_counter() - t_wall0
+    launches = (ops.launch_count - launches0) // max(args.steps, 1)
+    timer, ops.timer = ops.timer, None
+    dev_ms = sum(a.elapsed_time(b) for a, b in evs)
+    clocks = sampler.stop() if sampler else None
+    per_op = {k: sum(a.elapsed_time(b) for a, b in v) / args.steps for k, v in timer.items()}
+    per_op_n = {k: len(v) / args.steps for k, v in timer.items()}
+
+    # ---- end-to-end timing through the public API with host buffers (e2e) ----
+    def e2e_step():
+        d = h2d_all()
+        r = step(d)
+        if w["kind"] == "c2":
+            out_host.copy_(r, non_blocking=True)
+        else:
+            out_host[0:1].copy_(r[1], non_blocking=True)
+            out_host[1:2].copy_(r[2], non_blocking=True)
+
+    for _ in range(min(args.warmup, 3)):
+        e2e_step()
+    barrier()
+    e2e_evs = []
+    for _ in range(args.steps):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        e2e_step()
+        e1.record()
+        e2e_evs.append((e0, e1))
+    barrier()
+    e2e_ms = sum(a.elapsed_time(b) for a, b in e2e_evs)
+
+    t = torch.tensor([dev_ms, e2e_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dev_ms, e2e_ms = float(t[0]), float(t[1])
+
+    if rank == 0:
+        hbm, which = measured_peaks()
+        total_states = B * world * args.steps
+        value = total_states / (dev_ms / 1e3)
+        e2e_value = total_states / (e2e_ms / 1e3)
+        hb = host["cur"]
+        h2d = sum(t_.numel() * t_.element_size() for t_ in (hb.x, hb.edge_index, hb.batch, hb.mask))
+        if w["kind"] == "c3":
+            h2d += host["nxt"].x.numel() * 4 + sum(host[k].numel() * 4 for k in ("actions", "rewards", "dones"))
+        d2h = out_host.numel() * 4
+        # dominant kernel + roofline
+        top = max(per_op, key=per_op.get)
+        top_ms = per_op[top] / per_op_n[top]
+        alg_b = op_bytes(top, w, Pa, Pc)
+        step_bytes = algorithmic_bytes(w, Pa, Pc)
+        roof = {"bound": "hbm", "kernel": top, "achieved": alg_b / (top_ms / 1e3) / 1e9, "peak": hbm,
+                "unit": "GB/s", "frac": alg_b / (top_ms / 1e3) / 1e9 / hbm, "traffic": None,
+                "peak_source": which, "kernel_ms_per_launch": top_ms, "kernel_share_of_step": per_op[top] / (dev_ms / args.steps),
+                "step_algorithmic_bytes": step_bytes,
+                "step_frac_of_hbm_roofline": step_bytes / (dev_ms / args.steps / 1e3) / 1e9 / hbm}
+        cpu = cpu_baseline(args, w, sample_states=min(B, 256 if w["kind"] == "c3" else 4096))
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": workload_name(w), "states_per_gpu": B, "n_max": n_max,
+                       "weights": "reference init (PyG glorot / torch Linear), torch.manual_seed(1234)",
+                       "l2": "flushed between timed steps (256 MiB write)",
+                       "parallelism": f"dp{world}" if w["kind"] == "c3" else f"replicas{world}"},
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                    "ms_per_step": e2e_ms / args.steps},
+            "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "cpu_baseline": cpu,
+            "per_op_ms": {k: round(v, 4) for k, v in sorted(per_op.items(), key=lambda kv: -kv[1])[:12]},
+            "wall_ms_per_step_incl_flush": t_wall / args.steps * 1e3,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def op_bytes(name: str, w, Pa, Pc) -> float:
+    """Algorithmic bytes of one launch of the named entry point."""
+    st = w["cur"]
+    Nt, E, B = st.x.shape[0], st.edge_index.shape[1], st.num_graphs
+    if name.startswith(("linear_", "gemm")):
+        dims = name[name.index("[") + 1:name.index("]")]
+        extra = dims.count("+")
+        M, N, K = (int(v) for v in dims.split("+")[0].split("x"))
+        return 4.0 * (M * K + K * N + M * N * (1 + extra))
+    if name.startswith("gnn_fwd"):
+        return 4.0 * Nt * 3 + 4.0 * (E + Nt) + 4.0 * (Nt + 1) + 4.0 * (B + 1) + 4.0 * B * 22
+    if name.startswith("gnn_bwd"):
+        return 4.0 * Nt * 3 + 4.0 * (E + Nt) + 4.0 * (Nt + 1) + 4.0 * (B + 1) + 4.0 * B * 22 + 3 * 4.0 * Nt * 24
+    if name.startswith("adam"):
+        n = int(name[name.index("[") + 1:name.index("]")])
+        return 36.0 * n
+    if name.startswith("pack_csr"):
+        return 2 * 16.0 * E + 8.0 * Nt + 4.0 * (E + Nt) + 4.0 * Nt
+    if name.startswith("colsum"):
+        M, N = (int(v) for v in name[name.index("[") + 1:name.index("]")].split("x"))
+        return 4.0 * M * N
+    return 0.0
+
+
+# ------------------------------------------------------------------------------------------------
+def oracle_step_fn(w, sample_states: int):
+    """The CPU oracle on the first ``sample_states`` states of the workload (fp32, all host threads)."""
+    from oracle import gsc_oracle as O
+    from gsc_b200 import synth
+    st = w["cur"]
+    S = min(sample_states, st.num_graphs)
+    nt = int(st.ptr[S])
+    e_sel = st.edge_index[0] < nt
+
+    def obs_of(s):
+        return {"x": torch.from_numpy(s.x[:nt]), "edge_index": torch.from_numpy(np.ascontiguousarray(s.edge_index[:, e_sel])),
+                "batch": torch.from_numpy(s.batch[:nt]), "mask": torch.from_numpy(s.mask[:S]), "num_graphs": S}
+    A = st.action_dim
+    a_sd = O.init_actor(3, 22, 2, A, seed=1234)
+    if w["kind"] == "c2":
+        o = obs_of(st)
+
+        def fn():
+            with torch.no_grad():
+                return O.actor_forward(a_sd, o)
+        return fn, S
+    c_sd = O.init_critic(3, 22, 2, A, seed=4321)
+    dd = O.OracleDDPG(a_sd, c_sd)
+    o_cur, o_nxt = obs_of(w["cur"]), obs_of(w["nxt"])
+    acts, rew, don = (torch.from_numpy(w[k][:S]) for k in ("actions", "rewards", "dones"))
+
+    def fn():
+        return dd.update(o_cur, o_nxt, acts, rew, don)
+    return fn, S
+
+
+def cpu_baseline(args, w, sample_states: int, reps: int = 3):
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    fn, S = oracle_step_fn(w, sample_states)
+    fn()
+    ts = []
+    for _ in range(reps):
+        t0 = time.perf_counter()
+        fn()
+        ts.append(time.perf_counter() - t0)
+    return {"value": S / statistics.median(ts), "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": f"{S} states of the same workload, fp32 oracle (plain PyTorch restatement of the PyG path), "
+                      f"median of {reps} after 1 warm-up"}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    w = make_workload(args, 0)
+    S = min(w["B"], 256 if w["kind"] == "c3" else 4096)
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    fn, S = oracle_step_fn(w, S)
+    for _ in range(max(1, min(args.warmup, 2))):
+        fn()
+    steps = max(1, min(args.steps, 10))
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        fn()
+    dt = time.perf_counter() - t0
+    value = S * steps / dt
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT,
+            "n_gpus": int(os.environ.get("WORLD_SIZE", "1")), "steps": steps, "warmup": max(1, min(args.warmup, 2)),
+            "ms_per_step": dt / steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": workload_name(w), "states_per_step": S,
+                       "note": "reference CPU path = oracle port (PyG absent); bounded sample per step"},
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
+                             "sample": f"{S} states per step x {steps} steps"},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default=os.environ.get("GSC_BENCH_WORKLOAD", "c2"), choices=["c2", "c3"])
+    ap.add_argument("--batch", type=int, default=0)
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

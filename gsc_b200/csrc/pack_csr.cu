@@ -1,0 +1,230 @@
+// Batch packer: int64 COO (PyG Batch layout) -> int32 CSR-by-target with one self-loop per node.
+//
+// Replaces the graph part of Batch.from_data_list (reference src/rlsp/agents/buffer.py:65-81) and
+// the remove_self_loops + add_self_loops that GATv2Conv.forward repeats on every call (reference
+// src/rlsp/agents/models.py:38,47 -> PyG 2.3.0).  Done once per minibatch, on the device.
+//
+// HBM traffic: reads 16 B/edge (twice: count + fill) + 8 B/node, writes 4 B/edge + 4 B/node.
+// All kernels are flat, coalesced, grid-stride; the row sort makes the neighbour order (and with
+// it every downstream fp32 sum) independent of the atomic fill order.
+#include "common.cuh"
+
+namespace gsc {
+
+constexpr int kScanThreads = 256;
+constexpr int kScanItems = 4;
+constexpr int kScanTile = kScanThreads * kScanItems;  // 1024 rows per scan block
+
+__global__ void pack_init_kernel(int32_t* __restrict__ deg, int64_t Nt, int32_t* __restrict__ stats) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i == 0) { stats[0] = 0; stats[1] = 0; stats[2] = 0; stats[3] = 0; }
+  for (; i < Nt; i += (int64_t)gridDim.x * blockDim.x) deg[i] = 1;  // the self-loop
+}
+
+__global__ void pack_count_kernel(const int64_t* __restrict__ ei, int64_t E, int64_t Nt,
+                                  const int64_t* __restrict__ batch, int32_t* __restrict__ deg,
+                                  int32_t* __restrict__ stats) {
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < E;
+       e += (int64_t)gridDim.x * blockDim.x) {
+    int64_t s = ei[e], d = ei[E + e];
+    if (s < 0 || s >= Nt || d < 0 || d >= Nt) { atomicOr(stats + 2, 1); continue; }
+    if (batch != nullptr && batch[s] != batch[d]) { atomicOr(stats + 2, 8); continue; }
+    if (s != d) atomicAdd(deg + d, 1);
+  }
+}
+
+// Block-local exclusive scan of deg -> rowptr, block totals -> blocksum.
+__global__ void __launch_bounds__(kScanThreads)
+pack_scan_local_kernel(const int32_t* __restrict__ deg, int64_t Nt, int32_t* __restrict__ rowptr,
+                       int32_t* __restrict__ blocksum) {
+  __shared__ int32_t warp_tot[kScanThreads / 32];
+  int64_t base = (int64_t)blockIdx.x * kScanTile + (int64_t)threadIdx.x * kScanItems;
+  int32_t v[kScanItems];
+  int32_t tsum = 0;
+#pragma unroll
+  for (int k = 0; k < kScanItems; ++k) {
+    v[k] = (base + k < Nt) ? deg[base + k] : 0;
+    tsum += v[k];
+  }
+  int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  int32_t incl = tsum;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    int32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += t;
+  }
+  if (lane == 31) warp_tot[warp] = incl;
+  __syncthreads();
+  int32_t woff = 0;
+  for (int w = 0; w < warp; ++w) woff += warp_tot[w];
+  int32_t run = woff + incl - tsum;
+#pragma unroll
+  for (int k = 0; k < kScanItems; ++k) {
+    if (base + k < Nt) rowptr[base + k] = run;
+    run += v[k];
+  }
+  if (threadIdx.x == kScanThreads - 1) blocksum[blockIdx.x] = run;
+}
+
+// Single block: exclusive scan of the block totals in place; total -> blocksum[nb].
+__global__ void __launch_bounds__(1024) pack_scan_blocks_kernel(int32_t* __restrict__ blocksum, int nb) {
+  __shared__ int32_t warp_tot[32];
+  __shared__ int32_t carry_s;
+  if (threadIdx.x == 0) carry_s = 0;
+  __syncthreads();
+  int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int start = 0; start < nb; start += 1024) {
+    int i = start + threadIdx.x;
+    int32_t v = (i < nb) ? blocksum[i] : 0;
+    int32_t incl = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      int32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += t;
+    }
+    if (lane == 31) warp_tot[warp] = incl;
+    __syncthreads();
+    int32_t woff = 0;
+    for (int w = 0; w < warp; ++w) woff += warp_tot[w];
+    int32_t carry = carry_s;
+    if (i < nb) blocksum[i] = carry + woff + incl - v;
+    __syncthreads();
+    if (threadIdx.x == 1023) carry_s = carry + woff + incl;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) blocksum[nb] = carry_s;
+}
+
+// rowptr += block offset; cursor (the deg array) := 0; rowptr[Nt] and stats[0] := total.
+__global__ void pack_scan_add_kernel(int32_t* __restrict__ rowptr, int32_t* __restrict__ cursor,
+                                     const int32_t* __restrict__ blocksum, int64_t Nt, int nb,
+                                     int32_t* __restrict__ stats) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i == 0) { rowptr[Nt] = blocksum[nb]; stats[0] = blocksum[nb]; }
+  for (; i < Nt; i += (int64_t)gridDim.x * blockDim.x) {
+    rowptr[i] += blocksum[i / kScanTile];
+    cursor[i] = 0;
+  }
+}
+
+__global__ void pack_fill_kernel(const int64_t* __restrict__ ei, int64_t E, int64_t Nt,
+                                 const int64_t* __restrict__ batch, const int32_t* __restrict__ rowptr,
+                                 int32_t* __restrict__ cursor, int32_t* __restrict__ col) {
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < E;
+       e += (int64_t)gridDim.x * blockDim.x) {
+    int64_t s = ei[e], d = ei[E + e];
+    if (s < 0 || s >= Nt || d < 0 || d >= Nt || s == d) continue;
+    if (batch != nullptr && batch[s] != batch[d]) continue;
+    int pos = atomicAdd(cursor + d, 1);
+    col[rowptr[d] + pos] = (int32_t)s;
+  }
+}
+
+// One thread per row: sort the neighbour sources ascending, put the self-loop last.
+__global__ void pack_rows_kernel(const int32_t* __restrict__ rowptr, int32_t* __restrict__ col, int64_t Nt) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < Nt;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    int lo = rowptr[i], hi = rowptr[i + 1] - 1;
+    for (int a = lo + 1; a < hi; ++a) {
+      int32_t key = col[a];
+      int b = a - 1;
+      while (b >= lo && col[b] > key) { col[b + 1] = col[b]; --b; }
+      col[b + 1] = key;
+    }
+    col[hi] = (int32_t)i;
+  }
+}
+
+__global__ void pack_graph_ptr_kernel(const int64_t* __restrict__ batch, int64_t Nt, int64_t B,
+                                      int32_t* __restrict__ graph_ptr, int32_t* __restrict__ stats) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (batch == nullptr) {
+    if (i == 0) { graph_ptr[0] = 0; for (int64_t g = 1; g <= B; ++g) graph_ptr[g] = (int32_t)Nt; }
+    return;
+  }
+  if (Nt == 0) {
+    for (; i <= B; i += (int64_t)gridDim.x * blockDim.x) graph_ptr[i] = 0;
+    return;
+  }
+  for (; i < Nt; i += (int64_t)gridDim.x * blockDim.x) {
+    int64_t b = batch[i];
+    int64_t prev = (i > 0) ? batch[i - 1] : -1;
+    if (b < 0 || b >= B) { atomicOr(stats + 2, 2); continue; }
+    if (b < prev) { atomicOr(stats + 2, 4); continue; }
+    for (int64_t g = prev + 1; g <= b; ++g) graph_ptr[g] = (int32_t)i;  // empty graphs too
+    if (i == Nt - 1)
+      for (int64_t g = b + 1; g <= B; ++g) graph_ptr[g] = (int32_t)Nt;
+  }
+}
+
+__global__ void pack_max_nodes_kernel(const int32_t* __restrict__ graph_ptr, int64_t B,
+                                      int32_t* __restrict__ stats) {
+  int32_t m = 0;
+  for (int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; g < B;
+       g += (int64_t)gridDim.x * blockDim.x)
+    m = max(m, graph_ptr[g + 1] - graph_ptr[g]);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
+  if ((threadIdx.x & 31) == 0 && m > 0) atomicMax(stats + 1, m);
+}
+
+static inline int flat_grid(int64_t n, int threads) {
+  int64_t b = ceil_div(n > 0 ? n : 1, threads);
+  int64_t cap = (int64_t)kNumSMs * 16;
+  return (int)(b < cap ? b : cap);
+}
+
+}  // namespace gsc
+
+using namespace gsc;
+
+extern "C" size_t gsc_pack_csr_workspace_bytes(int64_t num_nodes, int64_t num_edges) {
+  (void)num_edges;
+  int64_t nb = ceil_div(num_nodes > 0 ? num_nodes : 1, kScanTile);
+  return align_up((size_t)(num_nodes > 0 ? num_nodes : 1) * 4, 256) + align_up((size_t)(nb + 1) * 4, 256);
+}
+
+extern "C" int gsc_pack_csr(const int64_t* edge_index, int64_t E, const int64_t* batch, int64_t Nt,
+                            int64_t B, int32_t* rowptr, int32_t* col, int32_t* graph_ptr,
+                            int32_t* stats, void* workspace, size_t workspace_bytes, void* stream_) {
+  cudaStream_t st = (cudaStream_t)stream_;
+  GSC_REQUIRE(Nt >= 0 && E >= 0 && B >= 1, "gsc_pack_csr: bad sizes Nt=%lld E=%lld B=%lld",
+              (long long)Nt, (long long)E, (long long)B);
+  GSC_REQUIRE(E + Nt < (int64_t)INT32_MAX, "gsc_pack_csr: E+Nt=%lld exceeds the int32 CSR range",
+              (long long)(E + Nt));
+  GSC_REQUIRE(rowptr && col && graph_ptr && stats && workspace, "gsc_pack_csr: null output pointer");
+  GSC_REQUIRE(E == 0 || edge_index, "gsc_pack_csr: null edge_index");
+  if (workspace_bytes < gsc_pack_csr_workspace_bytes(Nt, E))
+    return fail(GSC_EWORKSPACE, "gsc_pack_csr: workspace %zu < %zu", workspace_bytes,
+                gsc_pack_csr_workspace_bytes(Nt, E));
+  int32_t* deg = (int32_t*)workspace;
+  int nb = (int)ceil_div(Nt > 0 ? Nt : 1, kScanTile);
+  int32_t* blocksum = (int32_t*)((char*)workspace + align_up((size_t)(Nt > 0 ? Nt : 1) * 4, 256));
+
+  pack_init_kernel<<<flat_grid(Nt, 256), 256, 0, st>>>(deg, Nt, stats);
+  GSC_LAUNCH_CHECK("pack_init_kernel");
+  if (E > 0) {
+    pack_count_kernel<<<flat_grid(E, 256), 256, 0, st>>>(edge_index, E, Nt, batch, deg, stats);
+    GSC_LAUNCH_CHECK("pack_count_kernel");
+  }
+  pack_scan_local_kernel<<<nb, kScanThreads, 0, st>>>(deg, Nt, rowptr, blocksum);
+  GSC_LAUNCH_CHECK("pack_scan_local_kernel");
+  pack_scan_blocks_kernel<<<1, 1024, 0, st>>>(blocksum, nb);
+  GSC_LAUNCH_CHECK("pack_scan_blocks_kernel");
+  pack_scan_add_kernel<<<flat_grid(Nt, 256), 256, 0, st>>>(rowptr, deg, blocksum, Nt, nb, stats);
+  GSC_LAUNCH_CHECK("pack_scan_add_kernel");
+  if (E > 0) {
+    pack_fill_kernel<<<flat_grid(E, 256), 256, 0, st>>>(edge_index, E, Nt, batch, rowptr, deg, col);
+    GSC_LAUNCH_CHECK("pack_fill_kernel");
+  }
+  if (Nt > 0) {
+    pack_rows_kernel<<<flat_grid(Nt, 128), 128, 0, st>>>(rowptr, col, Nt);
+    GSC_LAUNCH_CHECK("pack_rows_kernel");
+  }
+  int64_t gp_n = (batch == nullptr) ? 1 : (Nt > 0 ? Nt : B + 1);
+  pack_graph_ptr_kernel<<<flat_grid(gp_n, 256), 256, 0, st>>>(batch, Nt, B, graph_ptr, stats);
+  GSC_LAUNCH_CHECK("pack_graph_ptr_kernel");
+  pack_max_nodes_kernel<<<flat_grid(B, 256), 256, 0, st>>>(graph_ptr, B, stats);
+  GSC_LAUNCH_CHECK("pack_max_nodes_kernel");
+  return GSC_OK;
+}

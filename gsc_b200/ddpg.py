@@ -1,0 +1,123 @@
+"""DDPG update on the CUDA path -- the gradient-step block of the reference training loop.
+
+``DDPGUpdater.update`` performs exactly what reference src/rlsp/agents/simple_ddpg.py:312-322 does
+per minibatch -- ``_update_critic`` (:204-219), ``_update_actor`` (:221-227),
+``_update_target_networks`` (:229-234) -- as a fixed sequence of libgsc_b200 launches with no
+autograd graph, no per-tensor optimizer loop and no host synchronisation:
+
+  target actor/critic forward -> critic forward -> TD/MSE -> critic backward -> [all-reduce]
+  -> fused Adam+soft-update(critic) -> actor forward -> critic forward (updated weights)
+  -> backward through the critic into the action -> actor backward -> [all-reduce]
+  -> fused Adam+soft-update(actor).
+
+Data parallelism: every rank holds a replica and ``B/W`` states; losses are
+scaled by ``1/B_global`` and the flat gradient buffer of each network is summed with one NCCL
+all-reduce before its optimizer step.  The critic gradient that the reference's ``actor_loss.backward()``
+also produces is never consumed there (zeroed by the next ``zero_grad``), so it is not computed.
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import numpy as np
+import torch
+
+from . import ops
+from .graph import GraphBatch
+from .models import Actor, QNetwork, net_backward, net_forward
+
+
+class DDPGUpdater:
+    def __init__(self, actor: Actor, qf1: QNetwork, target_actor: Actor, qf1_target: QNetwork,
+                 lr: float = 1e-3, gamma: float = 0.99, tau: float = 1e-4, betas=(0.9, 0.999),
+                 eps: float = 1e-8, process_group=None, world_size: int = 1):
+        self.actor, self.qf1, self.target_actor, self.qf1_target = actor, qf1, target_actor, qf1_target
+        self.lr, self.gamma, self.tau, self.betas, self.eps = lr, gamma, tau, betas, eps
+        self.pg, self.world_size = process_group, int(world_size)
+        for net in (actor, qf1, target_actor, qf1_target):
+            net._check_flat()
+        z = lambda net: torch.zeros_like(net.flat)
+        self.g_actor, self.m_actor, self.v_actor = z(actor), z(actor), z(actor)
+        self.g_critic, self.m_critic, self.v_critic = z(qf1), z(qf1), z(qf1)
+        self.step_actor = 0
+        self.step_critic = 0
+        self._neg = None
+
+    # -- pieces, named after the reference methods ---------------------------------------------
+    def _allreduce(self, flat_grad: torch.Tensor) -> None:
+        if self.world_size > 1:
+            torch.distributed.all_reduce(flat_grad, op=torch.distributed.ReduceOp.SUM, group=self.pg)
+
+    def update_critic(self, nxt: GraphBatch, cur: GraphBatch, dones, rewards, actions):
+        """reference _update_critic (simple_ddpg.py:204-219)."""
+        B = cur.num_graphs
+        scale = 1.0 / (B * self.world_size)
+        ta, tq, q = self.target_actor, self.qf1_target, self.qf1
+        a2, _ = net_forward(ta, ta.flat, nxt, None, save=False, out_mul=nxt.mask, clamp1=True)
+        q2, _ = net_forward(tq, tq.flat, nxt, a2, save=False)
+        qv, ctx = net_forward(q, q.flat, cur, actions, save=True)
+        _, dq, loss = ops.td_mse(rewards, dones, q2, qv, self.gamma, scale)
+        net_backward(q, q.flat, cur, ctx, dq.view(B, 1), self.g_critic)
+        self._allreduce(self.g_critic)
+        self.step_critic += 1
+        ops.adam_soft_update(q.flat, self.g_critic, self.m_critic, self.v_critic, tq.flat, self.lr,
+                             self.betas[0], self.betas[1], self.eps, self.step_critic, self.tau)
+        return qv.view(-1), loss
+
+    def update_actor(self, cur: GraphBatch):
+        """reference _update_actor (simple_ddpg.py:221-227) + the actor half of
+        _update_target_networks (:229-234)."""
+        B = cur.num_graphs
+        scale = 1.0 / (B * self.world_size)
+        ac, q, ta = self.actor, self.qf1, self.target_actor
+        a, ctx_a = net_forward(ac, ac.flat, cur, None, save=True, out_mul=cur.mask)
+        q_pi, ctx_q = net_forward(q, q.flat, cur, a, save=True, save_gnn=False)
+        if self._neg is None or self._neg.shape[0] != B or float(self._neg_scale) != scale:
+            self._neg = torch.full((B, 1), -scale, dtype=torch.float32, device=a.device)
+            self._neg_scale = scale
+        # d(-mean q)/dq = -1/B_global ; back through the critic into the action, times mask
+        dz = net_backward(q, q.flat, cur, ctx_q, self._neg, None, want_action_grad=True,
+                          action_grad_mul=cur.mask)
+        net_backward(ac, ac.flat, cur, ctx_a, dz, self.g_actor)
+        self._allreduce(self.g_actor)
+        self.step_actor += 1
+        ops.adam_soft_update(ac.flat, self.g_actor, self.m_actor, self.v_actor, ta.flat, self.lr,
+                             self.betas[0], self.betas[1], self.eps, self.step_actor, self.tau)
+        actor_loss = ops.colsum(q_pi) * (-scale)
+        return actor_loss
+
+    def update(self, cur: GraphBatch, nxt: GraphBatch, actions, rewards, dones):
+        """One gradient step of reference simple_ddpg.py:312-322.  Returns
+        (qf1_a_values [B], qf1_loss [1], actor_loss [1]); the losses are this rank's share."""
+        cur.csr()
+        nxt.share_topology_from(cur)
+        qv, q_loss = self.update_critic(nxt, cur, dones, rewards, actions)
+        a_loss = self.update_actor(cur)
+        return qv, q_loss, a_loss
+
+
+@torch.no_grad()
+def predict(actor: Actor, obs) -> torch.Tensor:
+    """reference SimpleDDPG.predict (simple_ddpg.py:331-336) / inference.predict (inference.py:11-15)."""
+    gb = GraphBatch.wrap(obs)
+    y, _ = net_forward(actor, actor._check_flat(), gb, None, save=False, out_mul=gb.mask)
+    return y
+
+
+def post_process_actions(action, num_nodes: int) -> torch.Tensor:
+    """reference SimpleDDPG.post_process_actions (simple_ddpg.py:374-395) on the GPU.
+
+    ``action``: [A] or [R, A] fp32 (tensor or ndarray).  Returns fp64 of the same shape."""
+    t = torch.as_tensor(action, dtype=torch.float32)
+    if not t.is_cuda:
+        t = t.cuda()
+    out = ops.actor_head(t, num_nodes)
+    return out.view(t.shape) if t.dim() == 1 else out
+
+
+def choose_action(actor: Actor, obs, noise: torch.Tensor, num_nodes: int) -> torch.Tensor:
+    """The non-warm-up branch of reference _choose_action (simple_ddpg.py:187-199) followed by
+    post_process_actions, with the Gaussian sample ``noise`` ([R, A] fp64) supplied by the caller."""
+    y = predict(actor, obs)
+    low, high = float(np.min(actor.low)), float(np.max(actor.high))
+    return ops.actor_head(y, num_nodes, noise=noise, low=low, high=high)

@@ -1,0 +1,292 @@
+"""Tensor-level wrappers over the C-ABI (device pointers of torch CUDA tensors -> libgsc_b200).
+
+torch is used here for device memory and streams only; all arithmetic happens in the library.
+Every wrapper enqueues on torch's current stream and never synchronises.
+"""
+from __future__ import annotations
+
+from typing import List, Optional, Sequence, Tuple
+
+import torch
+
+from . import _lib
+from ._lib import EPI_BIAS, EPI_CLAMP1, EPI_GATE, EPI_MUL, EPI_RELU, GemmArgs, check
+
+_workspaces = {}
+launch_count = 0          # kernels enqueued through this module (bench.py reports it)
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+def _need_cuda(*ts):
+    for t in ts:
+        if t is not None and not t.is_cuda:
+            raise _lib.GscError("gsc_b200 ops need CUDA tensors (there is no CPU fallback)")
+
+
+def workspace(nbytes: int, device, tag: str = "main") -> Tuple[Optional[torch.Tensor], int]:
+    """Grow-only scratch buffer per (device, tag); the library itself never allocates."""
+    if nbytes <= 0:
+        return None, 0
+    key = (torch.device(device).index, tag)
+    ws = _workspaces.get(key)
+    if ws is None or ws.numel() < nbytes:
+        ws = torch.empty(int(nbytes * 1.25) + 256, dtype=torch.uint8, device=device)
+        _workspaces[key] = ws
+    return ws, ws.numel()
+
+
+def _count(n: int):
+    global launch_count
+    launch_count += n
+
+
+# Optional per-entry-point CUDA-event timing (bench.py uses it for the roofline of the dominant
+# kernel).  ``timer`` maps name -> list of (start_event, end_event); events are recorded on the
+# launching stream around the C-ABI call, no synchronisation happens here.
+timer = None
+
+
+class _Timed:
+    __slots__ = ("name", "ev")
+
+    def __init__(self, name):
+        self.name = name
+
+    def __enter__(self):
+        if timer is not None:
+            self.ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+            self.ev[0].record(torch.cuda.current_stream())
+        return self
+
+    def __exit__(self, *exc):
+        if timer is not None:
+            self.ev[1].record(torch.cuda.current_stream())
+            timer.setdefault(self.name, []).append(self.ev)
+        return False
+
+
+# ---------------------------------------------------------------------------------------------
+def pack_csr(edge_index: torch.Tensor, batch: Optional[torch.Tensor], num_nodes: int, num_graphs: int):
+    """COO int64 -> (rowptr, col, graph_ptr, stats) int32 on the device (include/gsc_b200.h)."""
+    _need_cuda(edge_index, batch)
+    lib = _lib.load()
+    dev = edge_index.device
+    edge_index = edge_index.contiguous()
+    if edge_index.dtype != torch.int64:
+        edge_index = edge_index.to(torch.int64)
+    if batch is not None:
+        batch = batch.contiguous().to(torch.int64)
+    E = int(edge_index.shape[1])
+    rowptr = torch.empty(num_nodes + 1, dtype=torch.int32, device=dev)
+    col = torch.empty(E + num_nodes, dtype=torch.int32, device=dev)
+    graph_ptr = torch.empty(num_graphs + 1, dtype=torch.int32, device=dev)
+    stats = torch.empty(4, dtype=torch.int32, device=dev)
+    ws, wsn = workspace(lib.gsc_pack_csr_workspace_bytes(num_nodes, E), dev, "pack")
+    with _Timed("pack_csr"):
+        check(lib.gsc_pack_csr(_ptr(edge_index), E, _ptr(batch), num_nodes, num_graphs, _ptr(rowptr),
+                               _ptr(col), _ptr(graph_ptr), _ptr(stats), _ptr(ws), wsn, _stream()),
+              "gsc_pack_csr")
+    _count(9 if E > 0 else 7)
+    return rowptr, col, graph_ptr, stats
+
+
+def gnn_param_floats(in_dim: int, hidden: int, num_layers: int) -> int:
+    return int(_lib.load().gsc_gnn_param_floats(in_dim, hidden, num_layers))
+
+
+def gnn_embed_fwd(x, rowptr, col, graph_ptr, num_graphs: int, max_nodes: int, params: torch.Tensor,
+                  hidden: int, num_layers: int, num_iter: int, save: bool = False):
+    _need_cuda(x, params)
+    lib = _lib.load()
+    x = x.contiguous()
+    Nt, in_dim = int(x.shape[0]), int(x.shape[1])
+    emb = torch.empty(num_graphs, hidden, dtype=torch.float32, device=x.device)
+    saved = None
+    if save:
+        saved = torch.empty(int(lib.gsc_gnn_saved_floats(Nt, hidden, num_layers, num_iter)),
+                            dtype=torch.float32, device=x.device)
+    with _Timed("gnn_fwd"):
+        check(lib.gsc_gnn_embed_fwd(_ptr(x), Nt, in_dim, _ptr(rowptr), _ptr(col), _ptr(graph_ptr),
+                                    num_graphs, max_nodes, _ptr(params), hidden, num_layers, num_iter,
+                                    _ptr(emb), _ptr(saved), _stream()), "gsc_gnn_embed_fwd")
+    _count(1)
+    return emb, saved
+
+
+def gnn_embed_bwd(x, rowptr, col, graph_ptr, num_graphs: int, max_nodes: int, params, hidden: int,
+                  num_layers: int, num_iter: int, saved, d_emb, d_params: Optional[torch.Tensor] = None):
+    _need_cuda(x, params, saved, d_emb)
+    lib = _lib.load()
+    x = x.contiguous()
+    d_emb = d_emb.contiguous()
+    Nt, in_dim = int(x.shape[0]), int(x.shape[1])
+    if d_params is None:
+        d_params = torch.empty_like(params)
+    ws, wsn = workspace(lib.gsc_gnn_bwd_workspace_bytes(num_graphs, in_dim, hidden, num_layers),
+                        x.device, "gnn_bwd")
+    with _Timed("gnn_bwd"):
+        check(lib.gsc_gnn_embed_bwd(_ptr(x), Nt, in_dim, _ptr(rowptr), _ptr(col), _ptr(graph_ptr),
+                                    num_graphs, max_nodes, _ptr(params), hidden, num_layers, num_iter,
+                                    _ptr(saved), _ptr(d_emb), _ptr(d_params), _ptr(ws), wsn, _stream()),
+              "gsc_gnn_embed_bwd")
+    _count(2)
+    return d_params
+
+
+# ---------------------------------------------------------------------------------------------
+def _row_major(t: torch.Tensor, what: str) -> torch.Tensor:
+    if t.dim() != 2 or (t.shape[1] > 1 and t.stride(1) != 1) or t.dtype != torch.float32:
+        raise _lib.GscError(f"{what}: need a 2-D fp32 tensor with unit column stride, got "
+                            f"shape={tuple(t.shape)} stride={t.stride()} dtype={t.dtype}")
+    return t
+
+
+def _ld(t: torch.Tensor) -> int:
+    return int(t.stride(0)) if t.shape[0] > 1 else max(int(t.stride(0)), int(t.shape[1]))
+
+
+def gemm_raw(segs: Sequence[tuple], M: int, N: int, out: torch.Tensor, flags: int = 0,
+             bias=None, mul=None, gate=None, tag: str = "gemm"):
+    """segs: (A_tensor, a_rs, a_cs, B_tensor, b_rs, b_cs, K) with A/B giving the base pointers."""
+    lib = _lib.load()
+    args = GemmArgs()
+    ktot = 0
+    for s, (A, ars, acs, B, brs, bcs, K) in enumerate(segs):
+        _need_cuda(A, B)
+        args.A[s], args.B[s], args.K[s] = A.data_ptr(), B.data_ptr(), K
+        args.a_rs[s], args.a_cs[s], args.b_rs[s], args.b_cs[s] = ars, acs, brs, bcs
+        ktot += K
+    args.num_seg, args.flags = len(segs), flags
+    args.bias = _ptr(bias)
+    if mul is not None:
+        args.mul, args.ld_mul = mul.data_ptr(), _ld(mul)
+    if gate is not None:
+        args.gate, args.ld_gate = gate.data_ptr(), _ld(gate)
+    need = lib.gsc_gemm_workspace_bytes(M, N, ktot)
+    ws, wsn = workspace(need, out.device, "gemm")
+    with _Timed(f"{tag}[{M}x{N}x{ktot}{'+m' if mul is not None else ''}{'+g' if gate is not None else ''}]"):
+        check(lib.gsc_gemm(args, M, N, out.data_ptr(), _ld(out), _ptr(ws), wsn, _stream()), "gsc_gemm")
+    _count(2 if need else 1)
+    return out
+
+
+def linear_fwd(inputs: List[torch.Tensor], weight: torch.Tensor, bias: Optional[torch.Tensor],
+               relu: bool = False, mul: Optional[torch.Tensor] = None, clamp1: bool = False,
+               out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """act(cat(inputs, 1) @ weight.T + bias) [* mul] without materialising the concatenation.
+
+    weight: [N, sum K_s] fp32, may be a strided row view (its row stride is used)."""
+    weight = _row_major(weight, "linear_fwd weight")
+    M, N = int(inputs[0].shape[0]), int(weight.shape[0])
+    ldw = _ld(weight)
+    segs, off = [], 0
+    for x in inputs:
+        x = _row_major(x, "linear_fwd input")
+        K = int(x.shape[1])
+        segs.append((x, _ld(x), 1, weight[:, off:], 1, ldw, K))
+        off += K
+    if off != weight.shape[1]:
+        raise _lib.GscError(f"linear_fwd: inputs have {off} columns, weight expects {weight.shape[1]}")
+    if out is None:
+        out = torch.empty(M, N, dtype=torch.float32, device=weight.device)
+    flags = (EPI_BIAS if bias is not None else 0) | (EPI_RELU if relu else 0) | \
+            (EPI_MUL if mul is not None else 0) | (EPI_CLAMP1 if clamp1 else 0)
+    return gemm_raw(segs, M, N, out, flags, bias=bias, mul=mul, tag="linear_fwd")
+
+
+def linear_dgrad(dY: torch.Tensor, weight: torch.Tensor, col_off: int, K: int,
+                 mul: Optional[torch.Tensor] = None, gate: Optional[torch.Tensor] = None,
+                 out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """dX[M, K] = dY[M, N] @ weight[:, col_off:col_off+K]  (* mul) (gated by gate > 0)."""
+    dY = _row_major(dY, "linear_dgrad dY")
+    weight = _row_major(weight, "linear_dgrad weight")
+    M, N = int(dY.shape[0]), int(dY.shape[1])
+    if out is None:
+        out = torch.empty(M, K, dtype=torch.float32, device=dY.device)
+    flags = (EPI_MUL if mul is not None else 0) | (EPI_GATE if gate is not None else 0)
+    seg = (dY, _ld(dY), 1, weight[:, col_off:], _ld(weight), 1, N)
+    return gemm_raw([seg], M, K, out, flags, mul=mul, gate=gate, tag="linear_dgrad")
+
+
+def linear_wgrad(dY: torch.Tensor, inputs: List[torch.Tensor], dW: torch.Tensor) -> torch.Tensor:
+    """dW[N, sum K_s] = dY^T @ cat(inputs, 1), one GEMM per input segment, written in place."""
+    dY = _row_major(dY, "linear_wgrad dY")
+    dW = _row_major(dW, "linear_wgrad dW")
+    M, N = int(dY.shape[0]), int(dY.shape[1])
+    off = 0
+    for x in inputs:
+        x = _row_major(x, "linear_wgrad input")
+        K = int(x.shape[1])
+        seg = (dY, 1, _ld(dY), x, _ld(x), 1, M)
+        gemm_raw([seg], N, K, dW[:, off:off + K], 0, tag="linear_wgrad")
+        off += K
+    return dW
+
+
+def mul_gate(x: torch.Tensor, mul: Optional[torch.Tensor] = None, gate: Optional[torch.Tensor] = None):
+    """x * mul, zeroed where gate <= 0 (standalone form of the GEMM epilogue)."""
+    x = _row_major(x, "mul_gate x")
+    out = torch.empty(x.shape, dtype=torch.float32, device=x.device)
+    check(_lib.load().gsc_mul_gate(_ptr(x), _ld(x), _ptr(mul), _ld(mul) if mul is not None else 0,
+                                   _ptr(gate), _ld(gate) if gate is not None else 0, int(x.shape[0]),
+                                   int(x.shape[1]), _ptr(out), _ld(out), _stream()), "gsc_mul_gate")
+    _count(1)
+    return out
+
+
+def colsum(X: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    X = _row_major(X, "colsum")
+    if out is None:
+        out = torch.empty(X.shape[1], dtype=torch.float32, device=X.device)
+    with _Timed(f"colsum[{int(X.shape[0])}x{int(X.shape[1])}]"):
+        check(_lib.load().gsc_colsum(_ptr(X), _ld(X), int(X.shape[0]), int(X.shape[1]), _ptr(out), _stream()),
+              "gsc_colsum")
+    _count(1)
+    return out
+
+
+def td_mse(rewards, dones, q_next, q, gamma: float, loss_scale: float):
+    B = int(q.numel())
+    y = torch.empty(B, dtype=torch.float32, device=q.device)
+    dq = torch.empty(B, dtype=torch.float32, device=q.device)
+    loss = torch.empty(1, dtype=torch.float32, device=q.device)
+    check(_lib.load().gsc_td_mse(_ptr(rewards.contiguous()), _ptr(dones.contiguous()),
+                                 _ptr(q_next.contiguous()), _ptr(q.contiguous()), gamma, loss_scale,
+                                 B, _ptr(y), _ptr(dq), _ptr(loss), _stream()), "gsc_td_mse")
+    _count(1)
+    return y, dq, loss
+
+
+def adam_soft_update(p, g, m, v, target, lr, beta1, beta2, eps, step: int, tau: float):
+    for t in (p, g, m, v, target):
+        if t is not None and not t.is_contiguous():
+            raise _lib.GscError("adam_soft_update needs flat contiguous buffers")
+    with _Timed(f"adam_soft_update[{int(p.numel())}]"):
+        check(_lib.load().gsc_adam_soft_update(_ptr(p), _ptr(g), _ptr(m), _ptr(v), _ptr(target),
+                                               int(p.numel()), lr, beta1, beta2, eps, step, tau, _stream()),
+              "gsc_adam_soft_update")
+    _count(1)
+
+
+def actor_head(y: torch.Tensor, group: int, noise: Optional[torch.Tensor] = None,
+               low: float = 0.0, high: float = 1.0) -> torch.Tensor:
+    """post_process_actions (and, with ``noise``, the exploration step) -> fp64 [R, A]."""
+    _need_cuda(y, noise)
+    y = y.contiguous().to(torch.float32)
+    if y.dim() == 1:
+        y = y.unsqueeze(0)
+    R, A = int(y.shape[0]), int(y.shape[1])
+    if noise is not None:
+        noise = noise.contiguous().to(torch.float64)
+    out = torch.empty(R, A, dtype=torch.float64, device=y.device)
+    check(_lib.load().gsc_actor_head(_ptr(y), _ptr(noise), R, A, group, low, high, _ptr(out), _stream()),
+          "gsc_actor_head")
+    _count(1)
+    return out

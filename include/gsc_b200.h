@@ -1,0 +1,152 @@
+/*
+ * gsc_b200 -- C-ABI of the B200-native GSC hot path (GNN embedder + DDPG actor/critic).
+ *
+ * Every entry point takes raw DEVICE pointers, sizes and a CUDA stream (a cudaStream_t passed as
+ * void*), enqueues its kernels on that stream and returns without synchronising.  Return value:
+ * 0 on success, a negative GSC_E* code otherwise; gsc_last_error() gives the message of the last
+ * failure on the calling thread.  The library never allocates device memory: callers pass
+ * workspaces sized by the *_workspace_bytes() queries.  All floating point data is fp32 row-major,
+ * graph indices are int32 once packed (the reference's int64 COO is the packer's input).
+ *
+ * "reference" citations are relative to the farzad1132/GSC tree.  The reference has no FFI; the
+ * Python call sites below are what each entry point replaces (see INTEGRATION.md for the binding).
+ */
+#ifndef GSC_B200_H
+#define GSC_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GSC_OK 0
+#define GSC_EINVAL (-1)      /* bad argument (null pointer, size out of the supported range) */
+#define GSC_ECUDA (-2)       /* a CUDA runtime call or kernel launch failed */
+#define GSC_EWORKSPACE (-3)  /* workspace too small */
+
+#define GSC_MAX_HIDDEN 32    /* GNN_features supported by the embedder kernels (reference: 22) */
+#define GSC_MAX_APPS 16      /* 1 + num_iter*(num_layers-1) GATv2 applications per forward */
+
+/* Epilogue flags of gsc_gemm (applied in this order). */
+#define GSC_EPI_BIAS 1       /* v += bias[j]                                  */
+#define GSC_EPI_RELU 2       /* v = max(v, 0)                                 */
+#define GSC_EPI_MUL 4        /* v *= mul[i, j]     (mask product)             */
+#define GSC_EPI_GATE 8       /* v = gate[i, j] > 0 ? v : 0  (ReLU backward)   */
+#define GSC_EPI_CLAMP1 16    /* v = min(max(v, -1), 1)                        */
+
+int gsc_version(void);
+const char* gsc_last_error(void);
+
+/* ---- batch packer ------------------------------------------------------------------------
+ * Replaces the graph part of Batch.from_data_list (reference src/rlsp/agents/buffer.py:65-81,
+ * src/rlsp/agents/simple_ddpg.py:29-38) and the per-call remove_self_loops + add_self_loops of
+ * GATv2Conv.forward (called at reference src/rlsp/agents/models.py:38,47).
+ * In : edge_index[2, E] int64 COO (row 0 = source, row 1 = target; node ids already offset per
+ *      graph), batch[Nt] int64 sorted graph id of every node (NULL => one graph).
+ * Out: CSR by target with exactly one self-loop per node, stored last in its row:
+ *      rowptr[Nt+1], col[<= E+Nt] (sources, ascending within a row), graph_ptr[B+1],
+ *      stats[4] = {Et (edges incl. self-loops), max nodes per graph, error flag, 0}.
+ * stats[2] != 0 means an edge endpoint or graph id was out of range. */
+size_t gsc_pack_csr_workspace_bytes(int64_t num_nodes, int64_t num_edges);
+int gsc_pack_csr(const int64_t* edge_index, int64_t num_edges, const int64_t* batch,
+                 int64_t num_nodes, int64_t num_graphs, int32_t* rowptr, int32_t* col,
+                 int32_t* graph_ptr, int32_t* stats, void* workspace, size_t workspace_bytes,
+                 void* stream);
+
+/* ---- GNN embedder ------------------------------------------------------------------------
+ * Replaces GNNEmbedder.forward (reference src/rlsp/agents/models.py:37-53): encoder GATv2Conv,
+ * ReLU, num_iter x (num_layers-1) process GATv2Conv applications, global_mean_pool -- one launch.
+ * params: flat fp32, per conv in state-dict order {att[H], bias[H], lin_l.weight[H,in],
+ *         lin_l.bias[H], lin_r.weight[H,in], lin_r.bias[H]}, encoder (in = in_dim) first, then
+ *         process[0..num_layers-2] (in = H).
+ * emb   : [B, H] output.
+ * saved : NULL for inference, else gsc_gnn_saved_floats() floats receiving what backward needs.
+ * max_nodes: upper bound on nodes per graph (stats[1] of the packer). */
+int64_t gsc_gnn_param_floats(int in_dim, int hidden, int num_layers);
+int64_t gsc_gnn_saved_floats(int64_t num_nodes, int hidden, int num_layers, int num_iter);
+int gsc_gnn_embed_fwd(const float* x, int64_t num_nodes, int in_dim, const int32_t* rowptr,
+                      const int32_t* col, const int32_t* graph_ptr, int64_t num_graphs,
+                      int max_nodes, const float* params, int hidden, int num_layers, int num_iter,
+                      float* emb, float* saved, void* stream);
+
+/* Backward of the above (the reference gets it from torch autograd: loss.backward() at
+ * reference src/rlsp/agents/simple_ddpg.py:216,224).  d_params (same layout as params) is
+ * OVERWRITTEN with the gradient; process-conv weights applied several times receive the sum.
+ * The per-CTA partial sums live in the workspace and are reduced in a fixed order, so the result
+ * is deterministic. */
+size_t gsc_gnn_bwd_workspace_bytes(int64_t num_graphs, int in_dim, int hidden, int num_layers);
+int gsc_gnn_embed_bwd(const float* x, int64_t num_nodes, int in_dim, const int32_t* rowptr,
+                      const int32_t* col, const int32_t* graph_ptr, int64_t num_graphs,
+                      int max_nodes, const float* params, int hidden, int num_layers, int num_iter,
+                      const float* saved, const float* d_emb, float* d_params, void* workspace,
+                      size_t workspace_bytes, void* stream);
+
+/* ---- dense layers (PyG MLP: reference src/rlsp/agents/models.py:80-83,119-122) -------------
+ * One strided GEMM, C[M,N] = epilogue( sum_s A_s * B_s ), with up to three K-segments so that
+ * th.cat([emb, mask, a], 1) (reference models.py:90-91,150) is never materialised:
+ *   A_s(i,k) = A[s][i*a_rs[s] + k*a_cs[s]],  B_s(k,j) = B[s][k*b_rs[s] + j*b_cs[s]],  k < K[s].
+ * Forward  (Linear):  A = input [M,K] (rs=ld, cs=1), B = weight[N, ldw] column slice (rs=1, cs=ldw).
+ * dgrad    (dX)    :  A = dY [M,N'],  B = weight slice (rs=ldw, cs=1).
+ * wgrad    (dW)    :  A = dY^T (rs=1, cs=ld), B = input (rs=ld, cs=1); reduction over the batch.
+ * Large-K / few-tile shapes are split along K into the workspace and reduced deterministically. */
+typedef struct {
+  const float* A[3];
+  const float* B[3];
+  int64_t K[3];
+  int64_t a_rs[3], a_cs[3];
+  int64_t b_rs[3], b_cs[3];
+  int num_seg;
+  int flags;             /* GSC_EPI_* */
+  const float* bias;     /* [N]          */
+  const float* mul;      /* [M, ld_mul]  */
+  int64_t ld_mul;
+  const float* gate;     /* [M, ld_gate] */
+  int64_t ld_gate;
+} gsc_gemm_args;
+
+size_t gsc_gemm_workspace_bytes(int64_t M, int64_t N, int64_t K_total);
+int gsc_gemm(const gsc_gemm_args* args, int64_t M, int64_t N, float* C, int64_t ldc,
+             void* workspace, size_t workspace_bytes, void* stream);
+
+/* out = x * mul (if mul != NULL), zeroed where gate <= 0 (if gate != NULL): the mask product of
+ * Actor.forward (reference src/rlsp/agents/models.py:153) and ReLU backward, for callers that hold
+ * an upstream gradient not produced by gsc_gemm's epilogue (torch autograd). */
+int gsc_mul_gate(const float* x, int64_t ldx, const float* mul, int64_t ld_mul, const float* gate,
+                 int64_t ld_gate, int64_t M, int64_t N, float* out, int64_t ldo, void* stream);
+
+/* out[j] = sum_i X[i*ld + j]  (bias gradients). */
+int gsc_colsum(const float* X, int64_t ld, int64_t M, int64_t N, float* out, void* stream);
+
+/* ---- TD target + MSE (reference src/rlsp/agents/simple_ddpg.py:206-212) -------------------
+ * y = r + (1-d)*gamma*q_next ; loss[0] = loss_scale * sum (q-y)^2 ; dq = 2*loss_scale*(q-y).
+ * loss_scale = 1/B_global so that data-parallel ranks sum to the batch mean. */
+int gsc_td_mse(const float* rewards, const float* dones, const float* q_next, const float* q,
+               float gamma, float loss_scale, int64_t B, float* y, float* dq, float* loss,
+               void* stream);
+
+/* ---- fused Adam + soft target update ------------------------------------------------------
+ * torch 1.13 Adam (reference src/rlsp/agents/simple_ddpg.py:162-163,217,225) followed by
+ * target <- tau*p + (1-tau)*target (reference :229-234) over one flat parameter buffer.
+ * step is the 1-based Adam step; target may be NULL (plain Adam). */
+int gsc_adam_soft_update(float* p, const float* g, float* m, float* v, float* target, int64_t n,
+                         float lr, float beta1, float beta2, float eps, int64_t step, float tau,
+                         void* stream);
+
+/* ---- actor head ---------------------------------------------------------------------------
+ * post_process_actions + normalize_scheduling_probabilities (reference
+ * src/rlsp/agents/simple_ddpg.py:374-395, 338-372), applied to R action vectors of A values each,
+ * groups of `group` consecutive destinations (N_max).  Arithmetic follows the scalar types of the
+ * reference's pinned numpy 1.23.4: fp64 sums / quotients / round(.,10) on the widened fp32 inputs,
+ * sequential in destination order.  out: [R, A] fp64.
+ * noise (nullable, [R, A] fp64 samples of N(rand_mu, rand_sigma)) first applies the exploration
+ * step of _choose_action (reference :190-199; scale_action/unscale_action of reference
+ * src/rlsp/agents/models.py:127-144 with scalar bounds low/high) in fp32 as numpy does. */
+int gsc_actor_head(const float* y, const double* noise, int64_t R, int64_t A, int group,
+                   float low, float high, double* out, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GSC_B200_H */
