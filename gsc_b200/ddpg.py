@@ -23,6 +23,7 @@ import numpy as np
 import torch
 
 from . import ops
+from .dp import allreduce_flat
 from .graph import GraphBatch
 from .models import Actor, QNetwork, net_backward, net_forward
 
@@ -46,7 +47,7 @@ class DDPGUpdater:
     # -- pieces, named after the reference methods ---------------------------------------------
     def _allreduce(self, flat_grad: torch.Tensor) -> None:
         if self.world_size > 1:
-            torch.distributed.all_reduce(flat_grad, op=torch.distributed.ReduceOp.SUM, group=self.pg)
+            allreduce_flat(flat_grad, self.pg)
 
     def update_critic(self, nxt: GraphBatch, cur: GraphBatch, dones, rewards, actions):
         """reference _update_critic (simple_ddpg.py:204-219)."""

@@ -21,6 +21,19 @@ def rel_err(got, ref):
     return float(np.abs(got - ref).max() / max(np.abs(ref).max(), 1e-30))
 
 
+def grad_err(got, ref, scale):
+    """Error of one gradient tensor relative to max(its own magnitude, 1e-3 x the largest gradient of
+    the network): tensors whose true gradient is ~0 (e.g. lin_r.bias, to which the segment softmax
+    is shift-invariant) hold only fp32 cancellation noise and cannot be judged against themselves."""
+    got = np.asarray(got, dtype=np.float64)
+    ref = np.asarray(ref, dtype=np.float64)
+    return float(np.abs(got - ref).max() / max(np.abs(ref).max(), 1e-3 * scale))
+
+
+def _gscale(g, prefix):
+    return max(float(np.abs(v).max()) for k, v in g.items() if k.startswith(prefix))
+
+
 def _nets(g, tau=1e-2):
     spec = AgentSpec(int(g["n_max"]), target_model_update=tau)
     nets = []
@@ -78,12 +91,12 @@ def test_autograd_path_matches_golden_gradients(golden_ddpg):
     q_opt.zero_grad()
     qf1_loss.backward()
     for k, p in qf1.named_parameters():
-        assert rel_err(p.grad.cpu().numpy(), g["gcritic_f64." + k]) < TOL, k
+        assert grad_err(p.grad.cpu().numpy(), g["gcritic_f64." + k], _gscale(g, "gcritic_f64.")) < TOL, k
     q_opt.step()
     actor_loss = -qf1(cur, actor(cur)).mean()
     actor_loss.backward()
     for k, p in actor.named_parameters():
-        assert rel_err(p.grad.cpu().numpy(), g["gactor_f64." + k]) < TOL, k
+        assert grad_err(p.grad.cpu().numpy(), g["gactor_f64." + k], _gscale(g, "gactor_f64.")) < TOL, k
 
 
 def test_fused_ddpg_step_matches_golden(golden_ddpg):
@@ -99,9 +112,9 @@ def test_fused_ddpg_step_matches_golden(golden_ddpg):
             gq = dict(zip([k for k, _ in qf1.named_parameters()], qf1.param_views(upd.g_critic)))
             ga = dict(zip([k for k, _ in actor.named_parameters()], actor.param_views(upd.g_actor)))
             for k, v in gq.items():
-                assert rel_err(v.cpu().numpy(), g["gcritic_f64." + k]) < TOL, k
+                assert grad_err(v.cpu().numpy(), g["gcritic_f64." + k], _gscale(g, "gcritic_f64.")) < TOL, k
             for k, v in ga.items():
-                assert rel_err(v.cpu().numpy(), g["gactor_f64." + k]) < TOL, k
+                assert grad_err(v.cpu().numpy(), g["gactor_f64." + k], _gscale(g, "gactor_f64.")) < TOL, k
     assert rel_err(np.array([float(ql), float(al)]), g["losses_f64"]) < TOL
     for k, p in actor.named_parameters():
         assert rel_err(p.detach().cpu().numpy(), g["post_actor_f64." + k]) < TOL, k
