@@ -16,6 +16,7 @@ _lib = None
 
 EPI_BIAS, EPI_RELU, EPI_MUL, EPI_GATE, EPI_CLAMP1 = 1, 2, 4, 8, 16
 MAX_HIDDEN = 32
+PACK_NOALLOC_MAX_NODES = 1 << 20
 
 
 class GemmArgs(Structure):
@@ -35,6 +36,8 @@ _PROTOS = {
     "gsc_pack_csr_workspace_bytes": (c_size_t, [c_int64, c_int64]),
     "gsc_pack_csr": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_int64, c_void_p, c_void_p,
                              c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+    "gsc_pack_csr_noalloc": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_int64, c_void_p, c_void_p,
+                                     c_void_p, c_void_p, c_void_p]),
     "gsc_gnn_param_floats": (c_int64, [c_int, c_int, c_int]),
     "gsc_gnn_saved_floats": (c_int64, [c_int64, c_int, c_int, c_int]),
     "gsc_gnn_embed_fwd": (c_int, [c_void_p, c_int64, c_int, c_void_p, c_void_p, c_void_p, c_int64,

@@ -8,6 +8,7 @@
 // All kernels are flat, coalesced, grid-stride; the row sort makes the neighbour order (and with
 // it every downstream fp32 sum) independent of the atomic fill order.
 #include "common.cuh"
+#include <mutex>
 
 namespace gsc {
 
@@ -227,4 +228,70 @@ extern "C" int gsc_pack_csr(const int64_t* edge_index, int64_t E, const int64_t*
   pack_max_nodes_kernel<<<flat_grid(B, 256), 256, 0, st>>>(graph_ptr, B, stats);
   GSC_LAUNCH_CHECK("pack_max_nodes_kernel");
   return GSC_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// gsc_pack_csr_noalloc: the packer for callers that cannot provide a workspace.
+//
+// gsc_pack_csr needs two scratch arrays (per-node degree counters that later serve as fill
+// cursors, and the scan's block totals) and expects the caller to allocate them.  Some callers of
+// this library cannot allocate device memory at the point where they pack a batch:
+//   * the per-environment-step rollout / serving loop (predict() on one small graph), which runs
+//     beside a training stream: a cudaMalloc there synchronises the whole device and stalls the
+//     update that is in flight;
+//   * an integrator binding the C-ABI from a host that was handed a fixed device-memory budget
+//     (only its input and output buffers) and owns no caching allocator such as torch's.
+// For them the scratch lives in the library image: a file-scope __device__ array, resident on every
+// GPU that loads libgsc_b200 from load to exit.  It covers batches of up to
+// GSC_PACK_NOALLOC_MAX_NODES nodes (4 B per node + 4 B per 1024 nodes, ~4.2 MB); larger batches
+// are rejected with GSC_EINVAL and must use gsc_pack_csr with a caller workspace.
+//
+// Rules of use:
+//   * The first call on each device resolves the array's device address (cudaGetSymbolAddress, with
+//     that device current) and caches it; make that first call before any stream capture begins.
+//   * Every call on a device shares the one array and finds in it whatever the previous call left.
+//     Nothing is assumed about those contents: the packer's own init/scan kernels rewrite every
+//     element they later read (degrees are set to 1, block totals are written before they are
+//     scanned, cursors are zeroed by the scan), so no separate clearing pass is needed.
+//   * Two calls whose kernels overlap on the same GPU (different streams, or different host
+//     threads) race on the array and corrupt each other's CSR.  Serialise them, or use gsc_pack_csr.
+// No cudaMalloc / cudaFree / allocating library routine is called here.
+namespace gsc {
+
+constexpr int64_t kNoAllocMaxNodes = GSC_PACK_NOALLOC_MAX_NODES;
+constexpr size_t kNoAllocScratchBytes =
+    ((size_t)kNoAllocMaxNodes * 4 + 255) / 256 * 256 +
+    (((size_t)(kNoAllocMaxNodes + kScanTile - 1) / kScanTile + 1) * 4 + 255) / 256 * 256;
+
+static __device__ __align__(256) unsigned char g_pack_scratch[kNoAllocScratchBytes];
+
+constexpr int kMaxDevices = 64;
+static void* g_pack_scratch_addr[kMaxDevices] = {nullptr};   // device address per ordinal, set once
+static std::mutex g_pack_scratch_mu;
+
+}  // namespace gsc
+
+extern "C" int gsc_pack_csr_noalloc(const int64_t* edge_index, int64_t E, const int64_t* batch, int64_t Nt,
+                                    int64_t B, int32_t* rowptr, int32_t* col, int32_t* graph_ptr,
+                                    int32_t* stats, void* stream_) {
+  GSC_REQUIRE(Nt >= 0 && Nt <= kNoAllocMaxNodes,
+              "gsc_pack_csr_noalloc: %lld nodes exceed the built-in scratch (max %lld nodes); "
+              "use gsc_pack_csr with a caller-provided workspace",
+              (long long)Nt, (long long)kNoAllocMaxNodes);
+  int dev = -1;
+  GSC_CUDA_TRY(cudaGetDevice(&dev));
+  GSC_REQUIRE(dev >= 0 && dev < kMaxDevices, "gsc_pack_csr_noalloc: device ordinal %d not supported", dev);
+  std::lock_guard<std::mutex> lock(g_pack_scratch_mu);
+  void* scratch = g_pack_scratch_addr[dev];
+  if (scratch == nullptr) {
+    // `g_pack_scratch` named in host code is only a handle; the kernels need its device address.
+    GSC_CUDA_TRY(cudaGetSymbolAddress(&scratch, g_pack_scratch));
+    GSC_REQUIRE(scratch != nullptr, "gsc_pack_csr_noalloc: cudaGetSymbolAddress returned null");
+    g_pack_scratch_addr[dev] = scratch;
+  }
+  if (gsc_pack_csr_workspace_bytes(Nt, E) > kNoAllocScratchBytes)
+    return fail(GSC_EINVAL, "gsc_pack_csr_noalloc: batch needs %zu scratch bytes, built-in array has %zu",
+                gsc_pack_csr_workspace_bytes(Nt, E), kNoAllocScratchBytes);
+  return gsc_pack_csr(edge_index, E, batch, Nt, B, rowptr, col, graph_ptr, stats, scratch,
+                      kNoAllocScratchBytes, stream_);
 }

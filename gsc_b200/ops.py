@@ -97,6 +97,37 @@ def pack_csr(edge_index: torch.Tensor, batch: Optional[torch.Tensor], num_nodes:
     return rowptr, col, graph_ptr, stats
 
 
+def pack_csr_noalloc(edge_index: torch.Tensor, batch: Optional[torch.Tensor], num_nodes: int, num_graphs: int,
+                     out: Optional[tuple] = None):
+    """``pack_csr`` through the entry point that takes no workspace and allocates nothing (its
+    scratch is a fixed array inside the library, at most ``_lib.PACK_NOALLOC_MAX_NODES`` nodes).
+
+    For the per-step rollout / serving loop, where a device allocation would stall the training
+    stream, and for hosts without an allocator.  Pass ``out=(rowptr, col, graph_ptr, stats)``
+    preallocated int32 tensors to keep the call itself allocation-free; calls that overlap on one
+    GPU share the scratch and must be serialised."""
+    _need_cuda(edge_index, batch)
+    lib = _lib.load()
+    dev = edge_index.device
+    if edge_index.dtype != torch.int64 or not edge_index.is_contiguous():
+        raise _lib.GscError("pack_csr_noalloc: edge_index must be a contiguous int64 tensor")
+    if batch is not None and (batch.dtype != torch.int64 or not batch.is_contiguous()):
+        raise _lib.GscError("pack_csr_noalloc: batch must be a contiguous int64 tensor")
+    E = int(edge_index.shape[1])
+    if out is None:
+        out = (torch.empty(num_nodes + 1, dtype=torch.int32, device=dev),
+               torch.empty(E + num_nodes, dtype=torch.int32, device=dev),
+               torch.empty(num_graphs + 1, dtype=torch.int32, device=dev),
+               torch.empty(4, dtype=torch.int32, device=dev))
+    rowptr, col, graph_ptr, stats = out
+    with _Timed("pack_csr_noalloc"):
+        check(lib.gsc_pack_csr_noalloc(_ptr(edge_index), E, _ptr(batch), num_nodes, num_graphs, _ptr(rowptr),
+                                       _ptr(col), _ptr(graph_ptr), _ptr(stats), _stream()),
+              "gsc_pack_csr_noalloc")
+    _count(9 if E > 0 else 7)
+    return rowptr, col, graph_ptr, stats
+
+
 def gnn_param_floats(in_dim: int, hidden: int, num_layers: int) -> int:
     return int(_lib.load().gsc_gnn_param_floats(in_dim, hidden, num_layers))
 

@@ -55,6 +55,21 @@ int gsc_pack_csr(const int64_t* edge_index, int64_t num_edges, const int64_t* ba
                  int32_t* graph_ptr, int32_t* stats, void* workspace, size_t workspace_bytes,
                  void* stream);
 
+/* Same packer, same outputs, but no workspace argument and no allocation anywhere: the scratch is a
+ * fixed array inside the library image, resident on every GPU that loads the library.  This entry
+ * point has NO counterpart in the reference.  It exists for callers that cannot allocate device
+ * memory when they pack: the per-environment-step rollout/serving loop running beside a training
+ * stream (a cudaMalloc there synchronises the device and stalls the update in flight), and hosts
+ * that bind this C-ABI with a fixed device-memory budget and no caching allocator.
+ * Limit: num_nodes <= GSC_PACK_NOALLOC_MAX_NODES, otherwise GSC_EINVAL (use gsc_pack_csr).
+ * The first call on a device looks up the array's device address -- make it before any stream
+ * capture.  All calls on a device share the array: the packer rewrites every element it reads, so
+ * stale contents are harmless, but calls that overlap on the GPU race and must be serialised. */
+#define GSC_PACK_NOALLOC_MAX_NODES (1 << 20)
+int gsc_pack_csr_noalloc(const int64_t* edge_index, int64_t num_edges, const int64_t* batch,
+                         int64_t num_nodes, int64_t num_graphs, int32_t* rowptr, int32_t* col,
+                         int32_t* graph_ptr, int32_t* stats, void* stream);
+
 /* ---- GNN embedder ------------------------------------------------------------------------
  * Replaces GNNEmbedder.forward (reference src/rlsp/agents/models.py:37-53): encoder GATv2Conv,
  * ReLU, num_iter x (num_layers-1) process GATv2Conv applications, global_mean_pool -- one launch.
