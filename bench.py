@@ -127,6 +127,7 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=dev)
     w = make_workload(args, rank)
     B, n_max = w["B"], w["n_max"]
+    ops.precision = args.precision
     spec = AgentSpec(n_max)
     torch.manual_seed(1234)
     actor = Actor(spec).to(dev)
@@ -266,8 +267,11 @@ def run_ours(args):
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32" if args.precision == "fp32" else "tf32 tensor-core GEMMs (fp32 accumulate), f32 elsewhere",
+            "data": "synthetic",
             "config": {"workload": workload_name(w), "states_per_gpu": B, "n_max": n_max,
+                       "precision": args.precision,
                        "weights": "reference init (PyG glorot / torch Linear), torch.manual_seed(1234)",
                        "l2": "flushed between timed steps (256 MiB write)",
                        "parallelism": f"dp{world}" if w["kind"] == "c3" else f"replicas{world}"},
@@ -391,6 +395,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default=os.environ.get("GSC_BENCH_WORKLOAD", "c2"), choices=["c2", "c3"])
     ap.add_argument("--batch", type=int, default=0)
+    ap.add_argument("--precision", default=os.environ.get("GSC_BENCH_PRECISION", "tf32"), choices=["fp32", "tf32"],
+                    help="dense layers: exact fp32 FMA kernel, or tcgen05 tensor cores (TF32 operands, fp32 accumulate)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":

@@ -12,6 +12,11 @@
 
 namespace gsc {
 
+// gemm_tc.cu
+bool gemm_tc_supported(const gsc_gemm_args* a, int64_t M, int64_t N, bool* a_mn, bool* b_mn);
+int gemm_tc_launch(const gsc_gemm_args* a, int64_t M, int64_t N, float* C, int64_t ldc, void* workspace,
+                   size_t workspace_bytes, bool a_mn, bool b_mn, cudaStream_t st, int* used_splits);
+
 constexpr int kBM = 64, kBN = 64, kBK = 16, kGemmThreads = 256, kPad = 4;
 
 struct GemmDev {
@@ -202,7 +207,13 @@ extern "C" size_t gsc_gemm_workspace_bytes(int64_t M, int64_t N, int64_t K_total
   // upper bound over any segmentation of K_total into <= 3 segments
   if (M <= 0 || N <= 0) return 0;
   const int tiles = (int)(ceil_div(K_total > 0 ? K_total : 1, kBK) + 2);
-  const int64_t s = max_splits(M, N, tiles);
+  int64_t s = max_splits(M, N, tiles);
+  // tensor-core path: 128x128 tiles, up to one split per SM, >= 4 k-blocks of 32 per split
+  const int64_t tc_tiles = ceil_div(M, 128) * ceil_div(N, 128);
+  int64_t tc = tc_tiles >= kNumSMs ? 1 : ceil_div(kNumSMs, tc_tiles);
+  const int64_t tc_by_k = (ceil_div(K_total > 0 ? K_total : 1, 32) + 2) / 4;
+  if (tc > tc_by_k) tc = tc_by_k;
+  if (tc > s) s = tc;
   return s > 1 ? (size_t)s * (size_t)M * (size_t)N * 4 : 0;
 }
 
@@ -228,6 +239,24 @@ extern "C" int gsc_gemm(const gsc_gemm_args* a, int64_t M, int64_t N, float* C, 
   GSC_REQUIRE(!(g.flags & GSC_EPI_MUL) || g.mul, "gsc_gemm: GSC_EPI_MUL without mul");
   GSC_REQUIRE(!(g.flags & GSC_EPI_GATE) || g.gate, "gsc_gemm: GSC_EPI_GATE without gate");
   g.M = M; g.N = N; g.ldc = ldc; g.C = C;
+  if (a->flags & GSC_EPI_TF32) {
+    bool a_mn = false, b_mn = false;
+    // tiny problems stay on the exact path: the tensor-core pipeline has a fixed fill cost
+    if ((double)M * (double)N * (double)tiles * kBK >= 4.0e6 && gemm_tc_supported(a, M, N, &a_mn, &b_mn)) {
+      int splits = 1;
+      int rc = gemm_tc_launch(a, M, N, C, ldc, workspace, workspace_bytes, a_mn, b_mn, st, &splits);
+      if (rc) return rc;
+      if (splits > 1) {
+        g.splits = splits;
+        g.partial = (float*)workspace;
+        int64_t blocks = ceil_div(M * N, 256);
+        if (blocks > 8 * kNumSMs) blocks = 8 * kNumSMs;
+        gemm_finalize_kernel<<<(int)blocks, 256, 0, st>>>(g);
+        GSC_LAUNCH_CHECK("gemm_finalize_kernel");
+      }
+      return GSC_OK;
+    }
+  }
   g.tiles_total = tiles;
   plan_split(M, N, tiles, &g.splits, &g.tiles_per_split);
   if (g.splits > 1) {

@@ -1,0 +1,412 @@
+// Tensor-core path of gsc_gemm (GSC_EPI_TF32): tcgen05.mma kind::tf32, fp32 accumulation in TMEM,
+// operands streamed by TMA (128-byte swizzle) through a multi-stage shared-memory ring.
+//
+// Serves the dense layers of the PyG MLP (reference src/rlsp/agents/models.py:80-83,119-122) in
+// all three roles -- forward (both operands K-major), dgrad (B MN-major) and wgrad (both MN-major)
+// -- with the same K-segment / epilogue contract as the exact-fp32 SIMT kernel in gemm.cu.
+//
+// CTA = 192 threads, persistent over (m-tile, n-tile, k-split) work items:
+//   warp 0      TMA producer   one elected lane issues cp.async.bulk.tensor per stage
+//   warp 1      MMA issuer     one elected lane issues 4 x tcgen05.mma (K = 8 each) per 32-wide
+//                              k-block; tcgen05.commit frees the stage / publishes the accumulator
+//   warps 2..5  epilogue       tcgen05.ld (32 lanes x 32 columns per warp), bias/ReLU/mask/gate/
+//                              clamp, 128-byte row segments to global
+// Tile 128 x 128, two TMEM accumulator buffers (2 x 128 columns) so the epilogue of tile i overlaps
+// the loads and MMAs of tile i+1.  Roofline: HBM for the mask/action/output streams
+// (4(MK + KN + MN) algorithmic bytes), tensor pipe (TF32) for large-batch shapes.
+#include "common.cuh"
+#include <cuda.h>
+#include <mutex>
+
+namespace gsc {
+
+constexpr int kTcBM = 128, kTcBN = 128, kTcBK = 32;          // fp32 elements; BK * 4 B = one 128 B swizzle row
+constexpr int kTcStages = 6;
+constexpr int kTcThreads = 192;
+constexpr int kTcStageBytes = (kTcBM + kTcBN) * kTcBK * 4;   // 32 KB
+constexpr int kTcSmemBytes = kTcStages * kTcStageBytes + 1024 /*align*/ + 256 /*barriers*/;
+constexpr int kTmemCols = 2 * kTcBN;                          // 256
+
+struct TcParams {
+  int64_t M, N, ldc, ld_mul, ld_gate;
+  float* C;
+  float* partial;
+  const float* bias;
+  const float* mul;
+  const float* gate;
+  int flags, num_seg;
+  int kb_end[3];          // exclusive prefix of 32-wide k-blocks per segment
+  int kb_total, kb_per_split, splits, tiles_m, tiles_n;
+};
+
+// ---------------------------------------------------------------- PTX helpers
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred P1;\n"
+      "LAB_WAIT:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
+      "@P1 bra DONE;\n"
+      "bra LAB_WAIT;\n"
+      "DONE:\n"
+      "}" ::"r"(bar), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tc_mma_tf32(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+                                            uint32_t accumulate) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "setp.ne.b32 p, %4, 0;\n"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n"
+      "}" ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void tc_ld32(uint32_t taddr, float (&v)[32]) {
+  uint32_t r[32];
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+        "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+        "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+  for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+}
+
+// Shared-memory matrix descriptor (sm_100 version bit), byte offsets >> 4.
+//   K-major operands : SWIZZLE_128B (layout type 2), 16-byte swizzle atoms, 8-row groups (SBO = 1024 B).
+//   MN-major fp32    : SWIZZLE_128B_BASE32B (layout type 1): 32-bit types transposed by the tensor core
+//                      need 32-byte swizzle atoms, the pattern repeats every 4 k-rows (SBO = 512 B) and
+//                      the 32-wide MN blocks are LBO apart; TMA writes it with SWIZZLE_128B_ATOM_32B.
+__device__ __forceinline__ uint64_t smem_desc(uint32_t addr, uint32_t lbo_bytes, uint32_t sbo_bytes, uint32_t layout) {
+  return (uint64_t)((addr >> 4) & 0x3FFF) | ((uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16) |
+         ((uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32) | (1ULL << 46) | ((uint64_t)layout << 61);
+}
+
+__device__ __forceinline__ float tc_epilogue(const TcParams& p, float v, int64_t i, int64_t j) {
+  if (p.flags & GSC_EPI_BIAS) v += p.bias[j];
+  if (p.flags & GSC_EPI_RELU) v = fmaxf(v, 0.f);
+  if (p.flags & GSC_EPI_MUL) v *= p.mul[i * p.ld_mul + j];
+  if (p.flags & GSC_EPI_GATE) v = p.gate[i * p.ld_gate + j] > 0.f ? v : 0.f;
+  if (p.flags & GSC_EPI_CLAMP1) v = fminf(fmaxf(v, -1.f), 1.f);
+  return v;
+}
+
+struct WorkItem {
+  int m0, n0, split, kb_begin, kb_end;
+};
+__device__ __forceinline__ WorkItem decode_work(const TcParams& p, int w) {
+  WorkItem it;
+  const int tm = w % p.tiles_m;
+  const int rest = w / p.tiles_m;
+  const int tn = rest % p.tiles_n;
+  it.split = rest / p.tiles_n;
+  it.m0 = tm * kTcBM;
+  it.n0 = tn * kTcBN;
+  it.kb_begin = it.split * p.kb_per_split;
+  it.kb_end = min(p.kb_total, it.kb_begin + p.kb_per_split);
+  return it;
+}
+
+template <bool A_MN, bool B_MN>
+__global__ void __launch_bounds__(kTcThreads, 1)
+gemm_tc_kernel(const __grid_constant__ TcParams p, const __grid_constant__ CUtensorMap mapA0,
+               const __grid_constant__ CUtensorMap mapA1, const __grid_constant__ CUtensorMap mapA2,
+               const __grid_constant__ CUtensorMap mapB0, const __grid_constant__ CUtensorMap mapB1,
+               const __grid_constant__ CUtensorMap mapB2) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;       // 1024 B: swizzle-128B atoms
+  const uint32_t bar_base = smem_base + kTcStages * kTcStageBytes;
+  // barriers: full[S], empty[S], tmem_full[2], tmem_empty[2], then the TMEM base address slot
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (kTcStages + s); };
+  auto tfull_bar = [&](int s) { return bar_base + 8u * (2 * kTcStages + s); };
+  auto tempty_bar = [&](int s) { return bar_base + 8u * (2 * kTcStages + 2 + s); };
+  const uint32_t tmem_slot = bar_base + 8u * (2 * kTcStages + 4);
+  uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int total_work = p.tiles_m * p.tiles_n * p.splits;
+
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < kTcStages; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+    for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), 4); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 2) {   // one warp allocates TMEM (256 columns) and later frees it
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(kTmemCols));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot_ptr;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
+        const WorkItem it = decode_work(p, w);
+        for (int kb = it.kb_begin; kb < it.kb_end; ++kb) {
+          int s = 0;
+          while (s < p.num_seg - 1 && kb >= p.kb_end[s]) ++s;
+          const int k0 = (kb - (s ? p.kb_end[s - 1] : 0)) * kTcBK;
+          const CUtensorMap* mA = s == 0 ? &mapA0 : (s == 1 ? &mapA1 : &mapA2);
+          const CUtensorMap* mB = s == 0 ? &mapB0 : (s == 1 ? &mapB1 : &mapB2);
+          mbar_wait(empty_bar(stage), phase ^ 1u);
+          mbar_expect_tx(full_bar(stage), kTcStageBytes);
+          const uint32_t sa = smem_base + stage * kTcStageBytes;
+          const uint32_t sb = sa + kTcBM * kTcBK * 4;
+          if (!A_MN) {
+            tma_load_2d(sa, mA, full_bar(stage), k0, it.m0);                       // box {32 k, 128 m}
+          } else {
+#pragma unroll
+            for (int b = 0; b < kTcBM / 32; ++b)                                    // box {32 m, 32 k}
+              tma_load_2d(sa + b * 4096, mA, full_bar(stage), it.m0 + 32 * b, k0);
+          }
+          if (!B_MN) {
+            tma_load_2d(sb, mB, full_bar(stage), k0, it.n0);                       // box {32 k, 128 n}
+          } else {
+#pragma unroll
+            for (int b = 0; b < kTcBN / 32; ++b)                                    // box {32 n, 32 k}
+              tma_load_2d(sb + b * 4096, mB, full_bar(stage), it.n0 + 32 * b, k0);
+          }
+          if (++stage == kTcStages) { stage = 0; phase ^= 1u; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      // instruction descriptor: D=f32, A=B=tf32, M=128, N=128, major bits
+      const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((A_MN ? 1u : 0u) << 15) |
+                             ((B_MN ? 1u : 0u) << 16) | ((uint32_t)(kTcBN >> 3) << 17) |
+                             ((uint32_t)(kTcBM >> 4) << 24);
+      int stage = 0;
+      uint32_t phase = 0;
+      int iter = 0;
+      for (int w = blockIdx.x; w < total_work; w += gridDim.x, ++iter) {
+        const WorkItem it = decode_work(p, w);
+        const int as = iter & 1;
+        mbar_wait(tempty_bar(as), (((uint32_t)iter >> 1) & 1u) ^ 1u);
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + (uint32_t)(as * kTcBN);
+        for (int kb = it.kb_begin; kb < it.kb_end; ++kb) {
+          mbar_wait(full_bar(stage), phase);
+          tc_fence_after();
+          const uint32_t sa = smem_base + stage * kTcStageBytes;
+          const uint32_t sb = sa + kTcBM * kTcBK * 4;
+#pragma unroll
+          for (int j = 0; j < kTcBK / 8; ++j) {
+            // K-major: 8 k = 32 B further inside the 128 B swizzle row.  MN-major: next 8-row k group.
+            const uint64_t da = A_MN ? smem_desc(sa + j * 1024, 4096, 512, 1) : smem_desc(sa + j * 32, 16, 1024, 2);
+            const uint64_t db = B_MN ? smem_desc(sb + j * 1024, 4096, 512, 1) : smem_desc(sb + j * 32, 16, 1024, 2);
+            tc_mma_tf32(tmem_d, da, db, idesc, (kb > it.kb_begin || j > 0) ? 1u : 0u);
+          }
+          tc_commit(empty_bar(stage));            // frees the smem stage once these MMAs retire
+          if (++stage == kTcStages) { stage = 0; phase ^= 1u; }
+        }
+        tc_commit(tfull_bar(as));                 // accumulator complete -> epilogue
+      }
+    }
+  } else {
+    // ===================== epilogue warps (2..5) =====================
+    const int quad = warp & 3;                    // TMEM lane quadrant this warp may access
+    int iter = 0;
+    for (int w = blockIdx.x; w < total_work; w += gridDim.x, ++iter) {
+      const WorkItem it = decode_work(p, w);
+      const int as = iter & 1;
+      mbar_wait(tfull_bar(as), ((uint32_t)iter >> 1) & 1u);
+      tc_fence_after();
+      const int64_t row = (int64_t)it.m0 + quad * 32 + lane;
+#pragma unroll 1
+      for (int c = 0; c < kTcBN / 32; ++c) {
+        float v[32];
+        tc_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(as * kTcBN + c * 32), v);
+        const int64_t col0 = (int64_t)it.n0 + c * 32;
+        if (row < p.M && col0 < p.N) {
+          if (p.splits == 1) {
+            float* dst = p.C + row * p.ldc + col0;
+            if (col0 + 32 <= p.N && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+#pragma unroll
+              for (int q = 0; q < 8; ++q) {
+                float4 o;
+                o.x = tc_epilogue(p, v[4 * q + 0], row, col0 + 4 * q + 0);
+                o.y = tc_epilogue(p, v[4 * q + 1], row, col0 + 4 * q + 1);
+                o.z = tc_epilogue(p, v[4 * q + 2], row, col0 + 4 * q + 2);
+                o.w = tc_epilogue(p, v[4 * q + 3], row, col0 + 4 * q + 3);
+                reinterpret_cast<float4*>(dst)[q] = o;
+              }
+            } else {
+#pragma unroll
+              for (int q = 0; q < 32; ++q)
+                if (col0 + q < p.N) dst[q] = tc_epilogue(p, v[q], row, col0 + q);
+            }
+          } else {
+            float* dst = p.partial + ((int64_t)it.split * p.M + row) * p.N + col0;
+#pragma unroll
+            for (int q = 0; q < 32; ++q)
+              if (col0 + q < p.N) dst[q] = v[q];
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tempty_bar(as));
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kTmemCols));
+  }
+}
+
+// ---------------------------------------------------------------- host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* sym = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(sym);
+  });
+  return fn;
+}
+
+// 2-D fp32 tensor map: inner extent `inner` (contiguous), `rows` rows of `row_stride` floats.
+static int make_map(CUtensorMap* map, const float* base, int64_t inner, int64_t rows, int64_t row_stride,
+                    int box_inner, int box_rows, int tf32_round, bool mn_major) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (!fn) return fail(GSC_ECUDA, "gemm_tc: cuTensorMapEncodeTiled is not available from the driver");
+  cuuint64_t dims[2] = {(cuuint64_t)inner, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)row_stride * 4};
+  cuuint32_t box[2] = {(cuuint32_t)box_inner, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(map, tf32_round ? CU_TENSOR_MAP_DATA_TYPE_TFLOAT32 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2,
+                  const_cast<float*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  mn_major ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS)
+    return fail(GSC_ECUDA, "gemm_tc: cuTensorMapEncodeTiled failed (%d) inner=%lld rows=%lld stride=%lld", (int)r,
+                (long long)inner, (long long)rows, (long long)row_stride);
+  return GSC_OK;
+}
+
+static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+// Can this problem run on the TMA-fed tensor-core kernel?  (16-byte aligned bases, row strides
+// that are multiples of 4 floats, a consistent major-ness across segments.)
+bool gemm_tc_supported(const gsc_gemm_args* a, int64_t M, int64_t N, bool* a_mn, bool* b_mn) {
+  if (M < 1 || N < 8) return false;
+  bool amn = false, bmn = false;
+  for (int s = 0; s < a->num_seg; ++s) {
+    if (a->K[s] <= 0) return false;
+    const bool ak = a->a_cs[s] == 1, am = a->a_rs[s] == 1 && !ak;
+    const bool bk = a->b_rs[s] == 1, bm = a->b_cs[s] == 1 && !bk;
+    if (!(ak || am) || !(bk || bm)) return false;
+    if (s == 0) { amn = am; bmn = bm; }
+    else if (amn != am || bmn != bm) return false;
+    const int64_t a_stride = am ? a->a_cs[s] : a->a_rs[s];
+    const int64_t b_stride = bm ? a->b_rs[s] : a->b_cs[s];
+    if (a_stride % 4 || b_stride % 4 || a_stride <= 0 || b_stride <= 0) return false;
+    if (!aligned16(a->A[s]) || !aligned16(a->B[s])) return false;
+  }
+  if (amn && !bmn) return false;      // not needed by any layer; not instantiated
+  *a_mn = amn; *b_mn = bmn;
+  return true;
+}
+
+static int tc_round_mode() {
+  static int mode = -1;
+  if (mode < 0) {
+    const char* e = getenv("GSC_TF32_TMA_ROUND");
+    mode = (e && e[0] == '0') ? 0 : 1;
+  }
+  return mode;
+}
+
+int gemm_tc_launch(const gsc_gemm_args* a, int64_t M, int64_t N, float* C, int64_t ldc, void* workspace,
+                   size_t workspace_bytes, bool a_mn, bool b_mn, cudaStream_t st, int* used_splits) {
+  TcParams p{};
+  CUtensorMap maps[6];
+  memset(maps, 0, sizeof(maps));
+  int kb = 0;
+  const int rnd = tc_round_mode();
+  for (int s = 0; s < a->num_seg; ++s) {
+    int rc;
+    if (!a_mn) rc = make_map(&maps[s], a->A[s], a->K[s], M, a->a_rs[s], kTcBK, kTcBM, rnd, false);
+    else rc = make_map(&maps[s], a->A[s], M, a->K[s], a->a_cs[s], 32, kTcBK, rnd, true);
+    if (rc) return rc;
+    if (!b_mn) rc = make_map(&maps[3 + s], a->B[s], a->K[s], N, a->b_cs[s], kTcBK, kTcBN, rnd, false);
+    else rc = make_map(&maps[3 + s], a->B[s], N, a->K[s], a->b_rs[s], 32, kTcBK, rnd, true);
+    if (rc) return rc;
+    kb += (int)ceil_div(a->K[s], kTcBK);
+    p.kb_end[s] = kb;
+  }
+  for (int s = a->num_seg; s < 3; ++s) { maps[s] = maps[0]; maps[3 + s] = maps[3]; p.kb_end[s] = kb; }
+  p.M = M; p.N = N; p.ldc = ldc; p.C = C; p.flags = a->flags; p.num_seg = a->num_seg;
+  p.bias = a->bias; p.mul = a->mul; p.gate = a->gate; p.ld_mul = a->ld_mul; p.ld_gate = a->ld_gate;
+  p.kb_total = kb;
+  p.tiles_m = (int)ceil_div(M, kTcBM);
+  p.tiles_n = (int)ceil_div(N, kTcBN);
+  const int64_t tiles = (int64_t)p.tiles_m * p.tiles_n;
+  // split K when the output tiles alone cannot fill the machine; keep >= 4 k-blocks per split
+  int64_t want = tiles >= kNumSMs ? 1 : ceil_div(kNumSMs, tiles);
+  int64_t max_by_k = kb / 4 > 0 ? kb / 4 : 1;
+  if (want > max_by_k) want = max_by_k;
+  if (workspace == nullptr) want = 1;
+  while (want > 1 && (size_t)want * (size_t)M * (size_t)N * 4 > workspace_bytes) --want;
+  p.kb_per_split = (int)ceil_div(kb, want);
+  p.splits = (int)ceil_div(kb, p.kb_per_split);
+  p.partial = (float*)workspace;
+  *used_splits = p.splits;
+  const int64_t work = tiles * p.splits;
+  const int grid = (int)(work < kNumSMs ? work : kNumSMs);
+
+  auto launch = [&](auto kernel) -> int {
+    GSC_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemBytes));
+    kernel<<<grid, kTcThreads, kTcSmemBytes, st>>>(p, maps[0], maps[1], maps[2], maps[3], maps[4], maps[5]);
+    GSC_LAUNCH_CHECK("gemm_tc_kernel");
+    return GSC_OK;
+  };
+  if (!a_mn && !b_mn) return launch(gemm_tc_kernel<false, false>);
+  if (!a_mn && b_mn) return launch(gemm_tc_kernel<false, true>);
+  return launch(gemm_tc_kernel<true, true>);
+}
+
+}  // namespace gsc

@@ -30,6 +30,7 @@ struct GnnArgs {
   const float* d_emb;     // bwd only
   float* partials;        // bwd only: [gridDim.x][param_floats]
   int64_t Nt;
+  int64_t emb_ld;         // row stride of emb (fwd) / d_emb (bwd), floats
   int B, in_dim, H, num_convs, num_apps, G, cap;
   int app_conv[GSC_MAX_APPS];
   int app_relu[GSC_MAX_APPS];
@@ -215,7 +216,7 @@ __global__ void __launch_bounds__(kGnnThreads, 2) gnn_fwd_kernel(const GnnArgs p
         const int n0 = p.graph_ptr[g] - nbase, n1 = p.graph_ptr[g + 1] - nbase;
         float s = 0.f;
         for (int i = n0; i < n1; ++i) s += hx_s[(size_t)i * HP + c];
-        p.emb[(size_t)g * p.H + c] = (n1 > n0) ? s / (float)(n1 - n0) : 0.f;
+        p.emb[(size_t)g * p.emb_ld + c] = (n1 > n0) ? s / (float)(n1 - n0) : 0.f;
       }
     }
     __syncthreads();
@@ -261,7 +262,7 @@ __global__ void __launch_bounds__(kGnnThreads, 1) gnn_bwd_kernel(const GnnArgs p
     for (int t = threadIdx.x; t < (g1 - g0) * HP; t += kGnnThreads) {
       const int g = g0 + t / HP, c = t % HP;
       const int n0 = p.graph_ptr[g] - nbase, n1 = p.graph_ptr[g + 1] - nbase;
-      const float v = (c < p.H && n1 > n0) ? p.d_emb[(size_t)g * p.H + c] / (float)(n1 - n0) : 0.f;
+      const float v = (c < p.H && n1 > n0) ? p.d_emb[(size_t)g * p.emb_ld + c] / (float)(n1 - n0) : 0.f;
       for (int i = n0; i < n1; ++i) dout_s[(size_t)i * HP + c] = v;
     }
     __syncthreads();
@@ -535,12 +536,12 @@ extern "C" int64_t gsc_gnn_saved_floats(int64_t num_nodes, int hidden, int num_l
 extern "C" int gsc_gnn_embed_fwd(const float* x, int64_t Nt, int in_dim, const int32_t* rowptr,
                                  const int32_t* col, const int32_t* graph_ptr, int64_t B, int max_nodes,
                                  const float* params, int H, int num_layers, int num_iter, float* emb,
-                                 float* saved, void* stream) {
+                                 int64_t emb_ld, float* saved, void* stream) {
   GnnArgs a{};
   int rc = build_args(a, x, Nt, in_dim, rowptr, col, graph_ptr, B, max_nodes, params, H, num_layers, num_iter);
   if (rc) return rc;
-  GSC_REQUIRE(emb, "gnn fwd: null emb");
-  a.emb = emb; a.saved = saved;
+  GSC_REQUIRE(emb && emb_ld >= H, "gnn fwd: null emb or emb_ld < hidden");
+  a.emb = emb; a.saved = saved; a.emb_ld = emb_ld;
   cudaStream_t st = (cudaStream_t)stream;
   switch (pick_hp(H)) {
     case 8: return launch_fwd<8>(a, st);
@@ -558,12 +559,13 @@ extern "C" size_t gsc_gnn_bwd_workspace_bytes(int64_t B, int in_dim, int H, int 
 extern "C" int gsc_gnn_embed_bwd(const float* x, int64_t Nt, int in_dim, const int32_t* rowptr,
                                  const int32_t* col, const int32_t* graph_ptr, int64_t B, int max_nodes,
                                  const float* params, int H, int num_layers, int num_iter,
-                                 const float* saved, const float* d_emb, float* d_params,
+                                 const float* saved, const float* d_emb, int64_t d_emb_ld, float* d_params,
                                  void* workspace, size_t workspace_bytes, void* stream) {
   GnnArgs a{};
   int rc = build_args(a, x, Nt, in_dim, rowptr, col, graph_ptr, B, max_nodes, params, H, num_layers, num_iter);
   if (rc) return rc;
-  GSC_REQUIRE(saved && d_emb && d_params && workspace, "gnn bwd: null pointer");
+  GSC_REQUIRE(saved && d_emb && d_params && workspace && d_emb_ld >= H, "gnn bwd: null pointer or d_emb_ld < hidden");
+  a.emb_ld = d_emb_ld;
   if (workspace_bytes < gsc_gnn_bwd_workspace_bytes(B, in_dim, H, num_layers))
     return fail(GSC_EWORKSPACE, "gnn bwd: workspace %zu < %zu", workspace_bytes,
                 gsc_gnn_bwd_workspace_bytes(B, in_dim, H, num_layers));

@@ -229,14 +229,18 @@ class _FlatNet(nn.Module):
 
     def views(self, flat: torch.Tensor):
         """Structured views of any buffer with this network's layout (params, grads, Adam state):
-        (gnn_flat, [(W_i, b_i), ...])."""
+        (gnn_flat, [(W_i, b_i, Wp_i, pad_i), ...]).  ``W_i`` is the logical ``[out, in]`` weight,
+        ``Wp_i`` the same rows including the ``pad_i`` leading pad columns (16-byte aligned base,
+        what the TMA-fed tensor-core GEMM wants)."""
         gnn = flat[:self._gnn_floats]
         n_gnn = len(self.embedder.ordered_params())
         lins = []
         rest = self._items[n_gnn:]
         for i in range(0, len(rest), 2):
             (wo, ws, wld, wpad), (bo, bs, _, _) = rest[i], rest[i + 1]
-            lins.append((self._view(flat, wo, ws, wld, wpad), self._view(flat, bo, bs, None, 0)))
+            n_out, n_in = ws
+            wp = flat[wo:wo + n_out * wld].view(n_out, wld)[:, :wpad + n_in]
+            lins.append((wp[:, wpad:], self._view(flat, bo, bs, None, 0), wp, wpad))
         return gnn, lins
 
     def param_views(self, flat: torch.Tensor) -> List[torch.Tensor]:
@@ -270,20 +274,28 @@ def net_forward(net: _FlatNet, flat: torch.Tensor, gb: GraphBatch, action: Optio
     """emb = GNN(gb); z = MLP(cat[emb, mask(, action)]); returns (z [* out_mul] [clamped], ctx).
 
     ``save`` keeps what ``net_backward`` needs; ``save_gnn=False`` skips the embedder activations
-    when only the gradient w.r.t. the action input will be asked for."""
+    when only the gradient w.r.t. the action input will be asked for.  The embedding is written
+    straight into a ``[B, pad + H]`` buffer whose leading ``pad`` columns are zero and line up with
+    the pad columns of the first weight, so every K-segment of the first layer is 16-byte aligned."""
     gnn, lins = net.views(flat)
-    emb, saved = net.embedder.embed(gb, save=save if save_gnn is None else save_gnn, params=gnn)
-    inputs = [emb, gb.mask] + ([action] if action is not None else [])
+    H = net.embedder.hidden_dim
+    pad0 = lins[0][3]
+    embp = torch.zeros(gb.num_graphs, pad0 + H, dtype=torch.float32, device=flat.device)
+    rowptr, col, gptr = gb.csr()
+    _, saved = ops.gnn_embed_fwd(gb.x, rowptr, col, gptr, gb.num_graphs, gb.max_nodes, gnn, H,
+                                 net.embedder.num_layers, net.embedder.num_iter,
+                                 save=save if save_gnn is None else save_gnn, out=embp[:, pad0:])
+    inputs = [embp, gb.mask] + ([action] if action is not None else [])
     hs = []
     h = None
     n = len(lins)
-    for i, (W, b) in enumerate(lins):
+    for i, (W, b, Wp, pad) in enumerate(lins):
         last = i == n - 1
-        h = ops.linear_fwd(inputs if i == 0 else [h], W, b, relu=not last,
+        h = ops.linear_fwd(inputs if i == 0 else [h], Wp if i == 0 else W, b, relu=not last,
                            mul=out_mul if last else None, clamp1=clamp1 and last)
         if not last:
             hs.append(h)
-    ctx = (emb, saved, inputs, hs) if save else None
+    ctx = (embp, saved, inputs, hs) if save else None
     return h, ctx
 
 
@@ -294,26 +306,29 @@ def net_backward(net: _FlatNet, flat: torch.Tensor, gb: GraphBatch, ctx, dz: tor
 
     Writes parameter gradients into ``grad_flat`` (same layout as ``flat``) unless it is None, and
     returns the gradient w.r.t. the action input (times ``action_grad_mul``) when requested."""
-    emb, saved, inputs, hs = ctx
+    embp, saved, inputs, hs = ctx
     gnn, lins = net.views(flat)
     g_gnn, g_lins = net.views(grad_flat) if grad_flat is not None else (None, None)
     H = net.embedder.hidden_dim
     d_action = None
     d = dz
     for i in range(len(lins) - 1, -1, -1):
-        W, _ = lins[i]
+        W, _, Wp, pad = lins[i]
         if grad_flat is not None:
-            ops.linear_wgrad(d, inputs if i == 0 else [hs[i - 1]], g_lins[i][0])
+            ops.linear_wgrad(d, inputs if i == 0 else [hs[i - 1]], g_lins[i][2] if i == 0 else g_lins[i][0])
             ops.colsum(d, out=g_lins[i][1])
         if i > 0:
             d = ops.linear_dgrad(d, W, 0, int(W.shape[1]), gate=hs[i - 1])
         else:
             if want_action_grad:
                 A = int(inputs[2].shape[1])
-                d_action = ops.linear_dgrad(d, W, H + int(inputs[1].shape[1]), A, mul=action_grad_mul)
+                d_action = ops.linear_dgrad(d, Wp, pad + H + int(inputs[1].shape[1]), A, mul=action_grad_mul)
             if grad_flat is not None:
-                d_emb = ops.linear_dgrad(d, W, 0, H)
-                net.embedder.embed_backward(gb, saved, d_emb, d_params=g_gnn, params=gnn)
+                d_embp = ops.linear_dgrad(d, Wp, 0, pad + H)
+                rowptr, col, gptr = gb.csr()
+                ops.gnn_embed_bwd(gb.x, rowptr, col, gptr, gb.num_graphs, gb.max_nodes, gnn, H,
+                                  net.embedder.num_layers, net.embedder.num_iter, saved, d_embp[:, pad:],
+                                  d_params=g_gnn)
     return d_action
 
 

@@ -15,6 +15,31 @@ from ._lib import EPI_BIAS, EPI_CLAMP1, EPI_GATE, EPI_MUL, EPI_RELU, GemmArgs, c
 _workspaces = {}
 launch_count = 0          # kernels enqueued through this module (bench.py reports it)
 
+# Arithmetic of the dense layers: "fp32" = exact FMA kernel (parity mode, default),
+# "tf32" = tcgen05 tensor cores (TF32 operands, fp32 accumulate in TMEM) where the operands are
+# TMA-mappable.  Tolerances of the two modes are stated separately in tests/ and DESIGN.md.
+precision = "fp32"
+EPI_TF32 = 32
+
+
+class use_precision:
+    """Context manager: ``with ops.use_precision("tf32"): ...``"""
+
+    def __init__(self, mode: str):
+        if mode not in ("fp32", "tf32"):
+            raise ValueError(mode)
+        self.mode = mode
+
+    def __enter__(self):
+        global precision
+        self.prev, precision = precision, self.mode
+        return self
+
+    def __exit__(self, *exc):
+        global precision
+        precision = self.prev
+        return False
+
 
 def _stream() -> int:
     return torch.cuda.current_stream().cuda_stream
@@ -70,6 +95,17 @@ class _Timed:
             self.ev[1].record(torch.cuda.current_stream())
             timer.setdefault(self.name, []).append(self.ev)
         return False
+
+
+def _row_major(t: torch.Tensor, what: str) -> torch.Tensor:
+    if t.dim() != 2 or (t.shape[1] > 1 and t.stride(1) != 1) or t.dtype != torch.float32:
+        raise _lib.GscError(f"{what}: need a 2-D fp32 tensor with unit column stride, got "
+                            f"shape={tuple(t.shape)} stride={t.stride()} dtype={t.dtype}")
+    return t
+
+
+def _ld(t: torch.Tensor) -> int:
+    return int(t.stride(0)) if t.shape[0] > 1 else max(int(t.stride(0)), int(t.shape[1]))
 
 
 # ---------------------------------------------------------------------------------------------
@@ -133,12 +169,14 @@ def gnn_param_floats(in_dim: int, hidden: int, num_layers: int) -> int:
 
 
 def gnn_embed_fwd(x, rowptr, col, graph_ptr, num_graphs: int, max_nodes: int, params: torch.Tensor,
-                  hidden: int, num_layers: int, num_iter: int, save: bool = False):
+                  hidden: int, num_layers: int, num_iter: int, save: bool = False,
+                  out: Optional[torch.Tensor] = None):
+    """``out``: optional [num_graphs, hidden] view with unit column stride (any row stride)."""
     _need_cuda(x, params)
     lib = _lib.load()
     x = x.contiguous()
     Nt, in_dim = int(x.shape[0]), int(x.shape[1])
-    emb = torch.empty(num_graphs, hidden, dtype=torch.float32, device=x.device)
+    emb = out if out is not None else torch.empty(num_graphs, hidden, dtype=torch.float32, device=x.device)
     saved = None
     if save:
         saved = torch.empty(int(lib.gsc_gnn_saved_floats(Nt, hidden, num_layers, num_iter)),
@@ -146,7 +184,7 @@ def gnn_embed_fwd(x, rowptr, col, graph_ptr, num_graphs: int, max_nodes: int, pa
     with _Timed("gnn_fwd"):
         check(lib.gsc_gnn_embed_fwd(_ptr(x), Nt, in_dim, _ptr(rowptr), _ptr(col), _ptr(graph_ptr),
                                     num_graphs, max_nodes, _ptr(params), hidden, num_layers, num_iter,
-                                    _ptr(emb), _ptr(saved), _stream()), "gsc_gnn_embed_fwd")
+                                    _ptr(emb), _ld(emb), _ptr(saved), _stream()), "gsc_gnn_embed_fwd")
     _count(1)
     return emb, saved
 
@@ -156,7 +194,8 @@ def gnn_embed_bwd(x, rowptr, col, graph_ptr, num_graphs: int, max_nodes: int, pa
     _need_cuda(x, params, saved, d_emb)
     lib = _lib.load()
     x = x.contiguous()
-    d_emb = d_emb.contiguous()
+    if d_emb.dim() != 2 or (d_emb.shape[1] > 1 and d_emb.stride(1) != 1):
+        d_emb = d_emb.contiguous()
     Nt, in_dim = int(x.shape[0]), int(x.shape[1])
     if d_params is None:
         d_params = torch.empty_like(params)
@@ -165,24 +204,13 @@ def gnn_embed_bwd(x, rowptr, col, graph_ptr, num_graphs: int, max_nodes: int, pa
     with _Timed("gnn_bwd"):
         check(lib.gsc_gnn_embed_bwd(_ptr(x), Nt, in_dim, _ptr(rowptr), _ptr(col), _ptr(graph_ptr),
                                     num_graphs, max_nodes, _ptr(params), hidden, num_layers, num_iter,
-                                    _ptr(saved), _ptr(d_emb), _ptr(d_params), _ptr(ws), wsn, _stream()),
+                                    _ptr(saved), _ptr(d_emb), _ld(d_emb), _ptr(d_params), _ptr(ws), wsn, _stream()),
               "gsc_gnn_embed_bwd")
     _count(2)
     return d_params
 
 
 # ---------------------------------------------------------------------------------------------
-def _row_major(t: torch.Tensor, what: str) -> torch.Tensor:
-    if t.dim() != 2 or (t.shape[1] > 1 and t.stride(1) != 1) or t.dtype != torch.float32:
-        raise _lib.GscError(f"{what}: need a 2-D fp32 tensor with unit column stride, got "
-                            f"shape={tuple(t.shape)} stride={t.stride()} dtype={t.dtype}")
-    return t
-
-
-def _ld(t: torch.Tensor) -> int:
-    return int(t.stride(0)) if t.shape[0] > 1 else max(int(t.stride(0)), int(t.shape[1]))
-
-
 def gemm_raw(segs: Sequence[tuple], M: int, N: int, out: torch.Tensor, flags: int = 0,
              bias=None, mul=None, gate=None, tag: str = "gemm"):
     """segs: (A_tensor, a_rs, a_cs, B_tensor, b_rs, b_cs, K) with A/B giving the base pointers."""
@@ -194,6 +222,8 @@ def gemm_raw(segs: Sequence[tuple], M: int, N: int, out: torch.Tensor, flags: in
         args.A[s], args.B[s], args.K[s] = A.data_ptr(), B.data_ptr(), K
         args.a_rs[s], args.a_cs[s], args.b_rs[s], args.b_cs[s] = ars, acs, brs, bcs
         ktot += K
+    if precision == "tf32":
+        flags |= EPI_TF32
     args.num_seg, args.flags = len(segs), flags
     args.bias = _ptr(bias)
     if mul is not None:

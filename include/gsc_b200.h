@@ -35,6 +35,9 @@ extern "C" {
 #define GSC_EPI_MUL 4        /* v *= mul[i, j]     (mask product)             */
 #define GSC_EPI_GATE 8       /* v = gate[i, j] > 0 ? v : 0  (ReLU backward)   */
 #define GSC_EPI_CLAMP1 16    /* v = min(max(v, -1), 1)                        */
+#define GSC_EPI_TF32 32      /* allow the tensor-core path: tcgen05 kind::tf32, fp32 accumulate.
+                                Without it the GEMM is exact fp32 (FMA).  Falls back to fp32 when
+                                the operands are not TMA-mappable (16 B bases, strides % 4 floats). */
 
 int gsc_version(void);
 const char* gsc_last_error(void);
@@ -76,7 +79,8 @@ int gsc_pack_csr_noalloc(const int64_t* edge_index, int64_t num_edges, const int
  * params: flat fp32, per conv in state-dict order {att[H], bias[H], lin_l.weight[H,in],
  *         lin_l.bias[H], lin_r.weight[H,in], lin_r.bias[H]}, encoder (in = in_dim) first, then
  *         process[0..num_layers-2] (in = H).
- * emb   : [B, H] output.
+ * emb   : [B, H] output with row stride emb_ld floats (>= H; lets the caller place the embedding
+ *         inside a padded, 16-byte aligned operand of the first dense layer).
  * saved : NULL for inference, else gsc_gnn_saved_floats() floats receiving what backward needs.
  * max_nodes: upper bound on nodes per graph (stats[1] of the packer). */
 int64_t gsc_gnn_param_floats(int in_dim, int hidden, int num_layers);
@@ -84,7 +88,7 @@ int64_t gsc_gnn_saved_floats(int64_t num_nodes, int hidden, int num_layers, int 
 int gsc_gnn_embed_fwd(const float* x, int64_t num_nodes, int in_dim, const int32_t* rowptr,
                       const int32_t* col, const int32_t* graph_ptr, int64_t num_graphs,
                       int max_nodes, const float* params, int hidden, int num_layers, int num_iter,
-                      float* emb, float* saved, void* stream);
+                      float* emb, int64_t emb_ld, float* saved, void* stream);
 
 /* Backward of the above (the reference gets it from torch autograd: loss.backward() at
  * reference src/rlsp/agents/simple_ddpg.py:216,224).  d_params (same layout as params) is
@@ -95,8 +99,8 @@ size_t gsc_gnn_bwd_workspace_bytes(int64_t num_graphs, int in_dim, int hidden, i
 int gsc_gnn_embed_bwd(const float* x, int64_t num_nodes, int in_dim, const int32_t* rowptr,
                       const int32_t* col, const int32_t* graph_ptr, int64_t num_graphs,
                       int max_nodes, const float* params, int hidden, int num_layers, int num_iter,
-                      const float* saved, const float* d_emb, float* d_params, void* workspace,
-                      size_t workspace_bytes, void* stream);
+                      const float* saved, const float* d_emb, int64_t d_emb_ld, float* d_params,
+                      void* workspace, size_t workspace_bytes, void* stream);
 
 /* ---- dense layers (PyG MLP: reference src/rlsp/agents/models.py:80-83,119-122) -------------
  * One strided GEMM, C[M,N] = epilogue( sum_s A_s * B_s ), with up to three K-segments so that
