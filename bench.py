@@ -174,11 +174,18 @@ def run_ours(args):
     def step(d):
         if w["kind"] == "c2":
             return ddpg.predict(actor, fresh(d["cur"]))
+        if graphed is not None:                 # static inputs already hold the batch
+            return graphed.replay()
         cur, nxt = fresh(d["cur"]), fresh(d["nxt"])
         return upd.update(cur, nxt, d["actions"], d["rewards"], d["dones"])
 
+    graphed = None
     resident = h2d_all()
     torch.cuda.synchronize()
+    use_graph = w["kind"] == "c3" and args.graph and world == 1
+    if use_graph:
+        graphed = ddpg.GraphedUpdate(upd, resident["cur"], resident["nxt"], resident["actions"],
+                                     resident["rewards"], resident["dones"])
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)     # > 126 MB L2
     out_host = torch.empty((B, w["cur"].action_dim), dtype=torch.float32).pin_memory() if w["kind"] == "c2" else \
         torch.empty(2, dtype=torch.float32).pin_memory()
@@ -212,12 +219,32 @@ def run_ours(args):
     timer, ops.timer = ops.timer, None
     dev_ms = sum(a.elapsed_time(b) for a, b in evs)
     clocks = sampler.stop() if sampler else None
-    per_op = {k: sum(a.elapsed_time(b) for a, b in v) / args.steps for k, v in timer.items()}
-    per_op_n = {k: len(v) / args.steps for k, v in timer.items()}
+    op_steps = args.steps
+    if graphed is not None:
+        # A graph replay has no host code between kernels, so per-kernel CUDA events are taken on a
+        # kernel-by-kernel pass of the same update right after the timed region (same inputs, L2
+        # flushed); the kernel count is what the capture enqueued.
+        op_steps = min(args.steps, 5)
+        ops.timer = {}
+        launches0 = ops.launch_count
+        g_keep, graphed = graphed, None
+        for _ in range(op_steps):
+            flush.zero_()
+            step(resident)
+        graphed = g_keep
+        barrier()
+        launches = (ops.launch_count - launches0) // op_steps
+        timer, ops.timer = ops.timer, None
+    per_op = {k: sum(a.elapsed_time(b) for a, b in v) / op_steps for k, v in timer.items()}
+    per_op_n = {k: len(v) / op_steps for k, v in timer.items()}
 
     # ---- end-to-end timing through the public API with host buffers (e2e) ----
     def e2e_step():
-        d = h2d_all()
+        if graphed is not None:                 # pinned host -> static device inputs -> graph replay
+            graphed.load(host["cur"], host["nxt"], host["actions"], host["rewards"], host["dones"])
+            d = None
+        else:
+            d = h2d_all()
         r = step(d)
         if w["kind"] == "c2":
             out_host.copy_(r, non_blocking=True)
@@ -271,7 +298,7 @@ def run_ours(args):
             "dtype": "f32" if args.precision == "fp32" else "tf32 tensor-core GEMMs (fp32 accumulate), f32 elsewhere",
             "data": "synthetic",
             "config": {"workload": workload_name(w), "states_per_gpu": B, "n_max": n_max,
-                       "precision": args.precision,
+                       "precision": args.precision, "cuda_graph": bool(graphed is not None),
                        "weights": "reference init (PyG glorot / torch Linear), torch.manual_seed(1234)",
                        "l2": "flushed between timed steps (256 MiB write)",
                        "parallelism": f"dp{world}" if w["kind"] == "c3" else f"replicas{world}"},
@@ -395,6 +422,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default=os.environ.get("GSC_BENCH_WORKLOAD", "c2"), choices=["c2", "c3"])
     ap.add_argument("--batch", type=int, default=0)
+    ap.add_argument("--no-graph", dest="graph", action="store_false",
+                    help="c3: launch the update kernel by kernel instead of replaying its CUDA graph")
     ap.add_argument("--precision", default=os.environ.get("GSC_BENCH_PRECISION", "tf32"), choices=["fp32", "tf32"],
                     help="dense layers: exact fp32 FMA kernel, or tcgen05 tensor cores (TF32 operands, fp32 accumulate)")
     args = ap.parse_args()

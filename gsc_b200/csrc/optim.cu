@@ -46,6 +46,47 @@ __global__ void __launch_bounds__(256) adam_soft_kernel(float* __restrict__ p, c
     adam_one(p[i], g[i], m[i], v[i], tgt ? tgt + i : nullptr, s);
 }
 
+// Device-side step counter variant (CUDA-graph replays cannot re-bake a host scalar): every thread
+// derives the bias corrections from *step_dev + 1; adam_step_inc_kernel bumps the counter afterwards.
+__global__ void __launch_bounds__(256) adam_soft_dev_kernel(float* __restrict__ p, const float* __restrict__ g,
+                                                            float* __restrict__ m, float* __restrict__ v,
+                                                            float* __restrict__ tgt, int64_t n,
+                                                            const int64_t* __restrict__ step_dev, float lr, float beta1,
+                                                            float beta2, float eps, float tau) {
+  const double step = (double)(*step_dev + 1);
+  AdamScalars s;
+  s.lr_over_bc1 = (float)((double)lr / (1.0 - pow((double)beta1, step)));
+  s.sqrt_bc2 = (float)sqrt(1.0 - pow((double)beta2, step));
+  s.beta1 = beta1; s.beta2 = beta2; s.eps = eps; s.tau = tau;
+  const bool vec = ((reinterpret_cast<uintptr_t>(p) | reinterpret_cast<uintptr_t>(g) | reinterpret_cast<uintptr_t>(m) |
+                     reinterpret_cast<uintptr_t>(v) | reinterpret_cast<uintptr_t>(tgt)) & 15) == 0;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int64_t done = 0;
+  if (vec) {
+    const int64_t n4 = n >> 2;
+    float4* p4 = reinterpret_cast<float4*>(p);
+    const float4* g4 = reinterpret_cast<const float4*>(g);
+    float4* m4 = reinterpret_cast<float4*>(m);
+    float4* v4 = reinterpret_cast<float4*>(v);
+    float4* t4 = reinterpret_cast<float4*>(tgt);
+    for (int64_t i = tid; i < n4; i += stride) {
+      float4 pp = p4[i], gg = g4[i], mm = m4[i], vv = v4[i];
+      float4 tt = tgt ? t4[i] : make_float4(0.f, 0.f, 0.f, 0.f);
+      adam_one(pp.x, gg.x, mm.x, vv.x, tgt ? &tt.x : nullptr, s);
+      adam_one(pp.y, gg.y, mm.y, vv.y, tgt ? &tt.y : nullptr, s);
+      adam_one(pp.z, gg.z, mm.z, vv.z, tgt ? &tt.z : nullptr, s);
+      adam_one(pp.w, gg.w, mm.w, vv.w, tgt ? &tt.w : nullptr, s);
+      p4[i] = pp; m4[i] = mm; v4[i] = vv;
+      if (tgt) t4[i] = tt;
+    }
+    done = n4 << 2;
+  }
+  for (int64_t i = done + tid; i < n; i += stride) adam_one(p[i], g[i], m[i], v[i], tgt ? tgt + i : nullptr, s);
+}
+
+__global__ void adam_step_inc_kernel(int64_t* step_dev) { *step_dev += 1; }
+
 // Scalar variant for buffers that are not 16-byte aligned.
 __global__ void __launch_bounds__(256) adam_soft_scalar_kernel(float* __restrict__ p, const float* __restrict__ g,
                                                                float* __restrict__ m, float* __restrict__ v,
@@ -128,6 +169,22 @@ extern "C" int gsc_adam_soft_update(float* p, const float* g, float* m, float* v
   else
     adam_soft_scalar_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(p, g, m, v, target, n, s);
   GSC_LAUNCH_CHECK("adam_soft_kernel");
+  return GSC_OK;
+}
+
+extern "C" int gsc_adam_soft_update_dev(float* p, const float* g, float* m, float* v, float* target, int64_t n,
+                                        float lr, float beta1, float beta2, float eps, int64_t* step_dev, float tau,
+                                        void* stream) {
+  GSC_REQUIRE(p && g && m && v && step_dev && n >= 0, "gsc_adam_soft_update_dev: bad arguments");
+  if (n == 0) return GSC_OK;
+  int64_t blocks = ceil_div(ceil_div(n, 4), 256);
+  const int64_t cap = 8LL * kNumSMs;
+  if (blocks > cap) blocks = cap;
+  adam_soft_dev_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(p, g, m, v, target, n, step_dev, lr, beta1, beta2,
+                                                                      eps, tau);
+  GSC_LAUNCH_CHECK("adam_soft_dev_kernel");
+  adam_step_inc_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(step_dev);
+  GSC_LAUNCH_CHECK("adam_step_inc_kernel");
   return GSC_OK;
 }
 

@@ -43,6 +43,9 @@ class DDPGUpdater:
         self.step_actor = 0
         self.step_critic = 0
         self._neg = None
+        # Adam step counters in device memory: [critic, actor].  Always used, so that an eager update
+        # and a CUDA-graph replay of it are the same launches.
+        self.steps_dev = torch.zeros(2, dtype=torch.int64, device=actor.flat.device)
 
     # -- pieces, named after the reference methods ---------------------------------------------
     def _allreduce(self, flat_grad: torch.Tensor) -> None:
@@ -61,8 +64,8 @@ class DDPGUpdater:
         net_backward(q, q.flat, cur, ctx, dq.view(B, 1), self.g_critic)
         self._allreduce(self.g_critic)
         self.step_critic += 1
-        ops.adam_soft_update(q.flat, self.g_critic, self.m_critic, self.v_critic, tq.flat, self.lr,
-                             self.betas[0], self.betas[1], self.eps, self.step_critic, self.tau)
+        ops.adam_soft_update_dev(q.flat, self.g_critic, self.m_critic, self.v_critic, tq.flat, self.lr,
+                                 self.betas[0], self.betas[1], self.eps, self.steps_dev[0:1], self.tau)
         return qv.view(-1), loss
 
     def update_actor(self, cur: GraphBatch):
@@ -82,8 +85,8 @@ class DDPGUpdater:
         net_backward(ac, ac.flat, cur, ctx_a, dz, self.g_actor)
         self._allreduce(self.g_actor)
         self.step_actor += 1
-        ops.adam_soft_update(ac.flat, self.g_actor, self.m_actor, self.v_actor, ta.flat, self.lr,
-                             self.betas[0], self.betas[1], self.eps, self.step_actor, self.tau)
+        ops.adam_soft_update_dev(ac.flat, self.g_actor, self.m_actor, self.v_actor, ta.flat, self.lr,
+                                 self.betas[0], self.betas[1], self.eps, self.steps_dev[1:2], self.tau)
         actor_loss = ops.colsum(q_pi) * (-scale)
         return actor_loss
 
@@ -95,6 +98,78 @@ class DDPGUpdater:
         qv, q_loss = self.update_critic(nxt, cur, dones, rewards, actions)
         a_loss = self.update_actor(cur)
         return qv, q_loss, a_loss
+
+
+class GraphedUpdate:
+    """``DDPGUpdater.update`` captured once into a CUDA graph and replayed per minibatch.
+
+    The whole gradient step (packer, five forward and three backward passes, both fused optimizer
+    launches, ~60 kernels) becomes one graph launch, which removes the per-launch host overhead that
+    dominates at the reference's batch size of 100.  The batch lives in STATIC device tensors
+    (``self.cur``, ``self.nxt``, ``self.actions``, ``self.rewards``, ``self.dones``): write the next
+    minibatch into them (``load``) and call ``replay``.  Shapes (B, Nt, E) are frozen at capture."""
+
+    def __init__(self, upd: DDPGUpdater, cur: GraphBatch, nxt: GraphBatch, actions, rewards, dones,
+                 warmup: int = 2):
+        self.upd = upd
+        mk = lambda gb, share=None: GraphBatch(
+            gb.x.clone(), gb.edge_index.clone() if share is None else share.edge_index,
+            gb.batch.clone() if share is None else share.batch,
+            gb.mask.clone() if share is None else share.mask, gb.num_graphs, gb.max_nodes)
+        self.cur = mk(cur)
+        self.nxt = mk(nxt, self.cur if nxt.edge_index is cur.edge_index else None)
+        self.actions, self.rewards, self.dones = actions.clone(), rewards.clone(), dones.clone()
+        nets = (upd.actor, upd.qf1, upd.target_actor, upd.qf1_target)
+        state = [t.clone() for t in (*[n.flat for n in nets], upd.m_actor, upd.v_actor, upd.m_critic,
+                                     upd.v_critic, upd.steps_dev)]
+        host_steps = (upd.step_actor, upd.step_critic)
+
+        def restore():
+            for dst, src in zip((*[n.flat for n in nets], upd.m_actor, upd.v_actor, upd.m_critic,
+                                 upd.v_critic, upd.steps_dev), state):
+                dst.copy_(src)
+            upd.step_actor, upd.step_critic = host_steps
+
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(warmup):            # sizes every workspace; its weight updates are rolled back
+                self._run()
+        torch.cuda.current_stream().wait_stream(side)
+        restore()
+        torch.cuda.synchronize()
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self.out = self._run()
+        restore()
+
+    def _run(self):
+        fresh = lambda gb: GraphBatch(gb.x, gb.edge_index, gb.batch, gb.mask, gb.num_graphs, gb.max_nodes)
+        return self.upd.update(fresh(self.cur), fresh(self.nxt), self.actions, self.rewards, self.dones)
+
+    def load(self, cur: GraphBatch, nxt: GraphBatch, actions, rewards, dones, non_blocking: bool = True):
+        """Copy a minibatch (host or device tensors of the captured shapes) into the static inputs."""
+        nb = non_blocking
+        self.cur.x.copy_(cur.x, non_blocking=nb)
+        self.cur.edge_index.copy_(cur.edge_index, non_blocking=nb)
+        self.cur.batch.copy_(cur.batch, non_blocking=nb)
+        self.cur.mask.copy_(cur.mask, non_blocking=nb)
+        self.nxt.x.copy_(nxt.x, non_blocking=nb)
+        if self.nxt.edge_index is not self.cur.edge_index:
+            self.nxt.edge_index.copy_(nxt.edge_index, non_blocking=nb)
+            self.nxt.batch.copy_(nxt.batch, non_blocking=nb)
+            self.nxt.mask.copy_(nxt.mask, non_blocking=nb)
+        self.actions.copy_(actions, non_blocking=nb)
+        self.rewards.copy_(rewards, non_blocking=nb)
+        self.dones.copy_(dones, non_blocking=nb)
+
+    def replay(self):
+        """One gradient step on the static inputs; returns (q_values, q_loss, actor_loss) tensors
+        that the graph overwrites on every replay."""
+        self.graph.replay()
+        self.upd.step_actor += 1
+        self.upd.step_critic += 1
+        return self.out
 
 
 @torch.no_grad()

@@ -336,6 +336,19 @@ def adam_soft_update(p, g, m, v, target, lr, beta1, beta2, eps, step: int, tau: 
     _count(1)
 
 
+def adam_soft_update_dev(p, g, m, v, target, lr, beta1, beta2, eps, step_dev: torch.Tensor, tau: float):
+    """Adam + soft update with the step counter in device memory (int64 scalar tensor, incremented
+    by the call) -- the form that can be replayed from a CUDA graph."""
+    for t in (p, g, m, v, target):
+        if t is not None and not t.is_contiguous():
+            raise _lib.GscError("adam_soft_update_dev needs flat contiguous buffers")
+    with _Timed(f"adam_soft_update[{int(p.numel())}]"):
+        check(_lib.load().gsc_adam_soft_update_dev(_ptr(p), _ptr(g), _ptr(m), _ptr(v), _ptr(target),
+                                                   int(p.numel()), lr, beta1, beta2, eps, _ptr(step_dev), tau,
+                                                   _stream()), "gsc_adam_soft_update_dev")
+    _count(2)
+
+
 def actor_head(y: torch.Tensor, group: int, noise: Optional[torch.Tensor] = None,
                low: float = 0.0, high: float = 1.0) -> torch.Tensor:
     """post_process_actions (and, with ``noise``, the exploration step) -> fp64 [R, A]."""

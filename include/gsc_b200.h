@@ -153,6 +153,13 @@ int gsc_adam_soft_update(float* p, const float* g, float* m, float* v, float* ta
                          float lr, float beta1, float beta2, float eps, int64_t step, float tau,
                          void* stream);
 
+/* Same update with the Adam step count kept in device memory: the kernel uses *step_dev + 1 and
+ * then increments *step_dev.  For callers that replay the update from a CUDA graph, where a host
+ * scalar would be frozen at capture time. */
+int gsc_adam_soft_update_dev(float* p, const float* g, float* m, float* v, float* target, int64_t n,
+                             float lr, float beta1, float beta2, float eps, int64_t* step_dev, float tau,
+                             void* stream);
+
 /* ---- actor head ---------------------------------------------------------------------------
  * post_process_actions + normalize_scheduling_probabilities (reference
  * src/rlsp/agents/simple_ddpg.py:374-395, 338-372), applied to R action vectors of A values each,

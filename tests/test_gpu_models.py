@@ -155,6 +155,39 @@ def test_fused_step_equals_oracle_on_config3_shape():
         assert np.abs(d_got - d_ref).max() < 0.05 * 3e-3 + 1e-7, k
 
 
+def test_cuda_graph_replay_equals_eager_updates():
+    n_max, B = 12, 10
+    cur_s, nxt_s, actions, rewards, dones = synth.make_transitions(B, n_max, 4, 12, seed=5, num_topologies=3)
+    spec = AgentSpec(n_max)
+
+    def build():
+        torch.manual_seed(7)
+        nets = [cls(spec).to(DEV) for cls in (Actor, QNetwork, Actor, QNetwork)]
+        nets[2].load_state_dict(nets[0].state_dict())
+        nets[3].load_state_dict(nets[1].state_dict())
+        return nets, ddpg.DDPGUpdater(*nets, lr=1e-3, gamma=0.99, tau=1e-2)
+
+    t = lambda a: torch.from_numpy(a).to(DEV)
+    cur, nxt = GraphBatch.from_states(cur_s).to(DEV), GraphBatch.from_states(nxt_s).to(DEV)
+    nets_e, upd_e = build()
+    nets_g, upd_g = build()
+    assert torch.equal(nets_e[0].flat, nets_g[0].flat)
+    graphed = ddpg.GraphedUpdate(upd_g, cur, nxt, t(actions), t(rewards), t(dones))
+    assert torch.equal(nets_e[0].flat, nets_g[0].flat), "capture must not change the weights"
+    fresh = lambda gb: GraphBatch(gb.x, gb.edge_index, gb.batch, gb.mask, gb.num_graphs, gb.max_nodes)
+    for step in range(3):
+        x2 = torch.rand_like(cur.x)                              # a new minibatch each step
+        cur_k = GraphBatch(x2, cur.edge_index, cur.batch, cur.mask, cur.num_graphs, cur.max_nodes)
+        qe, le, ae = upd_e.update(cur_k, fresh(nxt), t(actions), t(rewards) + step, t(dones))
+        graphed.load(cur_k, nxt, t(actions), t(rewards) + step, t(dones))
+        qg, lg, ag = graphed.replay()
+        assert rel_err(qg.cpu().numpy(), qe.cpu().numpy()) < 1e-5
+        assert rel_err([float(lg), float(ag)], [float(le), float(ae)]) < 1e-5
+    for ne, ng in zip(nets_e, nets_g):
+        assert rel_err(ng.flat.cpu().numpy(), ne.flat.cpu().numpy()) < 1e-5
+    assert upd_g.steps_dev.tolist() == [3, 3] and upd_e.steps_dev.tolist() == [3, 3]
+
+
 def test_replay_buffer_to_update_pipeline_runs():
     spec = AgentSpec(8)
     rb = GraphReplayBuffer(32, spec.env.action_space, device=DEV)
