@@ -12,7 +12,9 @@
 // and finally one thread per (graph, channel) for the mean-pool.  HBM traffic is the compulsory
 // 4nF + 4(e+n) + 4(n+1) bytes in and 4H bytes out per graph (+ the saved activations when training).
 #include "common.cuh"
+#include "tc_ptx.cuh"
 #include <math.h>
+#include <stdlib.h>
 
 namespace gsc {
 
@@ -220,6 +222,259 @@ __global__ void __launch_bounds__(kGnnThreads, 2) gnn_fwd_kernel(const GnnArgs p
       }
     }
     __syncthreads();
+  }
+}
+
+// ================================ tcgen05 forward ===========================================
+// Same fused forward, with the per-node linear transforms (the bulk of the FLOPs: 2*2*H*d_in per
+// node and application) moved to the 5th-gen tensor cores while staying fp32-faithful:
+//   * node rows are split h = h_hi + h_lo (both exactly representable in TF32) and written by their
+//     owner thread into two shared-memory A operands; the weights [Wl;Wr] are split the same way
+//     once per CTA into two B operands;
+//   * one elected thread issues tcgen05.mma kind::tf32 for A_hi*B_hi + A_hi*B_lo + A_lo*B_hi
+//     (3xTF32, relative error ~2^-21) into a 128-lane x 2H-column TMEM accumulator per 128 nodes;
+//   * TMEM lane i belongs to node i, so tcgen05.ld hands every thread exactly its own xl|xr row --
+//     the thread-per-node layout that the attention/softmax/aggregation phase wants.
+// Operands use the no-swizzle K-major core-matrix layout (8 rows x 16 B), which lets a thread store
+// its row with 128-bit conflict-free st.shared and needs no padding for K = H.
+template <int HP>
+struct TcL {
+  static constexpr int kN = 2 * HP;                       // accumulator columns: xl | xr
+  static constexpr int kChunks = HP / 4;                  // 16-byte chunks per operand row
+  static constexpr int kGroupBytes = kChunks * 128;       // 8 rows x kChunks core matrices
+  static constexpr int kATile = 16 * kGroupBytes;         // 128-row A operand (== 128*HP*4 bytes)
+  static constexpr int kB = (kN / 8) * kGroupBytes;       // kN-row B operand
+  static constexpr int kVecFloats = 4 * HP;               // bl, br, att, bias
+  static constexpr int kConvBytes = 2 * kB + kVecFloats * 4;
+  __device__ __forceinline__ static int off(int r, int c) { return (r >> 3) * kGroupBytes + c * 128 + (r & 7) * 16; }
+};
+
+template <int HP>
+__device__ __forceinline__ void store_split_row(uint8_t* a_hi, uint8_t* a_lo, int row, const float (&h)[HP]) {
+  using T = TcL<HP>;
+#pragma unroll
+  for (int c4 = 0; c4 < HP / 4; ++c4) {
+    float4 hi, lo;
+    hi.x = to_tf32(h[4 * c4]);     lo.x = to_tf32(h[4 * c4] - hi.x);
+    hi.y = to_tf32(h[4 * c4 + 1]); lo.y = to_tf32(h[4 * c4 + 1] - hi.y);
+    hi.z = to_tf32(h[4 * c4 + 2]); lo.z = to_tf32(h[4 * c4 + 2] - hi.z);
+    hi.w = to_tf32(h[4 * c4 + 3]); lo.w = to_tf32(h[4 * c4 + 3] - hi.w);
+    *reinterpret_cast<float4*>(a_hi + T::off(row, c4)) = hi;
+    *reinterpret_cast<float4*>(a_lo + T::off(row, c4)) = lo;
+  }
+}
+
+// HP consecutive accumulator columns of this thread's TMEM lane.
+template <int HP>
+__device__ __forceinline__ void tmem_load_row(uint32_t taddr, float (&v)[HP]) {
+  uint32_t r[HP / 8][8];
+#pragma unroll
+  for (int q = 0; q < HP / 8; ++q) tc_ld8_nowait(taddr + 8 * q, r[q]);
+  tc_ld_wait();
+#pragma unroll
+  for (int q = 0; q < HP / 8; ++q)
+#pragma unroll
+    for (int e = 0; e < 8; ++e) v[8 * q + e] = __uint_as_float(r[q][e]);
+}
+
+template <int HP>
+__global__ void __launch_bounds__(kGnnThreads, 2) gnn_fwd_tc_kernel(const GnnArgs p, const int tmem_cols) {
+  using T = TcL<HP>;
+  extern __shared__ float4 smem4[];
+  uint8_t* sm = reinterpret_cast<uint8_t*>(smem4);
+  const int tiles = p.cap / 128;
+  uint8_t* convs = sm;
+  uint8_t* a_hi = convs + p.num_convs * T::kConvBytes;
+  uint8_t* a_lo = a_hi + tiles * T::kATile;
+  float* xl_s = reinterpret_cast<float*>(a_lo + tiles * T::kATile);
+  uint64_t* bar_ptr = reinterpret_cast<uint64_t*>(xl_s + (size_t)p.cap * HP);
+  uint32_t* tslot = reinterpret_cast<uint32_t*>(bar_ptr + 1);
+  const uint32_t bar = smem_u32(bar_ptr);
+  const int tid = threadIdx.x, warp = tid >> 5;
+
+  // ---- weights -> split B operands + small vectors ----
+  for (int cv = 0; cv < p.num_convs; ++cv) {
+    const int in = cv == 0 ? p.in_dim : p.H, H = p.H;
+    const float* src = p.params + conv_param_offset(cv, p.in_dim, p.H);
+    const float* att = src;
+    const float* bias = src + H;
+    const float* Wl = bias + H;
+    const float* bl = Wl + (int64_t)H * in;
+    const float* Wr = bl + H;
+    const float* br = Wr + (int64_t)H * in;
+    uint8_t* b_hi = convs + cv * T::kConvBytes;
+    uint8_t* b_lo = b_hi + T::kB;
+    float* vec = reinterpret_cast<float*>(b_lo + T::kB);
+    for (int t = tid; t < T::kN * HP; t += kGnnThreads) {
+      const int n = t / HP, k = t - n * HP, c = n % HP;
+      float val = 0.f;
+      if (c < H && k < in) val = (n >= HP ? Wr : Wl)[c * in + k];
+      const float hi = to_tf32(val), lo = to_tf32(val - hi);
+      const int byte = T::off(n, k >> 2) + (k & 3) * 4;
+      *reinterpret_cast<float*>(b_hi + byte) = hi;
+      *reinterpret_cast<float*>(b_lo + byte) = lo;
+    }
+    for (int t = tid; t < HP; t += kGnnThreads) {
+      const bool ok = t < H;
+      vec[t] = ok ? bl[t] : 0.f;
+      vec[HP + t] = ok ? br[t] : 0.f;
+      vec[2 * HP + t] = ok ? att[t] : 0.f;
+      vec[3 * HP + t] = ok ? bias[t] : 0.f;
+    }
+  }
+  if (tid == 0) {
+    mbar_init(bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 0) {
+    __syncwarp();
+    tmem_alloc(smem_u32(tslot), (uint32_t)tmem_cols);
+  }
+  fence_proxy_async_smem();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tslot;
+  const uint32_t lane_base = (uint32_t)((warp & 3) * 32) << 16;     // TMEM lane quadrant of this warp
+  // instruction descriptor: D=f32, A=B=tf32, both K-major, M=128, N=2*HP
+  const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(T::kN >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+  uint32_t parity = 0;
+  // optional phase timers (debug): partials[0..7] += cycles of {setup, x rows, mma, xl store, phase B, pool}
+  long long tprev = clock64();
+  const bool dbg = p.partials != nullptr && blockIdx.x == 0 && tid == 0;
+#define GSC_TICK(slot)                                                                  \
+  do {                                                                                  \
+    if (dbg) { long long tn = clock64(); p.partials[slot] += (float)(tn - tprev); tprev = tn; } \
+  } while (0)
+  GSC_TICK(0);
+
+  const int num_chunks = (p.B + p.G - 1) / p.G;
+  for (int chunk = blockIdx.x; chunk < num_chunks; chunk += gridDim.x) {
+    const int g0 = chunk * p.G, g1 = min(p.B, g0 + p.G);
+    const int nbase = p.graph_ptr[g0];
+    const int nc = p.graph_ptr[g1] - nbase;
+    const int warp_first = tid & ~31;                                // slot loops must be warp-uniform (tcgen05.ld)
+
+    // encoder input rows: x -> split operand rows
+    for (int i = tid; i < nc; i += kGnnThreads) {
+      float h[HP];
+#pragma unroll
+      for (int k = 0; k < HP; ++k) h[k] = (k < p.in_dim) ? p.x[((int64_t)nbase + i) * p.in_dim + k] : 0.f;
+      store_split_row<HP>(a_hi + (i >> 7) * T::kATile, a_lo + (i >> 7) * T::kATile, i & 127, h);
+    }
+    GSC_TICK(1);
+
+    for (int a = 0; a < p.num_apps; ++a) {
+      const int cv = p.app_conv[a];
+      const uint8_t* b_hi = convs + cv * T::kConvBytes;
+      const float* vec = reinterpret_cast<const float*>(b_hi + 2 * T::kB);
+      const int ksteps = ((cv == 0 ? p.in_dim : p.H) + 7) / 8;
+      const bool last = a == p.num_apps - 1;
+
+      // ---- phase A on the tensor cores ----
+      fence_proxy_async_smem();          // operand rows were written with st.shared
+      tc_fence_before();
+      __syncthreads();
+      if (tid == 0) {
+        tc_fence_after();
+        const int used_tiles = (nc + 127) >> 7;
+        for (int t = 0; t < used_tiles; ++t) {
+          const uint32_t ah = smem_u32(a_hi + t * T::kATile), al = smem_u32(a_lo + t * T::kATile);
+          const uint32_t bh = smem_u32(b_hi), blo = bh + T::kB;
+          const uint32_t d = tmem_base + (uint32_t)(t * T::kN);
+          for (int s = 0; s < ksteps; ++s) {
+            const uint32_t ko = s * 256;   // 8 k = two 16-byte chunks = 2 core matrices of 128 B
+            tc_mma_tf32(d, smem_desc(ah + ko, 128, T::kGroupBytes, 0), smem_desc(bh + ko, 128, T::kGroupBytes, 0), idesc, s > 0);
+            tc_mma_tf32(d, smem_desc(ah + ko, 128, T::kGroupBytes, 0), smem_desc(blo + ko, 128, T::kGroupBytes, 0), idesc, 1);
+            tc_mma_tf32(d, smem_desc(al + ko, 128, T::kGroupBytes, 0), smem_desc(bh + ko, 128, T::kGroupBytes, 0), idesc, 1);
+          }
+        }
+        tc_commit(bar);
+      }
+      mbar_wait(bar, parity);
+      parity ^= 1u;
+      tc_fence_after();
+      GSC_TICK(2);
+      // xl rows -> shared memory (neighbours gather them)
+      for (int i0 = warp_first; i0 < nc; i0 += kGnnThreads) {
+        const int i = i0 + (tid & 31);
+        float xl[HP];
+        tmem_load_row<HP>(tmem_base + lane_base + (uint32_t)((i >> 7) * T::kN), xl);
+        if (i < nc) {
+#pragma unroll
+          for (int c = 0; c < HP; ++c) xl[c] += vec[c];
+          store_row<HP>(xl_s + (size_t)i * HP, xl);
+        }
+      }
+      __syncthreads();
+      GSC_TICK(3);
+
+      // ---- phase B: attention scores, online segment softmax, mean aggregation ----
+      for (int i0 = warp_first; i0 < nc; i0 += kGnnThreads) {
+        const int i = i0 + (tid & 31);
+        float xr[HP], att[HP], acc[HP];
+        tmem_load_row<HP>(tmem_base + lane_base + (uint32_t)((i >> 7) * T::kN + HP), xr);
+        if (i < nc) {
+          load_row<HP>(vec + 2 * HP, att);
+#pragma unroll
+          for (int c = 0; c < HP; ++c) { xr[c] += vec[HP + c]; acc[c] = 0.f; }
+          float m = -INFINITY, l = 0.f;
+          const int e0 = p.rowptr[nbase + i], e1 = p.rowptr[nbase + i + 1];
+          for (int e = e0; e < e1; ++e) {
+            const int j = p.col[e] - nbase;
+            float v[HP];
+            load_row<HP>(xl_s + (size_t)j * HP, v);
+            float s = 0.f;
+#pragma unroll
+            for (int c = 0; c < HP; ++c) {
+              float t = v[c] + xr[c];
+              t = fmaxf(t, kNegSlope * t);
+              s = fmaf(att[c], t, s);
+            }
+            const float m_new = fmaxf(m, s);
+            const float sc = expf(m - m_new);
+            const float pe = expf(s - m_new);
+            l = fmaf(l, sc, pe);
+#pragma unroll
+            for (int c = 0; c < HP; ++c) acc[c] = fmaf(acc[c], sc, pe * v[c]);
+            m = m_new;
+          }
+          const float inv = 1.f / ((l + 1e-16f) * (float)(e1 - e0));
+          const bool relu = p.app_relu[a] != 0;
+#pragma unroll
+          for (int c = 0; c < HP; ++c) {
+            const float o = fmaf(acc[c], inv, vec[3 * HP + c]);
+            acc[c] = relu ? fmaxf(o, 0.f) : o;
+          }
+          if (p.saved != nullptr) store_row<HP>(p.saved + ((size_t)a * p.Nt + nbase + i) * HP, acc);
+          if (last) store_row<HP>(reinterpret_cast<float*>(a_lo) + (size_t)i * HP, acc);     // pool input
+          else store_split_row<HP>(a_hi + (i >> 7) * T::kATile, a_lo + (i >> 7) * T::kATile, i & 127, acc);
+        }
+      }
+      GSC_TICK(4);
+    }
+    __syncthreads();
+    // ---- global_mean_pool ----
+    const float* hx = reinterpret_cast<const float*>(a_lo);
+    for (int t = tid; t < (g1 - g0) * HP; t += kGnnThreads) {
+      const int g = g0 + t / HP, c = t % HP;
+      if (c < p.H) {
+        const int n0 = p.graph_ptr[g] - nbase, n1 = p.graph_ptr[g + 1] - nbase;
+        float s = 0.f;
+        for (int i = n0; i < n1; ++i) s += hx[(size_t)i * HP + c];
+        p.emb[(size_t)g * p.emb_ld + c] = (n1 > n0) ? s / (float)(n1 - n0) : 0.f;
+      }
+    }
+    __syncthreads();
+    GSC_TICK(5);
+  }
+#undef GSC_TICK
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, (uint32_t)tmem_cols);
   }
 }
 
@@ -501,6 +756,40 @@ static int launch_fwd(const GnnArgs& a, cudaStream_t st) {
   return GSC_OK;
 }
 
+// tcgen05 forward: usable when the TMEM accumulators (2*HP columns per 128 nodes) and the operand
+// tiles of the largest graph fit; otherwise the FMA kernel above runs.
+template <int HP>
+static int launch_fwd_tc(GnnArgs a, int max_nodes, cudaStream_t st, bool* done) {
+  using T = TcL<HP>;
+  *done = false;
+  const int cap = max_nodes <= kGnnThreads ? kGnnThreads : (max_nodes + 127) / 128 * 128;
+  const int tiles = cap / 128;
+  const size_t smem = (size_t)a.num_convs * T::kConvBytes + 2 * (size_t)tiles * T::kATile + (size_t)cap * HP * 4 + 16;
+  int cols = 32;
+  while (cols < tiles * T::kN) cols *= 2;
+  if (cols > 512 || smem > 200 * 1024) return GSC_OK;
+  a.cap = cap;
+  a.G = cap / max_nodes;
+  if (a.G < 1) a.G = 1;
+  GSC_CUDA_TRY(cudaFuncSetAttribute(gnn_fwd_tc_kernel<HP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const int chunks = (a.B + a.G - 1) / a.G;
+  const int per_sm = (2 * smem <= 220 * 1024 && 2 * cols <= 512) ? 2 : 1;
+  const int grid = chunks < per_sm * kNumSMs ? chunks : per_sm * kNumSMs;
+  gnn_fwd_tc_kernel<HP><<<grid, kGnnThreads, smem, st>>>(a, cols);
+  GSC_LAUNCH_CHECK("gnn_fwd_tc_kernel");
+  *done = true;
+  return GSC_OK;
+}
+
+static bool gnn_use_tc() {
+  static int mode = -1;
+  if (mode < 0) {
+    const char* e = getenv("GSC_GNN_FMA");
+    mode = (e && e[0] == '1') ? 0 : 1;
+  }
+  return mode == 1;
+}
+
 static int bwd_grid(int B, int G) {
   const int chunks = (B + G - 1) / G;
   return chunks < kNumSMs ? chunks : kNumSMs;
@@ -524,6 +813,11 @@ static int launch_bwd(const GnnArgs& a, float* d_params, cudaStream_t st) {
 
 using namespace gsc;
 
+static float* g_gnn_debug = nullptr;
+// Debug hook (not part of the public header): device buffer of >= 8 floats that block 0 of the
+// tcgen05 forward fills with per-phase cycle counts; nullptr disables it.
+extern "C" void gsc_debug_set_gnn_timers(float* dev_buf) { g_gnn_debug = dev_buf; }
+
 extern "C" int64_t gsc_gnn_param_floats(int in_dim, int hidden, int num_layers) {
   return conv_param_offset(num_layers, in_dim, hidden);
 }
@@ -542,7 +836,18 @@ extern "C" int gsc_gnn_embed_fwd(const float* x, int64_t Nt, int in_dim, const i
   if (rc) return rc;
   GSC_REQUIRE(emb && emb_ld >= H, "gnn fwd: null emb or emb_ld < hidden");
   a.emb = emb; a.saved = saved; a.emb_ld = emb_ld;
+  a.partials = g_gnn_debug;
   cudaStream_t st = (cudaStream_t)stream;
+  if (gnn_use_tc()) {
+    bool done = false;
+    switch (pick_hp(H)) {
+      case 8: rc = launch_fwd_tc<8>(a, max_nodes, st, &done); break;
+      case 16: rc = launch_fwd_tc<16>(a, max_nodes, st, &done); break;
+      case 24: rc = launch_fwd_tc<24>(a, max_nodes, st, &done); break;
+      default: rc = launch_fwd_tc<32>(a, max_nodes, st, &done); break;
+    }
+    if (rc || done) return rc;
+  }
   switch (pick_hp(H)) {
     case 8: return launch_fwd<8>(a, st);
     case 16: return launch_fwd<16>(a, st);

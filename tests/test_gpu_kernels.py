@@ -136,7 +136,10 @@ def test_gnn_embed_bwd_matches_autograd_of_oracle(B, n_max, lo, hi, H, F, num_la
     for nme in names:
         for k in ("att", "bias", "lin_l.weight", "lin_l.bias", "lin_r.weight", "lin_r.bias"):
             n = sd[nme + k].numel()
-            assert rel_err(got[off:off + n], want[off:off + n]) < 1e-4, nme + k
+            # relative to max(own magnitude, 1e-3 of the largest gradient): near-zero gradients
+            # (cancellation) hold only fp32 noise and cannot be judged against themselves
+            scale = max(np.abs(want[off:off + n]).max(), 1e-3 * np.abs(want).max())
+            assert np.abs(got[off:off + n] - want[off:off + n]).max() / scale < 1e-4, nme + k
             off += n
     # deterministic: a second run gives identical bits for everything but the atomically
     # accumulated d_xl path; bound that run-to-run jitter instead
