@@ -45,7 +45,7 @@ _PROTOS = {
     "gsc_gnn_bwd_workspace_bytes": (c_size_t, [c_int64, c_int, c_int, c_int]),
     "gsc_gnn_embed_bwd": (c_int, [c_void_p, c_int64, c_int, c_void_p, c_void_p, c_void_p, c_int64,
                                   c_int, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_int64, c_void_p,
-                                  c_void_p, c_size_t, c_void_p]),
+                                  c_void_p, c_void_p, c_size_t, c_void_p]),
     "gsc_gemm_workspace_bytes": (c_size_t, [c_int64, c_int64, c_int64]),
     "gsc_gemm": (c_int, [POINTER(GemmArgs), c_int64, c_int64, c_void_p, c_int64, c_void_p, c_size_t,
                          c_void_p]),

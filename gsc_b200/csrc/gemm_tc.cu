@@ -10,21 +10,28 @@
 //   warp 1      MMA issuer     one elected lane issues 4 x tcgen05.mma (K = 8 each) per 32-wide
 //                              k-block; tcgen05.commit frees the stage / publishes the accumulator
 //   warps 2..5  epilogue       tcgen05.ld (32 lanes x 32 columns per warp), bias/ReLU/mask/gate/
-//                              clamp, 128-byte row segments to global
+//                              clamp.  The mask (or gate) tile is prefetched by TMA into a 64 KB
+//                              swizzled buffer, combined in place with the accumulators and
+//                              written out with TMA stores: both streams are fully coalesced and
+//                              asynchronous (the [B, A] mask-in / action-out traffic is what
+//                              bounds these layers).  A direct-store path covers split-K partials
+//                              and operands that TMA cannot map.
 // Tile 128 x 128, two TMEM accumulator buffers (2 x 128 columns) so the epilogue of tile i overlaps
 // the loads and MMAs of tile i+1.  Roofline: HBM for the mask/action/output streams
 // (4(MK + KN + MN) algorithmic bytes), tensor pipe (TF32) for large-batch shapes.
 #include "common.cuh"
 #include "tc_ptx.cuh"
 #include <mutex>
+#include <stdlib.h>
 
 namespace gsc {
 
 constexpr int kTcBM = 128, kTcBN = 128, kTcBK = 32;          // fp32 elements; BK * 4 B = one 128 B swizzle row
-constexpr int kTcStages = 6;
+constexpr int kTcStages = 4;
 constexpr int kTcThreads = 192;
 constexpr int kTcStageBytes = (kTcBM + kTcBN) * kTcBK * 4;   // 32 KB
-constexpr int kTcSmemBytes = kTcStages * kTcStageBytes + 1024 /*align*/ + 256 /*barriers*/;
+constexpr int kTcEpiBytes = kTcBM * kTcBN * 4;                 // 64 KB: epilogue operand in, output tile out (in place)
+constexpr int kTcSmemBytes = kTcStages * kTcStageBytes + kTcEpiBytes + 1024 /*align*/ + 256 /*barriers*/;
 constexpr int kTmemCols = 2 * kTcBN;                          // 256
 
 struct TcParams {
@@ -37,6 +44,8 @@ struct TcParams {
   int flags, num_seg;
   int kb_end[3];          // exclusive prefix of 32-wide k-blocks per segment
   int kb_total, kb_per_split, splits, tiles_m, tiles_n;
+  int epi_tma;            // 1: output tile leaves through shared memory + TMA store (coalesced, asynchronous)
+  int epi_kind;           // operand streamed in by TMA for the epilogue: 0 none, 1 mul, 2 gate
 };
 
 __device__ __forceinline__ float tc_epilogue(const TcParams& p, float v, int64_t i, int64_t j) {
@@ -69,16 +78,20 @@ __global__ void __launch_bounds__(kTcThreads, 1)
 gemm_tc_kernel(const __grid_constant__ TcParams p, const __grid_constant__ CUtensorMap mapA0,
                const __grid_constant__ CUtensorMap mapA1, const __grid_constant__ CUtensorMap mapA2,
                const __grid_constant__ CUtensorMap mapB0, const __grid_constant__ CUtensorMap mapB1,
-               const __grid_constant__ CUtensorMap mapB2) {
+               const __grid_constant__ CUtensorMap mapB2, const __grid_constant__ CUtensorMap mapC,
+               const __grid_constant__ CUtensorMap mapE) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;       // 1024 B: swizzle-128B atoms
-  const uint32_t bar_base = smem_base + kTcStages * kTcStageBytes;
+  const uint32_t ebuf = smem_base + kTcStages * kTcStageBytes;             // epilogue tile, 4 x [128 rows x 128 B]
+  const uint32_t bar_base = ebuf + kTcEpiBytes;
   // barriers: full[S], empty[S], tmem_full[2], tmem_empty[2], then the TMEM base address slot
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto empty_bar = [&](int s) { return bar_base + 8u * (kTcStages + s); };
   auto tfull_bar = [&](int s) { return bar_base + 8u * (2 * kTcStages + s); };
   auto tempty_bar = [&](int s) { return bar_base + 8u * (2 * kTcStages + 2 + s); };
-  const uint32_t tmem_slot = bar_base + 8u * (2 * kTcStages + 4);
+  const uint32_t efull_bar = bar_base + 8u * (2 * kTcStages + 4);
+  const uint32_t eempty_bar = bar_base + 8u * (2 * kTcStages + 5);
+  const uint32_t tmem_slot = bar_base + 8u * (2 * kTcStages + 6);
   uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -87,6 +100,8 @@ gemm_tc_kernel(const __grid_constant__ TcParams p, const __grid_constant__ CUten
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < kTcStages; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
     for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), 4); }
+    mbar_init(efull_bar, 1);
+    mbar_init(eempty_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 2) {   // one warp allocates TMEM (256 columns) and later frees it
@@ -102,7 +117,7 @@ gemm_tc_kernel(const __grid_constant__ TcParams p, const __grid_constant__ CUten
     // ===================== TMA producer =====================
     if (lane == 0) {
       int stage = 0;
-      uint32_t phase = 0;
+      uint32_t phase = 0, ephase = 0;
       for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
         const WorkItem it = decode_work(p, w);
         for (int kb = it.kb_begin; kb < it.kb_end; ++kb) {
@@ -130,6 +145,13 @@ gemm_tc_kernel(const __grid_constant__ TcParams p, const __grid_constant__ CUten
               tma_load_2d(sb + b * 4096, mB, full_bar(stage), it.n0 + 32 * b, k0);
           }
           if (++stage == kTcStages) { stage = 0; phase ^= 1u; }
+        }
+        if (p.epi_tma && p.epi_kind) {             // prefetch the mask / gate tile of this work item
+          mbar_wait(eempty_bar, ephase ^ 1u);
+          mbar_expect_tx(efull_bar, kTcEpiBytes);
+#pragma unroll
+          for (int c = 0; c < kTcBN / 32; ++c) tma_load_2d(ebuf + c * 16384, &mapE, efull_bar, it.n0 + 32 * c, it.m0);
+          ephase ^= 1u;
         }
       }
     }
@@ -176,6 +198,59 @@ gemm_tc_kernel(const __grid_constant__ TcParams p, const __grid_constant__ CUten
       const int as = iter & 1;
       mbar_wait(tfull_bar(as), ((uint32_t)iter >> 1) & 1u);
       tc_fence_after();
+      if (p.epi_tma) {
+        // ---- TMA epilogue: accumulators (+ prefetched mask/gate tile) -> smem tile in place -> TMA store ----
+        if (p.epi_kind) mbar_wait(efull_bar, (uint32_t)iter & 1u);
+        const int lrow = quad * 32 + lane;
+        const int64_t grow = (int64_t)it.m0 + lrow;
+#pragma unroll 1
+        for (int c = 0; c < kTcBN / 32; ++c) {
+          float v[32];
+          tc_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(as * kTcBN + c * 32), v);
+          const uint32_t rbase = ebuf + c * 16384 + lrow * 128;
+          const int64_t col0 = (int64_t)it.n0 + c * 32;
+#pragma unroll
+          for (int q = 0; q < 8; ++q) {
+            const uint32_t addr = rbase + (uint32_t)((q ^ (lrow & 7)) << 4);          // 128 B swizzle
+            float4 e = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (p.epi_kind) asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(e.x), "=f"(e.y), "=f"(e.z), "=f"(e.w) : "r"(addr));
+            float o[4] = {v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]};
+            const float ev[4] = {e.x, e.y, e.z, e.w};
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              const int64_t col = col0 + 4 * q + u;
+              float t = o[u];
+              if ((p.flags & GSC_EPI_BIAS) && col < p.N) t += p.bias[col];
+              if (p.flags & GSC_EPI_RELU) t = fmaxf(t, 0.f);
+              if (p.epi_kind == 1) t *= ev[u];
+              if (p.flags & GSC_EPI_GATE) {
+                if (p.epi_kind == 2) t = ev[u] > 0.f ? t : 0.f;
+                else if (grow < p.M && col < p.N) t = p.gate[grow * p.ld_gate + col] > 0.f ? t : 0.f;
+              }
+              if (p.flags & GSC_EPI_CLAMP1) t = fminf(fmaxf(t, -1.f), 1.f);
+              o[u] = t;
+            }
+            asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(o[0]), "f"(o[1]), "f"(o[2]), "f"(o[3]) : "memory");
+          }
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(tempty_bar(as));                 // accumulator buffer is free again
+        fence_proxy_async_smem();                                    // st.shared -> visible to the TMA store
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (warp == 2 && lane == 0) {
+#pragma unroll
+          for (int c = 0; c < kTcBN / 32; ++c)
+            if (it.n0 + 32 * c < p.N)
+              asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(
+                               reinterpret_cast<uint64_t>(&mapC)), "r"(ebuf + c * 16384), "r"(it.n0 + 32 * c), "r"(it.m0) : "memory");
+          asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+          asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // smem tile may be overwritten
+          if (p.epi_kind) mbar_arrive(eempty_bar);
+        }
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        continue;
+      }
       const int64_t row = (int64_t)it.m0 + quad * 32 + lane;
 #pragma unroll 1
       for (int c = 0; c < kTcBN / 32; ++c) {
@@ -214,6 +289,7 @@ gemm_tc_kernel(const __grid_constant__ TcParams p, const __grid_constant__ CUten
     }
   }
 
+  if (warp == 2 && lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
   tc_fence_before();
   __syncthreads();
   if (warp == 2) {
@@ -295,7 +371,7 @@ static int tc_round_mode() {
 int gemm_tc_launch(const gsc_gemm_args* a, int64_t M, int64_t N, float* C, int64_t ldc, void* workspace,
                    size_t workspace_bytes, bool a_mn, bool b_mn, cudaStream_t st, int* used_splits) {
   TcParams p{};
-  CUtensorMap maps[6];
+  CUtensorMap maps[8];
   memset(maps, 0, sizeof(maps));
   int kb = 0;
   const int rnd = tc_round_mode();
@@ -327,12 +403,28 @@ int gemm_tc_launch(const gsc_gemm_args* a, int64_t M, int64_t N, float* C, int64
   p.splits = (int)ceil_div(kb, p.kb_per_split);
   p.partial = (float*)workspace;
   *used_splits = p.splits;
+  // TMA epilogue: needs a TMA-mappable output (and mask/gate operand); split-K partials keep direct stores
+  maps[6] = maps[0]; maps[7] = maps[0];
+  p.epi_tma = 0; p.epi_kind = 0;
+  const char* no_tma_epi = getenv("GSC_GEMM_DIRECT_EPILOGUE");
+  if (p.splits == 1 && !(no_tma_epi && no_tma_epi[0] == '1') && aligned16(C) && ldc % 4 == 0) {
+    const float* e = nullptr; int64_t lde = 0; int kind = 0;
+    if (a->flags & GSC_EPI_MUL) { e = a->mul; lde = a->ld_mul; kind = 1; }
+    else if (a->flags & GSC_EPI_GATE) { e = a->gate; lde = a->ld_gate; kind = 2; }
+    const bool e_ok = kind == 0 || (aligned16(e) && lde % 4 == 0);
+    if (e_ok) {
+      int rc = make_map(&maps[6], C, N, M, ldc, 32, kTcBM, 0, false);
+      if (rc) return rc;
+      if (kind) { rc = make_map(&maps[7], e, N, M, lde, 32, kTcBM, 0, false); if (rc) return rc; }
+      p.epi_tma = 1; p.epi_kind = kind;
+    }
+  }
   const int64_t work = tiles * p.splits;
   const int grid = (int)(work < kNumSMs ? work : kNumSMs);
 
   auto launch = [&](auto kernel) -> int {
     GSC_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemBytes));
-    kernel<<<grid, kTcThreads, kTcSmemBytes, st>>>(p, maps[0], maps[1], maps[2], maps[3], maps[4], maps[5]);
+    kernel<<<grid, kTcThreads, kTcSmemBytes, st>>>(p, maps[0], maps[1], maps[2], maps[3], maps[4], maps[5], maps[6], maps[7]);
     GSC_LAUNCH_CHECK("gemm_tc_kernel");
     return GSC_OK;
   };

@@ -31,6 +31,9 @@ struct GnnArgs {
   float* saved;           // fwd: written (nullable); bwd: read
   const float* d_emb;     // bwd only
   float* partials;        // bwd only: [gridDim.x][param_floats]
+  float* dbg;             // optional phase timers (debug hook), nullptr in production
+  const int32_t* stats;   // bwd: packer stats (stats[3] == 0 <=> symmetric graph), nullable
+  int gather_kernel_launched;   // bwd: the out-edge gather kernel handles symmetric graphs
   int64_t Nt;
   int64_t emb_ld;         // row stride of emb (fwd) / d_emb (bwd), floats
   int B, in_dim, H, num_convs, num_apps, G, cap;
@@ -341,10 +344,10 @@ __global__ void __launch_bounds__(kGnnThreads, 2) gnn_fwd_tc_kernel(const GnnArg
   uint32_t parity = 0;
   // optional phase timers (debug): partials[0..7] += cycles of {setup, x rows, mma, xl store, phase B, pool}
   long long tprev = clock64();
-  const bool dbg = p.partials != nullptr && blockIdx.x == 0 && tid == 0;
+  const bool dbg = p.dbg != nullptr && blockIdx.x == 0 && tid == 0;
 #define GSC_TICK(slot)                                                                  \
   do {                                                                                  \
-    if (dbg) { long long tn = clock64(); p.partials[slot] += (float)(tn - tprev); tprev = tn; } \
+    if (dbg) { long long tn = clock64(); p.dbg[slot] += (float)(tn - tprev); tprev = tn; } \
   } while (0)
   GSC_TICK(0);
 
@@ -432,8 +435,8 @@ __global__ void __launch_bounds__(kGnnThreads, 2) gnn_fwd_tc_kernel(const GnnArg
               s = fmaf(att[c], t, s);
             }
             const float m_new = fmaxf(m, s);
-            const float sc = expf(m - m_new);
-            const float pe = expf(s - m_new);
+            const float sc = __expf(m - m_new);
+            const float pe = __expf(s - m_new);
             l = fmaf(l, sc, pe);
 #pragma unroll
             for (int c = 0; c < HP; ++c) acc[c] = fmaf(acc[c], sc, pe * v[c]);
@@ -500,6 +503,8 @@ __global__ void __launch_bounds__(kGnnThreads, 1) gnn_bwd_kernel(const GnnArgs p
   float* dxl_s = xr_s + (size_t)p.cap * HP;                 // [cap][HP] d_xl (atomic target)
   float* dout_s = dxl_s + (size_t)p.cap * HP;               // [cap][HP] d_out of the current app
   float* hin_s = dout_s + (size_t)p.cap * HP;               // [cap][HP] input of the current app
+  // symmetric batches are handled by gnn_bwd_tc_kernel (out-edge gather, no atomics)
+  if (p.gather_kernel_launched && p.stats != nullptr && p.stats[3] == 0) return;
 
   for (int cv = 0; cv < p.num_convs; ++cv)
     load_conv_weights<HP>(wsm + cv * L::kFloats, p.params + conv_param_offset(cv, p.in_dim, p.H),
@@ -703,6 +708,529 @@ __global__ void __launch_bounds__(kGnnThreads, 1) gnn_bwd_kernel(const GnnArgs p
   }
 }
 
+// ================================ tcgen05 backward ==========================================
+// Backward with all three GEMM-shaped pieces on the tensor cores (3xTF32, fp32-faithful):
+//   (R) recompute   [xl|xr]      = h_in  x [Wl;Wr]^T          M=128 nodes, N=2HP,   K=d_in
+//   (H) input grad  d_h_in       = [dxl|dxr] x [Wl;Wr]        M=128 nodes, N=HP',   K=2HP
+// d_h_in stays in TMEM (lane = node) until the next application's edge phase consumes it.  The
+// edge phase (softmax backward, d_att, scatter of d_xl with shared-memory atomics) is one thread
+// per node.  The weight gradient
+//   (W) [dWl|dbl ; dWr|dbr] += [dxl|dxr]^T x [h_in|1]       (reduction over nodes)
+// contracts over the node index, i.e. both operands would be MN-major; for 32-bit operands the
+// tensor core only takes that through the 32-byte-atom swizzled image, a second copy of both
+// operands that does not fit next to the K-major ones.  It therefore runs on the FMA pipe with an
+// 8 x 5 register tile per lane (two 128-bit and ten 32-bit LDS per 40 FMAs), accumulated per CTA in
+// shared memory over all its chunks and applications and written out once per launch.
+template <int HP>
+struct TcB {
+  static constexpr int kN1 = 2 * HP;                               // (R) columns: xl | xr
+  static constexpr int kNH = (HP + 15) / 16 * 16;                  // (H) columns (N % 16 == 0 for M = 128)
+  static constexpr int kWCols = HP + 1;                            // (W) row: HP weight columns + bias column
+  static constexpr int kWFloats = 2 * HP * kWCols;                 // [2HP channels][HP+1]
+  static constexpr int kCG = HP / 4;                               // (W) lane tiling: channel groups of 8 ...
+  static constexpr int kKG = 32 / kCG;                             // ... times column groups
+  static constexpr int kKPer = (kWCols + kKG - 1) / kKG;
+  static constexpr int kHChunks = HP / 4 + 1;                      // h row: HP floats + [1,0,0,0]
+  static constexpr int kHGroup = kHChunks * 128;
+  static constexpr int kHTile = 16 * kHGroup;
+  static constexpr int kDChunks = 2 * HP / 4;                      // dx row: dxl | dxr
+  static constexpr int kDGroup = kDChunks * 128;
+  static constexpr int kDTile = 16 * kDGroup;
+  static constexpr int kB1Group = (HP / 4) * 128;                  // B1: 2HP rows x HP k
+  static constexpr int kB1 = (kN1 / 8) * kB1Group;
+  static constexpr int kB2Group = kDChunks * 128;                  // B2: kNH rows x 2HP k
+  static constexpr int kB2 = (kNH / 8) * kB2Group;
+  static constexpr int kVecFloats = 4 * HP;                        // bl, br, att, pad
+  static constexpr int kSlotFloats = (kGnnThreads / 32) * 2 * HP;  // per-warp private d_att | d_bias sums
+  static constexpr int kConvBytes = 2 * kB1 + 2 * kB2 + (kVecFloats + kSlotFloats) * 4;
+  static constexpr int kMaxConvs = 4;                              // (W) accumulators are per lane, per conv
+  __device__ __forceinline__ static int hoff(int r, int c) { return (r >> 3) * kHGroup + c * 128 + (r & 7) * 16; }
+  __device__ __forceinline__ static int doff(int r, int c) { return (r >> 3) * kDGroup + c * 128 + (r & 7) * 16; }
+};
+
+__device__ __forceinline__ void split4(const float4 v, float4& hi, float4& lo) {
+  hi.x = to_tf32(v.x); lo.x = to_tf32(v.x - hi.x);
+  hi.y = to_tf32(v.y); lo.y = to_tf32(v.y - hi.y);
+  hi.z = to_tf32(v.z); lo.z = to_tf32(v.z - hi.z);
+  hi.w = to_tf32(v.w); lo.w = to_tf32(v.w - hi.w);
+}
+
+template <int HP>
+__global__ void __launch_bounds__(kGnnThreads, 1) gnn_bwd_tc_kernel(const GnnArgs p, const int tmem_cols) {
+  using T = TcB<HP>;
+  extern __shared__ float4 smem4[];
+  uint8_t* sm = reinterpret_cast<uint8_t*>(smem4);
+  const int tiles = p.cap / 128;
+  uint8_t* convs = sm;
+  uint8_t* h_hi = convs + p.num_convs * T::kConvBytes;
+  uint8_t* h_lo = h_hi + tiles * T::kHTile + 1024;
+  uint8_t* d_hi = h_lo + tiles * T::kHTile + 1024;
+  uint8_t* d_lo = d_hi + tiles * T::kDTile + 1024;
+  uint8_t* tail = d_lo + tiles * T::kDTile + 1024;
+  // Needs every edge's reverse in the same CSR: asymmetric batches go to gnn_bwd_kernel instead.
+  if (p.stats == nullptr || p.stats[3] != 0) return;
+  // scratch that lives inside the (idle) dx operand buffers during the edge phase
+  float* xl_s = reinterpret_cast<float*>(d_lo);                               // [cap][HP] xl, later d_xl
+  float* g_s = reinterpret_cast<float*>(d_lo) + (size_t)p.cap * HP;           // [cap][HP] d_out / deg
+  float* xr_s = reinterpret_cast<float*>(d_hi);                               // [cap][HP]
+  float* dxr_raw = reinterpret_cast<float*>(d_hi) + (size_t)p.cap * HP;       // [cap][HP]
+  int* gid_s = reinterpret_cast<int*>(tail);                                  // [cap] graph of every node
+  float4* st_s = reinterpret_cast<float4*>(tail + (size_t)p.cap * 4);         // [cap] softmax max, 1/sum, sum alpha*d_alpha
+  uint64_t* bar_ptr = reinterpret_cast<uint64_t*>(tail + (size_t)p.cap * 20);
+  uint32_t* tslot = reinterpret_cast<uint32_t*>(bar_ptr + 1);
+  const uint32_t bar = smem_u32(bar_ptr);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+
+  // ---- weights: B1 = [Wl;Wr] rows (K = d_in), B2 = [Wl;Wr]^T rows (K = 2HP), split hi/lo ----
+  for (int cv = 0; cv < p.num_convs; ++cv) {
+    const int in = cv == 0 ? p.in_dim : p.H, H = p.H;
+    const float* src = p.params + conv_param_offset(cv, p.in_dim, p.H);
+    const float* att = src;
+    const float* Wl = src + 2 * H;
+    const float* bl = Wl + (int64_t)H * in;
+    const float* Wr = bl + H;
+    const float* br = Wr + (int64_t)H * in;
+    uint8_t* b1_hi = convs + cv * T::kConvBytes;
+    uint8_t* b1_lo = b1_hi + T::kB1;
+    uint8_t* b2_hi = b1_lo + T::kB1;
+    uint8_t* b2_lo = b2_hi + T::kB2;
+    float* vec = reinterpret_cast<float*>(b2_lo + T::kB2);
+    for (int t = tid; t < T::kN1 * HP; t += kGnnThreads) {           // B1[n][k], n = channel (xl | xr)
+      const int n = t / HP, k = t - n * HP, c = n % HP;
+      float val = 0.f;
+      if (c < H && k < in) val = (n >= HP ? Wr : Wl)[c * in + k];
+      const float hi = to_tf32(val), lo = to_tf32(val - hi);
+      const int byte = (n >> 3) * T::kB1Group + (k >> 2) * 128 + (n & 7) * 16 + (k & 3) * 4;
+      *reinterpret_cast<float*>(b1_hi + byte) = hi;
+      *reinterpret_cast<float*>(b1_lo + byte) = lo;
+    }
+    for (int t = tid; t < T::kNH * 2 * HP; t += kGnnThreads) {        // B2[n = k_in][kk = channel]
+      const int n = t / (2 * HP), kk = t - n * 2 * HP, c = kk % HP;
+      float val = 0.f;
+      if (c < H && n < in) val = (kk >= HP ? Wr : Wl)[c * in + n];
+      const float hi = to_tf32(val), lo = to_tf32(val - hi);
+      const int byte = (n >> 3) * T::kB2Group + (kk >> 2) * 128 + (n & 7) * 16 + (kk & 3) * 4;
+      *reinterpret_cast<float*>(b2_hi + byte) = hi;
+      *reinterpret_cast<float*>(b2_lo + byte) = lo;
+    }
+    for (int t = tid; t < HP; t += kGnnThreads) {
+      const bool ok = t < H;
+      vec[t] = ok ? bl[t] : 0.f;
+      vec[HP + t] = ok ? br[t] : 0.f;
+      vec[2 * HP + t] = ok ? att[t] : 0.f;
+      vec[3 * HP + t] = 0.f;
+    }
+    for (int t = tid; t < T::kSlotFloats; t += kGnnThreads) vec[4 * HP + t] = 0.f;   // d_att | d_bias slots
+  }
+  // (W) accumulators: an 8 x kKPer register tile per lane and conv, kept across every chunk and
+  // application of this CTA (local memory between uses) and reduced over the warps once, at the end.
+  float wacc[T::kMaxConvs][8 * T::kKPer];
+#pragma unroll
+  for (int cvv = 0; cvv < T::kMaxConvs; ++cvv)
+#pragma unroll
+    for (int u = 0; u < 8 * T::kKPer; ++u) wacc[cvv][u] = 0.f;
+  if (tid == 0) {
+    mbar_init(bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 0) {
+    __syncwarp();
+    tmem_alloc(smem_u32(tslot), (uint32_t)tmem_cols);
+  }
+  fence_proxy_async_smem();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tslot;
+  const uint32_t lane_base = (uint32_t)((warp & 3) * 32) << 16;
+  const uint32_t col_d1 = 0, col_d2 = (uint32_t)(tiles * T::kN1);
+  // instruction descriptors
+  const uint32_t idesc_base = (1u << 4) | (2u << 7) | (2u << 10);
+  const uint32_t idesc_r = idesc_base | ((uint32_t)(T::kN1 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+  const uint32_t idesc_h = idesc_base | ((uint32_t)(T::kNH >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+  uint32_t parity = 0;
+  long long tprev = clock64();
+  const bool dbg = p.dbg != nullptr && blockIdx.x == 0 && tid == 0;
+#define GSC_TICK(slot)                                                                  \
+  do {                                                                                  \
+    if (dbg) { long long tn = clock64(); p.dbg[slot] += (float)(tn - tprev); tprev = tn; } \
+  } while (0)
+
+  const int num_chunks = (p.B + p.G - 1) / p.G;
+  for (int chunk = blockIdx.x; chunk < num_chunks; chunk += gridDim.x) {
+    const int g0 = chunk * p.G, g1 = min(p.B, g0 + p.G);
+    const int nbase = p.graph_ptr[g0];
+    const int nc = p.graph_ptr[g1] - nbase;
+    const int warp_first = tid & ~31;
+    const int used_tiles = (nc + 127) >> 7;
+    GSC_TICK(0);
+    for (int g = g0 + warp; g < g1; g += kGnnThreads / 32)                  // node -> graph map
+      for (int i = p.graph_ptr[g] - nbase + lane; i < p.graph_ptr[g + 1] - nbase; i += 32) gid_s[i] = g;
+
+    for (int a = p.num_apps - 1; a >= 0; --a) {
+      const int cv = p.app_conv[a];
+      const int d_in = cv == 0 ? p.in_dim : p.H;
+      uint8_t* b1_hi = convs + cv * T::kConvBytes;
+      uint8_t* b2_hi = b1_hi + 2 * T::kB1;
+      float* vec = reinterpret_cast<float*>(b2_hi + 2 * T::kB2);
+      const bool last_app = a == p.num_apps - 1;
+
+      // ---- 1. layer input rows -> split h operand (with the constant-1 chunk) ----
+      for (int i = tid; i < nc; i += kGnnThreads) {
+        const int64_t node = (int64_t)nbase + i;
+        uint8_t* hh = h_hi + (i >> 7) * T::kHTile;
+        uint8_t* hl = h_lo + (i >> 7) * T::kHTile;
+        const int r = i & 127;
+#pragma unroll
+        for (int c4 = 0; c4 < HP / 4; ++c4) {
+          float4 v;
+          if (a == 0) {
+            v.x = (4 * c4 + 0 < p.in_dim) ? p.x[node * p.in_dim + 4 * c4 + 0] : 0.f;
+            v.y = (4 * c4 + 1 < p.in_dim) ? p.x[node * p.in_dim + 4 * c4 + 1] : 0.f;
+            v.z = (4 * c4 + 2 < p.in_dim) ? p.x[node * p.in_dim + 4 * c4 + 2] : 0.f;
+            v.w = (4 * c4 + 3 < p.in_dim) ? p.x[node * p.in_dim + 4 * c4 + 3] : 0.f;
+          } else {
+            v = reinterpret_cast<const float4*>(p.saved + ((size_t)(a - 1) * p.Nt + node) * HP)[c4];
+          }
+          float4 hi, lo;
+          split4(v, hi, lo);
+          *reinterpret_cast<float4*>(hh + T::hoff(r, c4)) = hi;
+          *reinterpret_cast<float4*>(hl + T::hoff(r, c4)) = lo;
+        }
+        *reinterpret_cast<float4*>(hh + T::hoff(r, HP / 4)) = make_float4(1.f, 0.f, 0.f, 0.f);
+        *reinterpret_cast<float4*>(hl + T::hoff(r, HP / 4)) = make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+      GSC_TICK(1);
+      // ---- 2. (R) on the tensor cores ----
+      fence_proxy_async_smem();
+      tc_fence_before();
+      __syncthreads();
+      if (tid == 0) {
+        tc_fence_after();
+        const int ksteps = (d_in + 7) / 8;
+        for (int t = 0; t < used_tiles; ++t) {
+          const uint32_t ah = smem_u32(h_hi + t * T::kHTile), al = smem_u32(h_lo + t * T::kHTile);
+          const uint32_t bh = smem_u32(b1_hi), blo = bh + T::kB1;
+          const uint32_t d = tmem_base + col_d1 + (uint32_t)(t * T::kN1);
+          for (int s = 0; s < ksteps; ++s) {
+            const uint32_t ko = s * 256;
+            tc_mma_tf32(d, smem_desc(ah + ko, 128, T::kHGroup, 0), smem_desc(bh + ko, 128, T::kB1Group, 0), idesc_r, s > 0);
+            tc_mma_tf32(d, smem_desc(ah + ko, 128, T::kHGroup, 0), smem_desc(blo + ko, 128, T::kB1Group, 0), idesc_r, 1);
+            tc_mma_tf32(d, smem_desc(al + ko, 128, T::kHGroup, 0), smem_desc(bh + ko, 128, T::kB1Group, 0), idesc_r, 1);
+          }
+        }
+        tc_commit(bar);
+      }
+      mbar_wait(bar, parity);
+      parity ^= 1u;
+      tc_fence_after();
+      GSC_TICK(2);
+      // ---- 3. xl, xr, g = d_out/deg rows -> smem (own rows) ----
+      {
+      float dbias[HP];
+#pragma unroll
+      for (int c = 0; c < HP; ++c) dbias[c] = 0.f;
+      for (int i0 = warp_first; i0 < nc; i0 += kGnnThreads) {
+        const int i = i0 + lane;
+        float xl[HP], xr[HP], g[HP];
+        const uint32_t t1 = tmem_base + lane_base + col_d1 + (uint32_t)((i >> 7) * T::kN1);
+        tmem_load_row<HP>(t1, xl);
+        tmem_load_row<HP>(t1 + HP, xr);
+        if (!last_app) tmem_load_row<HP>(tmem_base + lane_base + col_d2 + (uint32_t)((i >> 7) * T::kNH), g);
+        if (i < nc) {
+          const int64_t node = (int64_t)nbase + i;
+          if (last_app) {           // pool backward: d_emb[g] / n_g
+            const int gg = gid_s[i];
+            const float inv_n = 1.f / (float)(p.graph_ptr[gg + 1] - p.graph_ptr[gg]);
+#pragma unroll
+            for (int c = 0; c < HP; ++c) g[c] = (c < p.H) ? p.d_emb[(size_t)gg * p.emb_ld + c] * inv_n : 0.f;
+          }
+          if (p.app_relu[a]) {
+            float out[HP];
+            load_row<HP>(p.saved + ((size_t)a * p.Nt + node) * HP, out);
+#pragma unroll
+            for (int c = 0; c < HP; ++c) g[c] = out[c] > 0.f ? g[c] : 0.f;
+          }
+          const float inv_deg = 1.f / (float)(p.rowptr[node + 1] - p.rowptr[node]);
+#pragma unroll
+          for (int c = 0; c < HP; ++c) {
+            xl[c] += vec[c];
+            xr[c] += vec[HP + c];
+            dbias[c] += g[c];
+            g[c] *= inv_deg;
+          }
+          store_row<HP>(xl_s + (size_t)i * HP, xl);
+          store_row<HP>(xr_s + (size_t)i * HP, xr);
+          store_row<HP>(g_s + (size_t)i * HP, g);
+        }
+      }
+#pragma unroll
+      for (int c = 0; c < HP; ++c) {
+        const float sb = warp_sum(dbias[c]);
+        if (lane == (c & 31)) vec[4 * HP + (warp * 2 + 1) * HP + c] += sb;      // warp-private slot
+      }
+      }
+      __syncthreads();
+      GSC_TICK(3);
+
+      // ---- 4T. target side: softmax statistics, d_att, d_xr (gather over in-edges) ----
+      {
+      float datt[HP];
+#pragma unroll
+      for (int c = 0; c < HP; ++c) datt[c] = 0.f;
+      for (int i = tid; i < nc; i += kGnnThreads) {
+        float xr[HP], g[HP], att[HP], dxr[HP];
+        load_row<HP>(xr_s + (size_t)i * HP, xr);
+        load_row<HP>(g_s + (size_t)i * HP, g);
+        load_row<HP>(vec + 2 * HP, att);
+#pragma unroll
+        for (int c = 0; c < HP; ++c) dxr[c] = 0.f;
+        const int e0 = p.rowptr[nbase + i], e1 = p.rowptr[nbase + i + 1];
+        float m = -INFINITY, l = 0.f, dot = 0.f;
+        for (int e = e0; e < e1; ++e) {
+          const int j = p.col[e] - nbase;
+          float v[HP];
+          load_row<HP>(xl_s + (size_t)j * HP, v);
+          float s = 0.f, da = 0.f;
+#pragma unroll
+          for (int c = 0; c < HP; ++c) {
+            float t = v[c] + xr[c];
+            t = fmaxf(t, kNegSlope * t);
+            s = fmaf(att[c], t, s);
+            da = fmaf(g[c], v[c], da);
+          }
+          const float m_new = fmaxf(m, s);
+          const float sc = __expf(m - m_new);
+          const float pe = __expf(s - m_new);
+          l = fmaf(l, sc, pe);
+          dot = fmaf(dot, sc, pe * da);
+          m = m_new;
+        }
+        const float inv_l = 1.f / (l + 1e-16f);
+        dot *= inv_l;
+        st_s[i] = make_float4(m, inv_l, dot, 0.f);
+        for (int e = e0; e < e1; ++e) {
+          const int j = p.col[e] - nbase;
+          float v[HP];
+          load_row<HP>(xl_s + (size_t)j * HP, v);
+          float s = 0.f, da = 0.f;
+#pragma unroll
+          for (int c = 0; c < HP; ++c) {
+            float t = v[c] + xr[c];
+            t = fmaxf(t, kNegSlope * t);
+            s = fmaf(att[c], t, s);
+            da = fmaf(g[c], v[c], da);
+          }
+          const float ds = __expf(s - m) * inv_l * (da - dot);
+#pragma unroll
+          for (int c = 0; c < HP; ++c) {
+            const float u = v[c] + xr[c];
+            datt[c] = fmaf(ds, fmaxf(u, kNegSlope * u), datt[c]);
+            dxr[c] = fmaf(ds * att[c], (u > 0.f ? 1.f : kNegSlope), dxr[c]);
+          }
+        }
+        store_row<HP>(dxr_raw + (size_t)i * HP, dxr);
+      }
+#pragma unroll
+      for (int c = 0; c < HP; ++c) {
+        const float sa = warp_sum(datt[c]);
+        if (lane == (c & 31)) vec[4 * HP + (warp * 2) * HP + c] += sa;          // warp-private slot
+      }
+      }
+      __syncthreads();
+      // ---- 4S. source side: d_xl_j = sum over out-edges j->i of (alpha_ij g_i + d_u_ij); the graph is
+      //      symmetric, so the out-neighbours of j are the entries of its own CSR row ----
+      for (int j = tid; j < nc; j += kGnnThreads) {
+        float v[HP], att[HP], dxl[HP];
+        load_row<HP>(xl_s + (size_t)j * HP, v);
+        load_row<HP>(vec + 2 * HP, att);
+#pragma unroll
+        for (int c = 0; c < HP; ++c) dxl[c] = 0.f;
+        const int e0 = p.rowptr[nbase + j], e1 = p.rowptr[nbase + j + 1];
+        for (int e = e0; e < e1; ++e) {
+          const int i = p.col[e] - nbase;
+          float xr[HP], g[HP];
+          load_row<HP>(xr_s + (size_t)i * HP, xr);
+          load_row<HP>(g_s + (size_t)i * HP, g);
+          const float4 st = st_s[i];
+          float s = 0.f, da = 0.f;
+#pragma unroll
+          for (int c = 0; c < HP; ++c) {
+            float t = v[c] + xr[c];
+            t = fmaxf(t, kNegSlope * t);
+            s = fmaf(att[c], t, s);
+            da = fmaf(g[c], v[c], da);
+          }
+          const float alpha = __expf(s - st.x) * st.y;
+          const float ds = alpha * (da - st.z);
+#pragma unroll
+          for (int c = 0; c < HP; ++c) {
+            const float u = v[c] + xr[c];
+            dxl[c] = fmaf(alpha, g[c], fmaf(ds * att[c], (u > 0.f ? 1.f : kNegSlope), dxl[c]));
+          }
+        }
+        store_row<HP>(xl_s + (size_t)j * HP, dxl);       // own row: xl_j is not needed any more
+      }
+      __syncthreads();
+      GSC_TICK(4);
+      // ---- 5a. (W): weight / bias gradients of lin_l, lin_r (FMA pipe, register-tiled) ----
+      {
+        const int cg = lane % T::kCG, kg = lane / T::kCG;
+        const int c0 = 8 * cg, k0 = T::kKPer * kg;
+        const bool active = kg < T::kKG && k0 < T::kWCols;
+        float acc[8][T::kKPer];
+#pragma unroll
+        for (int u = 0; u < 8; ++u)
+#pragma unroll
+          for (int q = 0; q < T::kKPer; ++q) acc[u][q] = wacc[cv][u * T::kKPer + q];
+        if (active) {
+#pragma unroll 2
+          for (int i = warp; i < nc; i += kGnnThreads / 32) {
+            const float* dsrc = (c0 < HP) ? xl_s + (size_t)i * HP + c0 : dxr_raw + (size_t)i * HP + (c0 - HP);
+            const float4 d0 = reinterpret_cast<const float4*>(dsrc)[0], d1 = reinterpret_cast<const float4*>(dsrc)[1];
+            const float dv[8] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w};
+            const uint8_t* hh = h_hi + (i >> 7) * T::kHTile;
+            const uint8_t* hl = h_lo + (i >> 7) * T::kHTile;
+            float hv[T::kKPer];
+#pragma unroll
+            for (int q = 0; q < T::kKPer; ++q) {
+              const int k = k0 + q;
+              float h = 0.f;
+              if (k < HP) {
+                const int byte = T::hoff(i & 127, k >> 2) + (k & 3) * 4;
+                h = *reinterpret_cast<const float*>(hh + byte) + *reinterpret_cast<const float*>(hl + byte);
+              } else if (k == HP) {
+                h = 1.f;
+              }
+              hv[q] = h;
+            }
+#pragma unroll
+            for (int u = 0; u < 8; ++u)
+#pragma unroll
+              for (int q = 0; q < T::kKPer; ++q) acc[u][q] = fmaf(dv[u], hv[q], acc[u][q]);
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < 8; ++u)
+#pragma unroll
+          for (int q = 0; q < T::kKPer; ++q) wacc[cv][u * T::kKPer + q] = acc[u][q];
+      }
+      GSC_TICK(5);
+      // ---- 5b. [dxl | dxr] rows -> split dx operand (buffers overlap the scratch: read, sync, write) ----
+      {
+        float dl0[HP], dr0[HP], dl1[HP], dr1[HP];      // up to 2 node slots per thread (cap <= 512)
+        const int i_a = tid, i_b = tid + kGnnThreads;
+        if (i_a < nc) { load_row<HP>(xl_s + (size_t)i_a * HP, dl0); load_row<HP>(dxr_raw + (size_t)i_a * HP, dr0); }
+        if (i_b < nc) { load_row<HP>(xl_s + (size_t)i_b * HP, dl1); load_row<HP>(dxr_raw + (size_t)i_b * HP, dr1); }
+        __syncthreads();
+        auto put = [&](int i, const float (&dl)[HP], const float (&dr)[HP]) {
+          uint8_t* dh = d_hi + (i >> 7) * T::kDTile;
+          uint8_t* dlo = d_lo + (i >> 7) * T::kDTile;
+          const int r = i & 127;
+#pragma unroll
+          for (int c4 = 0; c4 < HP / 4; ++c4) {
+            float4 vl = make_float4(0.f, 0.f, 0.f, 0.f), vr = vl, hi, lo;
+            if (i < nc) {
+              vl = make_float4(dl[4 * c4], dl[4 * c4 + 1], dl[4 * c4 + 2], dl[4 * c4 + 3]);
+              vr = make_float4(dr[4 * c4], dr[4 * c4 + 1], dr[4 * c4 + 2], dr[4 * c4 + 3]);
+            }
+            split4(vl, hi, lo);
+            *reinterpret_cast<float4*>(dh + T::doff(r, c4)) = hi;
+            *reinterpret_cast<float4*>(dlo + T::doff(r, c4)) = lo;
+            split4(vr, hi, lo);
+            *reinterpret_cast<float4*>(dh + T::doff(r, HP / 4 + c4)) = hi;
+            *reinterpret_cast<float4*>(dlo + T::doff(r, HP / 4 + c4)) = lo;
+          }
+        };
+        if (i_a < used_tiles * 128) put(i_a, dl0, dr0);
+        if (i_b < used_tiles * 128) put(i_b, dl1, dr1);
+      }
+      GSC_TICK(6);
+      // ---- 6. (H) on the tensor cores ----
+      fence_proxy_async_smem();
+      tc_fence_before();
+      __syncthreads();
+      if (tid == 0) {
+        tc_fence_after();
+        for (int t = 0; t < used_tiles; ++t) {
+          const uint32_t xh = smem_u32(d_hi + t * T::kDTile), xlo = smem_u32(d_lo + t * T::kDTile);
+          if (a > 0) {
+            const uint32_t bh = smem_u32(b2_hi), blo = bh + T::kB2;
+            const uint32_t d = tmem_base + col_d2 + (uint32_t)(t * T::kNH);
+            for (int s = 0; s < 2 * HP / 8; ++s) {
+              const uint32_t ko = s * 256;
+              tc_mma_tf32(d, smem_desc(xh + ko, 128, T::kDGroup, 0), smem_desc(bh + ko, 128, T::kB2Group, 0), idesc_h, s > 0);
+              tc_mma_tf32(d, smem_desc(xh + ko, 128, T::kDGroup, 0), smem_desc(blo + ko, 128, T::kB2Group, 0), idesc_h, 1);
+              tc_mma_tf32(d, smem_desc(xlo + ko, 128, T::kDGroup, 0), smem_desc(bh + ko, 128, T::kB2Group, 0), idesc_h, 1);
+            }
+          }
+        }
+        tc_commit(bar);
+      }
+      mbar_wait(bar, parity);
+      parity ^= 1u;
+      tc_fence_after();
+      GSC_TICK(7);
+    }
+  }
+#undef GSC_TICK
+
+  // ---- CTA partial gradients -> workspace, in the flat state-dict layout of `params` ----
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const int64_t P = conv_param_offset(p.num_convs, p.in_dim, p.H);
+  float* out = p.partials + (size_t)blockIdx.x * P;
+  float* slab = reinterpret_cast<float*>(h_hi);       // [warps][2HP][kWCols]: operand buffers are idle now
+  for (int cv = 0; cv < p.num_convs; ++cv) {
+    const int in = (cv == 0) ? p.in_dim : p.H, H = p.H;
+    float* o = out + conv_param_offset(cv, p.in_dim, p.H);
+    const float* vec = reinterpret_cast<const float*>(convs + cv * T::kConvBytes + 2 * T::kB1 + 2 * T::kB2);
+    __syncthreads();
+    {
+      const int cg = lane % T::kCG, kg = lane / T::kCG;
+      const int c0 = 8 * cg, k0 = T::kKPer * kg;
+      if (kg < T::kKG && k0 < T::kWCols) {
+#pragma unroll
+        for (int u = 0; u < 8; ++u)
+#pragma unroll
+          for (int q = 0; q < T::kKPer; ++q)
+            if (k0 + q < T::kWCols) slab[(size_t)warp * T::kWFloats + (c0 + u) * T::kWCols + k0 + q] = wacc[cv][u * T::kKPer + q];
+      }
+    }
+    __syncthreads();
+    for (int t = tid; t < H; t += kGnnThreads) {
+      float sa = 0.f, sb = 0.f;
+      for (int w = 0; w < kGnnThreads / 32; ++w) {
+        sa += vec[4 * HP + (w * 2) * HP + t];
+        sb += vec[4 * HP + (w * 2 + 1) * HP + t];
+      }
+      o[t] = sa;
+      o[H + t] = sb;
+    }
+    auto gsum = [&](int idx) {
+      float sum = 0.f;
+      for (int w = 0; w < kGnnThreads / 32; ++w) sum += slab[(size_t)w * T::kWFloats + idx];
+      return sum;
+    };
+    for (int t = tid; t < 2 * H * in; t += kGnnThreads) {       // lin_l.weight then lin_r.weight
+      const int is_r = t >= H * in, tt = t - is_r * H * in;
+      const int c = tt / in, k = tt - c * in;
+      o[2 * H + (is_r ? (int64_t)H * in + H : 0) + tt] = gsum((is_r * HP + c) * T::kWCols + k);
+    }
+    for (int t = tid; t < 2 * H; t += kGnnThreads) {            // lin_l.bias then lin_r.bias
+      const int is_r = t >= H, c = t - is_r * H;
+      o[2 * H + (int64_t)H * in + (is_r ? (int64_t)H * in + H : 0) + c] = gsum((is_r * HP + c) * T::kWCols + HP);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, (uint32_t)tmem_cols);
+  }
+}
+
 __global__ void gnn_bwd_reduce_kernel(const float* __restrict__ partials, int num_partials, int64_t P,
                                       float* __restrict__ d_params) {
   for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < P;
@@ -795,13 +1323,45 @@ static int bwd_grid(int B, int G) {
   return chunks < kNumSMs ? chunks : kNumSMs;
 }
 
+// Launch plan of the tcgen05 / gather backward (symmetric batches): feasible when the two-slot
+// node mapping, the operand images and the TMEM accumulators fit.
 template <int HP>
-static int launch_bwd(const GnnArgs& a, float* d_params, cudaStream_t st) {
-  const size_t smem = (2 * (size_t)a.num_convs * ConvLayout<HP>::kFloats + 5 * (size_t)a.cap * HP) * 4;
-  GSC_REQUIRE(smem <= 227 * 1024, "gnn bwd: max_nodes=%d needs %zu B of shared memory (> 227 KB)", a.cap, smem);
-  GSC_CUDA_TRY(cudaFuncSetAttribute(gnn_bwd_kernel<HP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  const int grid = bwd_grid(a.B, a.G);
-  gnn_bwd_kernel<HP><<<grid, kGnnThreads, smem, st>>>(a);
+static bool plan_bwd_tc(const GnnArgs& a, int max_nodes, int* cap, int* cols, size_t* smem) {
+  using T = TcB<HP>;
+  *cap = max_nodes <= kGnnThreads ? kGnnThreads : (max_nodes + 127) / 128 * 128;
+  const int tiles = *cap / 128;
+  if (*cap > 384) return false;     // two node slots per thread; the atomic kernel must fit as well
+  *smem = (size_t)a.num_convs * T::kConvBytes + 2 * ((size_t)tiles * T::kHTile + 1024) +
+          2 * ((size_t)tiles * T::kDTile + 1024) + (size_t)*cap * 20 + 16;
+  const int need_cols = tiles * (T::kN1 + T::kNH);
+  *cols = 32;
+  while (*cols < need_cols) *cols *= 2;
+  return *cols <= 512 && *smem <= 227 * 1024 && a.num_convs <= T::kMaxConvs;
+}
+
+template <int HP>
+static int launch_bwd_both(GnnArgs a, int max_nodes, float* d_params, cudaStream_t st) {
+  // atomic (any graph) kernel geometry
+  const size_t smem_f = (2 * (size_t)a.num_convs * ConvLayout<HP>::kFloats + 5 * (size_t)a.cap * HP) * 4;
+  GSC_REQUIRE(smem_f <= 227 * 1024, "gnn bwd: max_nodes=%d needs %zu B of shared memory (> 227 KB)", a.cap, smem_f);
+  const int grid_f = bwd_grid(a.B, a.G);
+  int cap_t = 0, cols = 0;
+  size_t smem_t = 0;
+  const bool tc = gnn_use_tc() && a.stats != nullptr && plan_bwd_tc<HP>(a, max_nodes, &cap_t, &cols, &smem_t);
+  int grid = grid_f;
+  if (tc) {
+    GnnArgs t = a;
+    t.cap = cap_t;
+    t.G = cap_t / max_nodes < 1 ? 1 : cap_t / max_nodes;
+    const int grid_t = bwd_grid(t.B, t.G);
+    grid = grid_t > grid_f ? grid_t : grid_f;      // one partial per CTA of either kernel
+    GSC_CUDA_TRY(cudaFuncSetAttribute(gnn_bwd_tc_kernel<HP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_t));
+    gnn_bwd_tc_kernel<HP><<<grid, kGnnThreads, smem_t, st>>>(t, cols);   // returns at once unless symmetric
+    GSC_LAUNCH_CHECK("gnn_bwd_tc_kernel");
+    a.gather_kernel_launched = 1;
+  }
+  GSC_CUDA_TRY(cudaFuncSetAttribute(gnn_bwd_kernel<HP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_f));
+  gnn_bwd_kernel<HP><<<grid, kGnnThreads, smem_f, st>>>(a);              // returns at once if the other one ran
   GSC_LAUNCH_CHECK("gnn_bwd_kernel");
   const int64_t P = conv_param_offset(a.num_convs, a.in_dim, a.H);
   gnn_bwd_reduce_kernel<<<(int)ceil_div(P, 256), 256, 0, st>>>(a.partials, grid, P, d_params);
@@ -836,7 +1396,7 @@ extern "C" int gsc_gnn_embed_fwd(const float* x, int64_t Nt, int in_dim, const i
   if (rc) return rc;
   GSC_REQUIRE(emb && emb_ld >= H, "gnn fwd: null emb or emb_ld < hidden");
   a.emb = emb; a.saved = saved; a.emb_ld = emb_ld;
-  a.partials = g_gnn_debug;
+  a.dbg = g_gnn_debug;
   cudaStream_t st = (cudaStream_t)stream;
   if (gnn_use_tc()) {
     bool done = false;
@@ -865,7 +1425,8 @@ extern "C" int gsc_gnn_embed_bwd(const float* x, int64_t Nt, int in_dim, const i
                                  const int32_t* col, const int32_t* graph_ptr, int64_t B, int max_nodes,
                                  const float* params, int H, int num_layers, int num_iter,
                                  const float* saved, const float* d_emb, int64_t d_emb_ld, float* d_params,
-                                 void* workspace, size_t workspace_bytes, void* stream) {
+                                 const int32_t* pack_stats, void* workspace, size_t workspace_bytes,
+                                 void* stream) {
   GnnArgs a{};
   int rc = build_args(a, x, Nt, in_dim, rowptr, col, graph_ptr, B, max_nodes, params, H, num_layers, num_iter);
   if (rc) return rc;
@@ -875,11 +1436,13 @@ extern "C" int gsc_gnn_embed_bwd(const float* x, int64_t Nt, int in_dim, const i
     return fail(GSC_EWORKSPACE, "gnn bwd: workspace %zu < %zu", workspace_bytes,
                 gsc_gnn_bwd_workspace_bytes(B, in_dim, H, num_layers));
   a.saved = const_cast<float*>(saved); a.d_emb = d_emb; a.partials = (float*)workspace;
+  a.dbg = g_gnn_debug;
+  a.stats = pack_stats;
   cudaStream_t st = (cudaStream_t)stream;
   switch (pick_hp(H)) {
-    case 8: return launch_bwd<8>(a, d_params, st);
-    case 16: return launch_bwd<16>(a, d_params, st);
-    case 24: return launch_bwd<24>(a, d_params, st);
-    default: return launch_bwd<32>(a, d_params, st);
+    case 8: return launch_bwd_both<8>(a, max_nodes, d_params, st);
+    case 16: return launch_bwd_both<16>(a, max_nodes, d_params, st);
+    case 24: return launch_bwd_both<24>(a, max_nodes, d_params, st);
+    default: return launch_bwd_both<32>(a, max_nodes, d_params, st);
   }
 }

@@ -136,6 +136,30 @@ __global__ void pack_rows_kernel(const int32_t* __restrict__ rowptr, int32_t* __
   }
 }
 
+// stats[3] := 1 unless the packed graph is symmetric (every edge s->d has as many reverse edges
+// d->s).  Rows are sorted, so the reverse edge is found by binary search.  The embedder backward
+// uses the flag to read a node's out-edges from the same CSR instead of scattering with atomics.
+__global__ void pack_symmetry_kernel(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col,
+                                     int64_t Nt, int32_t* __restrict__ stats) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < Nt;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int lo = rowptr[i], hi = rowptr[i + 1] - 1;            // neighbours, self-loop excluded
+    int a = lo;
+    while (a < hi) {
+      const int32_t s = col[a];
+      int b = a + 1;
+      while (b < hi && col[b] == s) ++b;                          // multiplicity of s in row i
+      const int slo = rowptr[s], shi = rowptr[s + 1] - 1;
+      int l = slo, r = shi;                                       // lower bound of i in row s
+      while (l < r) { const int m = (l + r) >> 1; if (col[m] < (int32_t)i) l = m + 1; else r = m; }
+      int cnt = 0;
+      while (l + cnt < shi && col[l + cnt] == (int32_t)i) ++cnt;
+      if (cnt != b - a) { atomicOr(stats + 3, 1); return; }
+      a = b;
+    }
+  }
+}
+
 __global__ void pack_graph_ptr_kernel(const int64_t* __restrict__ batch, int64_t Nt, int64_t B,
                                       int32_t* __restrict__ graph_ptr, int32_t* __restrict__ stats) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -221,6 +245,10 @@ extern "C" int gsc_pack_csr(const int64_t* edge_index, int64_t E, const int64_t*
   if (Nt > 0) {
     pack_rows_kernel<<<flat_grid(Nt, 128), 128, 0, st>>>(rowptr, col, Nt);
     GSC_LAUNCH_CHECK("pack_rows_kernel");
+  }
+  if (Nt > 0) {
+    pack_symmetry_kernel<<<flat_grid(Nt, 128), 128, 0, st>>>(rowptr, col, Nt, stats);
+    GSC_LAUNCH_CHECK("pack_symmetry_kernel");
   }
   int64_t gp_n = (batch == nullptr) ? 1 : (Nt > 0 ? Nt : B + 1);
   pack_graph_ptr_kernel<<<flat_grid(gp_n, 256), 256, 0, st>>>(batch, Nt, B, graph_ptr, stats);

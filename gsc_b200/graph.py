@@ -160,6 +160,11 @@ class GraphBatch:
             self._csr = (rowptr, col, graph_ptr, stats)
         return self._csr[:3]
 
+    def pack_stats(self):
+        """The packer's device-side stats array [Et, max_nodes, error flags, asymmetry flag]."""
+        self.csr()
+        return self._csr[3]
+
     def share_topology_from(self, other: "GraphBatch") -> None:
         """Reuse another batch's packed CSR (a transition's next state has the same network)."""
         if other._csr is not None and other.edge_index is self.edge_index:

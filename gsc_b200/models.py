@@ -134,7 +134,8 @@ class GNNEmbedder(nn.Module):
         rowptr, col, gptr = gb.csr()
         return ops.gnn_embed_bwd(gb.x, rowptr, col, gptr, gb.num_graphs, gb.max_nodes,
                                  self.flat_params() if params is None else params, self.hidden_dim,
-                                 self.num_layers, self.num_iter, saved, d_emb, d_params)
+                                 self.num_layers, self.num_iter, saved, d_emb, d_params,
+                                 pack_stats=gb.pack_stats())
 
     def forward(self, x, adj_t, batch):
         class _Obs:
@@ -328,7 +329,7 @@ def net_backward(net: _FlatNet, flat: torch.Tensor, gb: GraphBatch, ctx, dz: tor
                 rowptr, col, gptr = gb.csr()
                 ops.gnn_embed_bwd(gb.x, rowptr, col, gptr, gb.num_graphs, gb.max_nodes, gnn, H,
                                   net.embedder.num_layers, net.embedder.num_iter, saved, d_embp[:, pad:],
-                                  d_params=g_gnn)
+                                  d_params=g_gnn, pack_stats=gb.pack_stats())
     return d_action
 
 

@@ -129,7 +129,7 @@ def pack_csr(edge_index: torch.Tensor, batch: Optional[torch.Tensor], num_nodes:
         check(lib.gsc_pack_csr(_ptr(edge_index), E, _ptr(batch), num_nodes, num_graphs, _ptr(rowptr),
                                _ptr(col), _ptr(graph_ptr), _ptr(stats), _ptr(ws), wsn, _stream()),
               "gsc_pack_csr")
-    _count(9 if E > 0 else 7)
+    _count(10 if E > 0 else 8)
     return rowptr, col, graph_ptr, stats
 
 
@@ -190,7 +190,8 @@ def gnn_embed_fwd(x, rowptr, col, graph_ptr, num_graphs: int, max_nodes: int, pa
 
 
 def gnn_embed_bwd(x, rowptr, col, graph_ptr, num_graphs: int, max_nodes: int, params, hidden: int,
-                  num_layers: int, num_iter: int, saved, d_emb, d_params: Optional[torch.Tensor] = None):
+                  num_layers: int, num_iter: int, saved, d_emb, d_params: Optional[torch.Tensor] = None,
+                  pack_stats: Optional[torch.Tensor] = None):
     _need_cuda(x, params, saved, d_emb)
     lib = _lib.load()
     x = x.contiguous()
@@ -204,7 +205,8 @@ def gnn_embed_bwd(x, rowptr, col, graph_ptr, num_graphs: int, max_nodes: int, pa
     with _Timed("gnn_bwd"):
         check(lib.gsc_gnn_embed_bwd(_ptr(x), Nt, in_dim, _ptr(rowptr), _ptr(col), _ptr(graph_ptr),
                                     num_graphs, max_nodes, _ptr(params), hidden, num_layers, num_iter,
-                                    _ptr(saved), _ptr(d_emb), _ld(d_emb), _ptr(d_params), _ptr(ws), wsn, _stream()),
+                                    _ptr(saved), _ptr(d_emb), _ld(d_emb), _ptr(d_params), _ptr(pack_stats),
+                                    _ptr(ws), wsn, _stream()),
               "gsc_gnn_embed_bwd")
     _count(2)
     return d_params

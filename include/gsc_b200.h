@@ -50,8 +50,9 @@ const char* gsc_last_error(void);
  *      graph), batch[Nt] int64 sorted graph id of every node (NULL => one graph).
  * Out: CSR by target with exactly one self-loop per node, stored last in its row:
  *      rowptr[Nt+1], col[<= E+Nt] (sources, ascending within a row), graph_ptr[B+1],
- *      stats[4] = {Et (edges incl. self-loops), max nodes per graph, error flag, 0}.
- * stats[2] != 0 means an edge endpoint or graph id was out of range. */
+ *      stats[4] = {Et (edges incl. self-loops), max nodes per graph, error flag, asymmetry flag}.
+ * stats[2] != 0 means an edge endpoint or graph id was out of range; stats[3] == 0 means every
+ * edge has its reverse (undirected topology, what from_networkx emits for the reference's graphs). */
 size_t gsc_pack_csr_workspace_bytes(int64_t num_nodes, int64_t num_edges);
 int gsc_pack_csr(const int64_t* edge_index, int64_t num_edges, const int64_t* batch,
                  int64_t num_nodes, int64_t num_graphs, int32_t* rowptr, int32_t* col,
@@ -93,14 +94,16 @@ int gsc_gnn_embed_fwd(const float* x, int64_t num_nodes, int in_dim, const int32
 /* Backward of the above (the reference gets it from torch autograd: loss.backward() at
  * reference src/rlsp/agents/simple_ddpg.py:216,224).  d_params (same layout as params) is
  * OVERWRITTEN with the gradient; process-conv weights applied several times receive the sum.
- * The per-CTA partial sums live in the workspace and are reduced in a fixed order, so the result
- * is deterministic. */
+ * The per-CTA partial sums live in the workspace and are reduced in a fixed order.
+ * pack_stats: the packer's stats array (device) or NULL.  When stats[3] says the graph is symmetric
+ * the kernel gathers along out-edges (no atomics, bit-reproducible); otherwise, or with NULL, it
+ * scatters with shared-memory atomics. */
 size_t gsc_gnn_bwd_workspace_bytes(int64_t num_graphs, int in_dim, int hidden, int num_layers);
 int gsc_gnn_embed_bwd(const float* x, int64_t num_nodes, int in_dim, const int32_t* rowptr,
                       const int32_t* col, const int32_t* graph_ptr, int64_t num_graphs,
                       int max_nodes, const float* params, int hidden, int num_layers, int num_iter,
                       const float* saved, const float* d_emb, int64_t d_emb_ld, float* d_params,
-                      void* workspace, size_t workspace_bytes, void* stream);
+                      const int32_t* pack_stats, void* workspace, size_t workspace_bytes, void* stream);
 
 /* ---- dense layers (PyG MLP: reference src/rlsp/agents/models.py:80-83,119-122) -------------
  * One strided GEMM, C[M,N] = epilogue( sum_s A_s * B_s ), with up to three K-segments so that

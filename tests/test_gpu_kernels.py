@@ -126,7 +126,8 @@ def test_gnn_embed_bwd_matches_autograd_of_oracle(B, n_max, lo, hi, H, F, num_la
     flat = _flat({k: v.detach() for k, v in sd.items()}, num_layers)
     emb, saved = ops.gnn_embed_fwd(gb.x, rowptr, col, gptr, B, gb.max_nodes, flat, H, num_layers, num_iter, save=True)
     d = ops.gnn_embed_bwd(gb.x, rowptr, col, gptr, B, gb.max_nodes, flat, H, num_layers, num_iter, saved,
-                          d_emb.float().to(DEV))
+                          d_emb.float().to(DEV), pack_stats=gb.pack_stats())
+    assert int(gb.pack_stats()[3]) == 0                       # undirected topology -> gather kernel
     want = _flat({k: v.grad for k, v in sd.items()}, num_layers).cpu().numpy()
     got = d.cpu().numpy()
     assert rel_err(got, want) < 1e-4
@@ -141,11 +142,39 @@ def test_gnn_embed_bwd_matches_autograd_of_oracle(B, n_max, lo, hi, H, F, num_la
             scale = max(np.abs(want[off:off + n]).max(), 1e-3 * np.abs(want).max())
             assert np.abs(got[off:off + n] - want[off:off + n]).max() / scale < 1e-4, nme + k
             off += n
-    # deterministic: a second run gives identical bits for everything but the atomically
-    # accumulated d_xl path; bound that run-to-run jitter instead
+    # the gather kernel has no floating-point atomics on the d_xl path; the small d_att / d_bias /
+    # weight-gradient accumulators are shared-memory atomics, so bound the run-to-run jitter
     d2 = ops.gnn_embed_bwd(gb.x, rowptr, col, gptr, B, gb.max_nodes, flat, H, num_layers, num_iter, saved,
-                           d_emb.float().to(DEV))
+                           d_emb.float().to(DEV), pack_stats=gb.pack_stats())
     assert rel_err(d2.cpu().numpy(), got) < 1e-5
+    # without the packer's symmetry flag the scatter (atomic) kernel runs: same gradients
+    d3 = ops.gnn_embed_bwd(gb.x, rowptr, col, gptr, B, gb.max_nodes, flat, H, num_layers, num_iter, saved,
+                           d_emb.float().to(DEV))
+    assert rel_err(d3.cpu().numpy(), want) < 1e-4
+
+
+def test_gnn_embed_bwd_directed_graph_uses_scatter_kernel():
+    """Edges without a reverse (stats[3] != 0): the gather kernel must stand down."""
+    B, H, F = 7, 22, 3
+    st, sd = _embed_case(B, 24, 5, 24, H, F, 2, 2, seed=77)
+    keep = np.ones(st.edge_index.shape[1], dtype=bool)
+    keep[::5] = False                                         # drop every 5th directed edge
+    ei = np.ascontiguousarray(st.edge_index[:, keep])
+    sd = {k: v.clone().requires_grad_(True) for k, v in sd.items()}
+    ref = O.gnn_embedder(torch.from_numpy(st.x).double(), torch.from_numpy(ei), torch.from_numpy(st.batch), sd, 2, 2,
+                         prefix="", num_graphs=B)
+    d_emb = torch.randn(B, H, generator=torch.Generator().manual_seed(2), dtype=torch.float64)
+    (ref * d_emb).sum().backward()
+    gb = GraphBatch.from_arrays(st.x, ei, st.batch, st.mask, B, int(st.n.max())).to(DEV)
+    rowptr, col, gptr = gb.csr()
+    assert int(gb.pack_stats()[3]) == 1
+    flat = _flat({k: v.detach() for k, v in sd.items()}, 2)
+    emb, saved = ops.gnn_embed_fwd(gb.x, rowptr, col, gptr, B, gb.max_nodes, flat, H, 2, 2, save=True)
+    assert rel_err(emb.cpu().numpy(), ref.detach().numpy()) < 2e-5
+    d = ops.gnn_embed_bwd(gb.x, rowptr, col, gptr, B, gb.max_nodes, flat, H, 2, 2, saved, d_emb.float().to(DEV),
+                          pack_stats=gb.pack_stats())
+    want = _flat({k: v.grad for k, v in sd.items()}, 2).cpu().numpy()
+    assert rel_err(d.cpu().numpy(), want) < 1e-4
 
 
 # ------------------------------------------------------------------ GEMM family

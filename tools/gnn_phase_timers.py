@@ -19,4 +19,12 @@ for (B,nm,lo,hi,links) in [(4096,24,16,24,None),(1024,100,100,100,150)]:
     e0,e1=torch.cuda.Event(enable_timing=True),torch.cuda.Event(enable_timing=True)
     e0.record(); ops.gnn_embed_fwd(gb.x,rp,col,gp,B,gb.max_nodes,gnn,22,2,2); e1.record(); torch.cuda.synchronize()
     lib.gsc_debug_set_gnn_timers(None)
-    print(B,nm,"kernel ms",e0.elapsed_time(e1),"cycles {setup,xrows,mma,xl,phaseB,pool}:",dbg.tolist()[:6])
+    print(B,nm,"fwd kernel ms",e0.elapsed_time(e1),"cycles {setup,xrows,mma,xl,phaseB,pool}:",dbg.tolist()[:6])
+    emb,saved=ops.gnn_embed_fwd(gb.x,rp,col,gp,B,gb.max_nodes,gnn,22,2,2,save=True)
+    d_emb=torch.randn_like(emb)
+    for it in range(2): ops.gnn_embed_bwd(gb.x,rp,col,gp,B,gb.max_nodes,gnn,22,2,2,saved,d_emb,pack_stats=gb.pack_stats())
+    torch.cuda.synchronize(); dbg.zero_()
+    lib.gsc_debug_set_gnn_timers(dbg.data_ptr())
+    e0.record(); ops.gnn_embed_bwd(gb.x,rp,col,gp,B,gb.max_nodes,gnn,22,2,2,saved,d_emb,pack_stats=gb.pack_stats()); e1.record(); torch.cuda.synchronize()
+    lib.gsc_debug_set_gnn_timers(None)
+    print(B,nm,"bwd kernel ms",e0.elapsed_time(e1),"cycles {chunk,hrows,R,rows,edgeT+S,W,split,H}:",dbg.tolist()[:8])
