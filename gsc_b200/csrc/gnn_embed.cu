@@ -19,6 +19,7 @@
 namespace gsc {
 
 constexpr int kGnnThreads = 256;
+constexpr int kColPerNode = 8;     // CSR entries staged in shared memory per node slot (else read from global)
 constexpr float kNegSlope = 0.2f;  // GATv2Conv default negative_slope
 
 struct GnnArgs {
@@ -240,6 +241,35 @@ __global__ void __launch_bounds__(kGnnThreads, 2) gnn_fwd_kernel(const GnnArgs p
 //     the thread-per-node layout that the attention/softmax/aggregation phase wants.
 // Operands use the no-swizzle K-major core-matrix layout (8 rows x 16 B), which lets a thread store
 // its row with 128-bit conflict-free st.shared and needs no padding for K = H.
+// leaky_relu(t, 0.2) = 0.6 t + 0.4 |t|, so the GATv2 score of edge j -> i splits into
+//   s_ij = att . lrelu(xl_j + xr_i) = 0.6 att.xl_j + 0.6 att.xr_i + sum_c (0.4 att_c) |xl_j,c + xr_i,c|
+// with the first two terms per-node scalars: two instructions per channel and edge instead of four.
+// Sums run in four independent accumulators (the kernels have few warps to hide FMA latency).
+template <int HP>
+__device__ __forceinline__ float dot4(const float (&a)[HP], const float (&b)[HP]) {
+  float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+#pragma unroll
+  for (int c = 0; c < HP; c += 4) {
+    s0 = fmaf(a[c], b[c], s0);
+    s1 = fmaf(a[c + 1], b[c + 1], s1);
+    s2 = fmaf(a[c + 2], b[c + 2], s2);
+    s3 = fmaf(a[c + 3], b[c + 3], s3);
+  }
+  return (s0 + s1) + (s2 + s3);
+}
+template <int HP>
+__device__ __forceinline__ float abs_score(const float (&v)[HP], const float (&xr)[HP], const float (&b)[HP]) {
+  float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+#pragma unroll
+  for (int c = 0; c < HP; c += 4) {
+    s0 = fmaf(b[c], fabsf(v[c] + xr[c]), s0);
+    s1 = fmaf(b[c + 1], fabsf(v[c + 1] + xr[c + 1]), s1);
+    s2 = fmaf(b[c + 2], fabsf(v[c + 2] + xr[c + 2]), s2);
+    s3 = fmaf(b[c + 3], fabsf(v[c + 3] + xr[c + 3]), s3);
+  }
+  return (s0 + s1) + (s2 + s3);
+}
+
 template <int HP>
 struct TcL {
   static constexpr int kN = 2 * HP;                       // accumulator columns: xl | xr
@@ -249,6 +279,8 @@ struct TcL {
   static constexpr int kB = (kN / 8) * kGroupBytes;       // kN-row B operand
   static constexpr int kVecFloats = 4 * HP;               // bl, br, att, bias
   static constexpr int kConvBytes = 2 * kB + kVecFloats * 4;
+  static constexpr int kXS = HP + 4;                      // xl row stride: 16 B-aligned, bank-conflict free;
+                                                          // slot [HP] holds 0.6 att.xl_j
   __device__ __forceinline__ static int off(int r, int c) { return (r >> 3) * kGroupBytes + c * 128 + (r & 7) * 16; }
 };
 
@@ -290,7 +322,9 @@ __global__ void __launch_bounds__(kGnnThreads, 2) gnn_fwd_tc_kernel(const GnnArg
   uint8_t* a_hi = convs + p.num_convs * T::kConvBytes;
   uint8_t* a_lo = a_hi + tiles * T::kATile;
   float* xl_s = reinterpret_cast<float*>(a_lo + tiles * T::kATile);
-  uint64_t* bar_ptr = reinterpret_cast<uint64_t*>(xl_s + (size_t)p.cap * HP);
+  int* rp_s = reinterpret_cast<int*>(xl_s + (size_t)p.cap * T::kXS);          // [cap + 4] chunk-local CSR row offsets
+  int* col_s = rp_s + p.cap + 4;                                              // [kColPerNode * cap] chunk-local sources
+  uint64_t* bar_ptr = reinterpret_cast<uint64_t*>(col_s + kColPerNode * p.cap);
   uint32_t* tslot = reinterpret_cast<uint32_t*>(bar_ptr + 1);
   const uint32_t bar = smem_u32(bar_ptr);
   const int tid = threadIdx.x, warp = tid >> 5;
@@ -357,6 +391,15 @@ __global__ void __launch_bounds__(kGnnThreads, 2) gnn_fwd_tc_kernel(const GnnArg
     const int nbase = p.graph_ptr[g0];
     const int nc = p.graph_ptr[g1] - nbase;
     const int warp_first = tid & ~31;                                // slot loops must be warp-uniform (tcgen05.ld)
+    // the chunk's CSR rows are walked by every application: stage them in shared memory once
+    const int ebase = p.rowptr[nbase];
+    const int ne = p.rowptr[nbase + nc] - ebase;
+    const bool staged = ne <= kColPerNode * p.cap;
+    for (int i = tid; i <= nc; i += kGnnThreads) rp_s[i] = p.rowptr[nbase + i] - ebase;
+    if (staged)
+      for (int e = tid; e < ne; e += kGnnThreads) col_s[e] = p.col[ebase + e] - nbase;
+    const int* colp = staged ? col_s : p.col + ebase;
+    const int coff = staged ? 0 : nbase;
 
     // encoder input rows: x -> split operand rows
     for (int i = tid; i < nc; i += kGnnThreads) {
@@ -404,9 +447,12 @@ __global__ void __launch_bounds__(kGnnThreads, 2) gnn_fwd_tc_kernel(const GnnArg
         float xl[HP];
         tmem_load_row<HP>(tmem_base + lane_base + (uint32_t)((i >> 7) * T::kN), xl);
         if (i < nc) {
+          float att[HP];
+          load_row<HP>(vec + 2 * HP, att);
 #pragma unroll
           for (int c = 0; c < HP; ++c) xl[c] += vec[c];
-          store_row<HP>(xl_s + (size_t)i * HP, xl);
+          store_row<HP>(xl_s + (size_t)i * T::kXS, xl);
+          xl_s[(size_t)i * T::kXS + HP] = 0.6f * dot4<HP>(att, xl);
         }
       }
       __syncthreads();
@@ -415,25 +461,22 @@ __global__ void __launch_bounds__(kGnnThreads, 2) gnn_fwd_tc_kernel(const GnnArg
       // ---- phase B: attention scores, online segment softmax, mean aggregation ----
       for (int i0 = warp_first; i0 < nc; i0 += kGnnThreads) {
         const int i = i0 + (tid & 31);
-        float xr[HP], att[HP], acc[HP];
+        float xr[HP], b[HP], acc[HP];
         tmem_load_row<HP>(tmem_base + lane_base + (uint32_t)((i >> 7) * T::kN + HP), xr);
         if (i < nc) {
-          load_row<HP>(vec + 2 * HP, att);
+          load_row<HP>(vec + 2 * HP, b);
 #pragma unroll
           for (int c = 0; c < HP; ++c) { xr[c] += vec[HP + c]; acc[c] = 0.f; }
-          float m = -INFINITY, l = 0.f;
-          const int e0 = p.rowptr[nbase + i], e1 = p.rowptr[nbase + i + 1];
-          for (int e = e0; e < e1; ++e) {
-            const int j = p.col[e] - nbase;
-            float v[HP];
-            load_row<HP>(xl_s + (size_t)j * HP, v);
-            float s = 0.f;
+          const float q_i = 0.6f * dot4<HP>(b, xr);
 #pragma unroll
-            for (int c = 0; c < HP; ++c) {
-              float t = v[c] + xr[c];
-              t = fmaxf(t, kNegSlope * t);
-              s = fmaf(att[c], t, s);
-            }
+          for (int c = 0; c < HP; ++c) b[c] *= 0.4f;
+          float m = -INFINITY, l = 0.f;
+          const int e0 = rp_s[i], e1 = rp_s[i + 1];
+          for (int e = e0; e < e1; ++e) {
+            const int j = colp[e] - coff;
+            float v[HP];
+            load_row<HP>(xl_s + (size_t)j * T::kXS, v);
+            const float s = xl_s[(size_t)j * T::kXS + HP] + q_i + abs_score<HP>(v, xr, b);
             const float m_new = fmaxf(m, s);
             const float sc = __expf(m - m_new);
             const float pe = __expf(s - m_new);
@@ -776,7 +819,12 @@ __global__ void __launch_bounds__(kGnnThreads, 1) gnn_bwd_tc_kernel(const GnnArg
   float* dxr_raw = reinterpret_cast<float*>(d_hi) + (size_t)p.cap * HP;       // [cap][HP]
   int* gid_s = reinterpret_cast<int*>(tail);                                  // [cap] graph of every node
   float4* st_s = reinterpret_cast<float4*>(tail + (size_t)p.cap * 4);         // [cap] softmax max, 1/sum, sum alpha*d_alpha
-  uint64_t* bar_ptr = reinterpret_cast<uint64_t*>(tail + (size_t)p.cap * 20);
+  float2* pq_s = reinterpret_cast<float2*>(tail + (size_t)p.cap * 20);        // [cap] 0.6 att.xl_j, 0.6 att.xr_i
+  int* rp_s = reinterpret_cast<int*>(tail + (size_t)p.cap * 28);              // [cap + 4] chunk-local CSR row offsets
+  int* col_s = rp_s + p.cap + 4;                                              // [kColPerNode * cap]
+  int* perm_s = col_s + kColPerNode * p.cap;                                  // [cap] nodes by descending degree
+  int* hist_s = perm_s + p.cap;                                               // [64] degree histogram / cursors
+  uint64_t* bar_ptr = reinterpret_cast<uint64_t*>(hist_s + 64);
   uint32_t* tslot = reinterpret_cast<uint32_t*>(bar_ptr + 1);
   const uint32_t bar = smem_u32(bar_ptr);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -866,6 +914,35 @@ __global__ void __launch_bounds__(kGnnThreads, 1) gnn_bwd_tc_kernel(const GnnArg
     GSC_TICK(0);
     for (int g = g0 + warp; g < g1; g += kGnnThreads / 32)                  // node -> graph map
       for (int i = p.graph_ptr[g] - nbase + lane; i < p.graph_ptr[g + 1] - nbase; i += 32) gid_s[i] = g;
+    // CSR rows of the chunk -> shared memory (walked 3x per application), and a degree-sorted node
+    // order for the edge passes: lanes of a warp then run rows of similar length instead of all
+    // waiting for the longest one.
+    const int ebase = p.rowptr[nbase];
+    const int ne = p.rowptr[nbase + nc] - ebase;
+    const bool staged = ne <= kColPerNode * p.cap;
+    for (int i = tid; i <= nc; i += kGnnThreads) rp_s[i] = p.rowptr[nbase + i] - ebase;
+    if (staged)
+      for (int e = tid; e < ne; e += kGnnThreads) col_s[e] = p.col[ebase + e] - nbase;
+    const int* colp = staged ? col_s : p.col + ebase;
+    const int coff = staged ? 0 : nbase;
+    if (tid < 64) hist_s[tid] = 0;
+    __syncthreads();
+    for (int i = tid; i < nc; i += kGnnThreads) atomicAdd(hist_s + 63 - min(rp_s[i + 1] - rp_s[i], 63), 1);
+    __syncthreads();
+    if (warp == 0) {                                   // exclusive scan of the 64 buckets
+      int a0 = hist_s[2 * lane], a1 = hist_s[2 * lane + 1];
+      int incl = a0 + a1;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += t;
+      }
+      hist_s[2 * lane] = incl - a0 - a1;
+      hist_s[2 * lane + 1] = incl - a1;
+    }
+    __syncthreads();
+    for (int i = tid; i < nc; i += kGnnThreads)
+      perm_s[atomicAdd(hist_s + 63 - min(rp_s[i + 1] - rp_s[i], 63), 1)] = i;
 
     for (int a = p.num_apps - 1; a >= 0; --a) {
       const int cv = p.app_conv[a];
@@ -925,7 +1002,7 @@ __global__ void __launch_bounds__(kGnnThreads, 1) gnn_bwd_tc_kernel(const GnnArg
       parity ^= 1u;
       tc_fence_after();
       GSC_TICK(2);
-      // ---- 3. xl, xr, g = d_out/deg rows -> smem (own rows) ----
+      // ---- 3. xl, xr, g = d_out/deg rows -> smem (own rows); per-node score scalars ----
       {
       float dbias[HP];
 #pragma unroll
@@ -951,7 +1028,9 @@ __global__ void __launch_bounds__(kGnnThreads, 1) gnn_bwd_tc_kernel(const GnnArg
 #pragma unroll
             for (int c = 0; c < HP; ++c) g[c] = out[c] > 0.f ? g[c] : 0.f;
           }
-          const float inv_deg = 1.f / (float)(p.rowptr[node + 1] - p.rowptr[node]);
+          const float inv_deg = 1.f / (float)(rp_s[i + 1] - rp_s[i]);
+          float att[HP];
+          load_row<HP>(vec + 2 * HP, att);
 #pragma unroll
           for (int c = 0; c < HP; ++c) {
             xl[c] += vec[c];
@@ -962,6 +1041,7 @@ __global__ void __launch_bounds__(kGnnThreads, 1) gnn_bwd_tc_kernel(const GnnArg
           store_row<HP>(xl_s + (size_t)i * HP, xl);
           store_row<HP>(xr_s + (size_t)i * HP, xr);
           store_row<HP>(g_s + (size_t)i * HP, g);
+          pq_s[i] = make_float2(0.6f * dot4<HP>(att, xl), 0.6f * dot4<HP>(att, xr));   // score scalars p_j, q_i
         }
       }
 #pragma unroll
@@ -978,27 +1058,23 @@ __global__ void __launch_bounds__(kGnnThreads, 1) gnn_bwd_tc_kernel(const GnnArg
       float datt[HP];
 #pragma unroll
       for (int c = 0; c < HP; ++c) datt[c] = 0.f;
-      for (int i = tid; i < nc; i += kGnnThreads) {
-        float xr[HP], g[HP], att[HP], dxr[HP];
+      for (int t = tid; t < nc; t += kGnnThreads) {
+        const int i = perm_s[t];
+        float xr[HP], g[HP], b[HP], sg[HP];
         load_row<HP>(xr_s + (size_t)i * HP, xr);
         load_row<HP>(g_s + (size_t)i * HP, g);
-        load_row<HP>(vec + 2 * HP, att);
+        load_row<HP>(vec + 2 * HP, b);
 #pragma unroll
-        for (int c = 0; c < HP; ++c) dxr[c] = 0.f;
-        const int e0 = p.rowptr[nbase + i], e1 = p.rowptr[nbase + i + 1];
+        for (int c = 0; c < HP; ++c) { b[c] *= 0.4f; sg[c] = 0.f; }
+        const float q_i = pq_s[i].y;
+        const int e0 = rp_s[i], e1 = rp_s[i + 1];
         float m = -INFINITY, l = 0.f, dot = 0.f;
         for (int e = e0; e < e1; ++e) {
-          const int j = p.col[e] - nbase;
+          const int j = colp[e] - coff;
           float v[HP];
           load_row<HP>(xl_s + (size_t)j * HP, v);
-          float s = 0.f, da = 0.f;
-#pragma unroll
-          for (int c = 0; c < HP; ++c) {
-            float t = v[c] + xr[c];
-            t = fmaxf(t, kNegSlope * t);
-            s = fmaf(att[c], t, s);
-            da = fmaf(g[c], v[c], da);
-          }
+          const float s = pq_s[j].x + q_i + abs_score<HP>(v, xr, b);
+          const float da = dot4<HP>(g, v);
           const float m_new = fmaxf(m, s);
           const float sc = __expf(m - m_new);
           const float pe = __expf(s - m_new);
@@ -1009,27 +1085,26 @@ __global__ void __launch_bounds__(kGnnThreads, 1) gnn_bwd_tc_kernel(const GnnArg
         const float inv_l = 1.f / (l + 1e-16f);
         dot *= inv_l;
         st_s[i] = make_float4(m, inv_l, dot, 0.f);
+        float ds_sum = 0.f;
         for (int e = e0; e < e1; ++e) {
-          const int j = p.col[e] - nbase;
+          const int j = colp[e] - coff;
           float v[HP];
           load_row<HP>(xl_s + (size_t)j * HP, v);
-          float s = 0.f, da = 0.f;
-#pragma unroll
-          for (int c = 0; c < HP; ++c) {
-            float t = v[c] + xr[c];
-            t = fmaxf(t, kNegSlope * t);
-            s = fmaf(att[c], t, s);
-            da = fmaf(g[c], v[c], da);
-          }
+          const float s = pq_s[j].x + q_i + abs_score<HP>(v, xr, b);
+          const float da = dot4<HP>(g, v);
           const float ds = __expf(s - m) * inv_l * (da - dot);
+          ds_sum += ds;
 #pragma unroll
           for (int c = 0; c < HP; ++c) {
             const float u = v[c] + xr[c];
-            datt[c] = fmaf(ds, fmaxf(u, kNegSlope * u), datt[c]);
-            dxr[c] = fmaf(ds * att[c], (u > 0.f ? 1.f : kNegSlope), dxr[c]);
+            datt[c] = fmaf(ds, fmaxf(u, kNegSlope * u), datt[c]);         // d_att += ds * lrelu(u)
+            sg[c] += (u > 0.f) ? ds : -ds;                                 // sum of ds * sign(u)
           }
         }
-        store_row<HP>(dxr_raw + (size_t)i * HP, dxr);
+        // d_xr_c = att_c * sum_e ds_e * lrelu'(u_e,c),  lrelu' = 0.6 + 0.4 sign   (b = 0.4 att)
+#pragma unroll
+        for (int c = 0; c < HP; ++c) sg[c] = b[c] * fmaf(1.5f, ds_sum, sg[c]);
+        store_row<HP>(dxr_raw + (size_t)i * HP, sg);
       }
 #pragma unroll
       for (int c = 0; c < HP; ++c) {
@@ -1040,35 +1115,35 @@ __global__ void __launch_bounds__(kGnnThreads, 1) gnn_bwd_tc_kernel(const GnnArg
       __syncthreads();
       // ---- 4S. source side: d_xl_j = sum over out-edges j->i of (alpha_ij g_i + d_u_ij); the graph is
       //      symmetric, so the out-neighbours of j are the entries of its own CSR row ----
-      for (int j = tid; j < nc; j += kGnnThreads) {
-        float v[HP], att[HP], dxl[HP];
+      for (int t = tid; t < nc; t += kGnnThreads) {
+        const int j = perm_s[t];
+        float v[HP], b[HP], dxl[HP], sg[HP];
         load_row<HP>(xl_s + (size_t)j * HP, v);
-        load_row<HP>(vec + 2 * HP, att);
+        load_row<HP>(vec + 2 * HP, b);
 #pragma unroll
-        for (int c = 0; c < HP; ++c) dxl[c] = 0.f;
-        const int e0 = p.rowptr[nbase + j], e1 = p.rowptr[nbase + j + 1];
+        for (int c = 0; c < HP; ++c) { b[c] *= 0.4f; dxl[c] = 0.f; sg[c] = 0.f; }
+        const float p_j = pq_s[j].x;
+        float ds_sum = 0.f;
+        const int e0 = rp_s[j], e1 = rp_s[j + 1];
         for (int e = e0; e < e1; ++e) {
-          const int i = p.col[e] - nbase;
+          const int i = colp[e] - coff;
           float xr[HP], g[HP];
           load_row<HP>(xr_s + (size_t)i * HP, xr);
           load_row<HP>(g_s + (size_t)i * HP, g);
           const float4 st = st_s[i];
-          float s = 0.f, da = 0.f;
-#pragma unroll
-          for (int c = 0; c < HP; ++c) {
-            float t = v[c] + xr[c];
-            t = fmaxf(t, kNegSlope * t);
-            s = fmaf(att[c], t, s);
-            da = fmaf(g[c], v[c], da);
-          }
+          const float s = p_j + pq_s[i].y + abs_score<HP>(v, xr, b);
+          const float da = dot4<HP>(g, v);
           const float alpha = __expf(s - st.x) * st.y;
           const float ds = alpha * (da - st.z);
+          ds_sum += ds;
 #pragma unroll
           for (int c = 0; c < HP; ++c) {
-            const float u = v[c] + xr[c];
-            dxl[c] = fmaf(alpha, g[c], fmaf(ds * att[c], (u > 0.f ? 1.f : kNegSlope), dxl[c]));
+            dxl[c] = fmaf(alpha, g[c], dxl[c]);
+            sg[c] += (v[c] + xr[c] > 0.f) ? ds : -ds;
           }
         }
+#pragma unroll
+        for (int c = 0; c < HP; ++c) dxl[c] = fmaf(b[c], fmaf(1.5f, ds_sum, sg[c]), dxl[c]);
         store_row<HP>(xl_s + (size_t)j * HP, dxl);       // own row: xl_j is not needed any more
       }
       __syncthreads();
@@ -1084,24 +1159,23 @@ __global__ void __launch_bounds__(kGnnThreads, 1) gnn_bwd_tc_kernel(const GnnArg
 #pragma unroll
           for (int q = 0; q < T::kKPer; ++q) acc[u][q] = wacc[cv][u * T::kKPer + q];
         if (active) {
+          int koff[T::kKPer];                       // byte offset of column k inside an operand row group
+#pragma unroll
+          for (int q = 0; q < T::kKPer; ++q) koff[q] = ((k0 + q) >> 2) * 128 + ((k0 + q) & 3) * 4;
+          const float* dbase = (c0 < HP) ? xl_s + c0 : dxr_raw + (c0 - HP);
 #pragma unroll 2
           for (int i = warp; i < nc; i += kGnnThreads / 32) {
-            const float* dsrc = (c0 < HP) ? xl_s + (size_t)i * HP + c0 : dxr_raw + (size_t)i * HP + (c0 - HP);
-            const float4 d0 = reinterpret_cast<const float4*>(dsrc)[0], d1 = reinterpret_cast<const float4*>(dsrc)[1];
+            const float4 d0 = reinterpret_cast<const float4*>(dbase + (size_t)i * HP)[0];
+            const float4 d1 = reinterpret_cast<const float4*>(dbase + (size_t)i * HP)[1];
             const float dv[8] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w};
-            const uint8_t* hh = h_hi + (i >> 7) * T::kHTile;
-            const uint8_t* hl = h_lo + (i >> 7) * T::kHTile;
+            const int rbase = (i >> 7) * T::kHTile + ((i & 127) >> 3) * T::kHGroup + (i & 7) * 16;
             float hv[T::kKPer];
 #pragma unroll
             for (int q = 0; q < T::kKPer; ++q) {
               const int k = k0 + q;
-              float h = 0.f;
-              if (k < HP) {
-                const int byte = T::hoff(i & 127, k >> 2) + (k & 3) * 4;
-                h = *reinterpret_cast<const float*>(hh + byte) + *reinterpret_cast<const float*>(hl + byte);
-              } else if (k == HP) {
-                h = 1.f;
-              }
+              float h = (k == HP) ? 1.f : 0.f;
+              if (k < HP) h = *reinterpret_cast<const float*>(h_hi + rbase + koff[q]) +
+                              *reinterpret_cast<const float*>(h_lo + rbase + koff[q]);
               hv[q] = h;
             }
 #pragma unroll
@@ -1284,6 +1358,16 @@ static int launch_fwd(const GnnArgs& a, cudaStream_t st) {
   return GSC_OK;
 }
 
+// Graphs per CTA: as many as fit the node capacity, but never so many that a small batch leaves SMs
+// idle (B = 100 graphs of 100 nodes would otherwise occupy 50 of the 148 SMs).
+static int graphs_per_cta(int cap, int max_nodes, int B, int ctas_per_sm) {
+  int G = cap / max_nodes;
+  if (G < 1) G = 1;
+  const int spread = (int)ceil_div(B, (int64_t)kNumSMs * ctas_per_sm);
+  if (G > spread) G = spread < 1 ? 1 : spread;
+  return G;
+}
+
 // tcgen05 forward: usable when the TMEM accumulators (2*HP columns per 128 nodes) and the operand
 // tiles of the largest graph fit; otherwise the FMA kernel above runs.
 template <int HP>
@@ -1292,16 +1376,16 @@ static int launch_fwd_tc(GnnArgs a, int max_nodes, cudaStream_t st, bool* done) 
   *done = false;
   const int cap = max_nodes <= kGnnThreads ? kGnnThreads : (max_nodes + 127) / 128 * 128;
   const int tiles = cap / 128;
-  const size_t smem = (size_t)a.num_convs * T::kConvBytes + 2 * (size_t)tiles * T::kATile + (size_t)cap * HP * 4 + 16;
+  const size_t smem = (size_t)a.num_convs * T::kConvBytes + 2 * (size_t)tiles * T::kATile + (size_t)cap * T::kXS * 4 +
+                      ((size_t)cap + 4 + (size_t)kColPerNode * cap) * 4 + 16;
   int cols = 32;
   while (cols < tiles * T::kN) cols *= 2;
   if (cols > 512 || smem > 200 * 1024) return GSC_OK;
   a.cap = cap;
-  a.G = cap / max_nodes;
-  if (a.G < 1) a.G = 1;
+  const int per_sm = (2 * smem <= 220 * 1024 && 2 * cols <= 512) ? 2 : 1;
+  a.G = graphs_per_cta(cap, max_nodes, a.B, per_sm);
   GSC_CUDA_TRY(cudaFuncSetAttribute(gnn_fwd_tc_kernel<HP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const int chunks = (a.B + a.G - 1) / a.G;
-  const int per_sm = (2 * smem <= 220 * 1024 && 2 * cols <= 512) ? 2 : 1;
   const int grid = chunks < per_sm * kNumSMs ? chunks : per_sm * kNumSMs;
   gnn_fwd_tc_kernel<HP><<<grid, kGnnThreads, smem, st>>>(a, cols);
   GSC_LAUNCH_CHECK("gnn_fwd_tc_kernel");
@@ -1332,7 +1416,8 @@ static bool plan_bwd_tc(const GnnArgs& a, int max_nodes, int* cap, int* cols, si
   const int tiles = *cap / 128;
   if (*cap > 384) return false;     // two node slots per thread; the atomic kernel must fit as well
   *smem = (size_t)a.num_convs * T::kConvBytes + 2 * ((size_t)tiles * T::kHTile + 1024) +
-          2 * ((size_t)tiles * T::kDTile + 1024) + (size_t)*cap * 20 + 16;
+          2 * ((size_t)tiles * T::kDTile + 1024) + (size_t)*cap * 28 +
+          ((size_t)*cap + 4 + (size_t)kColPerNode * *cap + (size_t)*cap + 64) * 4 + 16;
   const int need_cols = tiles * (T::kN1 + T::kNH);
   *cols = 32;
   while (*cols < need_cols) *cols *= 2;
@@ -1352,7 +1437,7 @@ static int launch_bwd_both(GnnArgs a, int max_nodes, float* d_params, cudaStream
   if (tc) {
     GnnArgs t = a;
     t.cap = cap_t;
-    t.G = cap_t / max_nodes < 1 ? 1 : cap_t / max_nodes;
+    t.G = graphs_per_cta(cap_t, max_nodes, t.B, 1);
     const int grid_t = bwd_grid(t.B, t.G);
     grid = grid_t > grid_f ? grid_t : grid_f;      // one partial per CTA of either kernel
     GSC_CUDA_TRY(cudaFuncSetAttribute(gnn_bwd_tc_kernel<HP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_t));

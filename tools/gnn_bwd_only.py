@@ -1,0 +1,17 @@
+import sys, os, torch
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from gsc_b200 import synth, ops
+from gsc_b200.graph import GraphBatch
+from gsc_b200.models import Actor, AgentSpec
+B, nm, lo, hi, links = 1024, 100, 100, 100, 150
+st = synth.make_states(B, nm, lo, hi, seed=1, fixed_links=links, num_topologies=32)
+gb = GraphBatch.from_states(st).to('cuda')
+actor = Actor(AgentSpec(nm)).to('cuda')
+gnn, _ = actor.views(actor.flat)
+rp, col, gp = gb.csr()
+emb, saved = ops.gnn_embed_fwd(gb.x, rp, col, gp, B, gb.max_nodes, gnn, 22, 2, 2, save=True)
+d_emb = torch.randn_like(emb)
+for it in range(3):
+    ops.gnn_embed_bwd(gb.x, rp, col, gp, B, gb.max_nodes, gnn, 22, 2, 2, saved, d_emb, pack_stats=gb.pack_stats())
+torch.cuda.synchronize()
+print("ok")
