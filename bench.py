@@ -71,42 +71,51 @@ def algorithmic_bytes(w, Pa: int, Pc: int) -> float:
 
 # ------------------------------------------------------------------------------------------------
 class ClockSampler:
-    FIELDS = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    """Samples SM clock and throttle reasons of one GPU through NVML on a background thread while
+    the timed region runs (B200_PROFILING.md: the clocks line)."""
 
-    def __init__(self, index: int):
-        self.proc = None
+    def __init__(self, index: int, period_s: float = 0.005):
+        import threading
+        self.samples, self.max_mhz, self.reasons, self.err = [], None, set(), None
+        self._stop = threading.Event()
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--id={index}", f"--query-gpu={self.FIELDS}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
-                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-        except Exception:
-            self.proc = None
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+        except Exception as e:          # no NVML: report it, never fail the bench
+            self.nv, self.err = None, repr(e)
+            return
+        self.period = period_s
+        self.th = threading.Thread(target=self._run, daemon=True)
+        self.th.start()
+
+    def _run(self):
+        nv = self.nv
+        names = {nv.nvmlClocksThrottleReasonHwSlowdown: "hw_slowdown",
+                 nv.nvmlClocksThrottleReasonHwThermalSlowdown: "hw_thermal_slowdown",
+                 nv.nvmlClocksThrottleReasonSwThermalSlowdown: "sw_thermal_slowdown",
+                 nv.nvmlClocksThrottleReasonSwPowerCap: "sw_power_cap"}
+        while not self._stop.is_set():
+            try:
+                self.samples.append(float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, nme in names.items():
+                    if r & bit:
+                        self.reasons.add(nme)
+            except Exception as e:
+                self.err = repr(e)
+                break
+            self._stop.wait(self.period)
 
     def stop(self):
-        if self.proc is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        self.proc.terminate()
-        try:
-            out, _ = self.proc.communicate(timeout=5)
-        except Exception:
-            self.proc.kill()
-            out = ""
-        sm, mx, reasons = [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for line in out.strip().splitlines():
-            parts = [p.strip() for p in line.split(",")]
-            if len(parts) < 6:
-                continue
-            try:
-                sm.append(float(parts[0])); mx.append(float(parts[1]))
-            except ValueError:
-                continue
-            for nme, val in zip(names, parts[2:6]):
-                if val.lower().startswith("active"):
-                    reasons.add(nme)
-        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+        if self.nv is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [f"nvml unavailable: {self.err}"], "samples": 0}
+        self._stop.set()
+        self.th.join(timeout=2)
+        return {"sm_mhz": statistics.median(self.samples) if self.samples else None, "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(self.samples)}
 
 
 # ------------------------------------------------------------------------------------------------
@@ -239,19 +248,53 @@ def run_ours(args):
     per_op_n = {k: len(v) / op_steps for k, v in timer.items()}
 
     # ---- end-to-end timing through the public API with host buffers (e2e) ----
-    def e2e_step():
-        if graphed is not None:                 # pinned host -> static device inputs -> graph replay
-            graphed.load(host["cur"], host["nxt"], host["actions"], host["rewards"], host["dones"])
-            d = None
-        else:
-            d = h2d_all()
-        r = step(d)
-        if w["kind"] == "c2":
-            out_host.copy_(r, non_blocking=True)
-        else:
+    # c2: the states (x, edge_index, batch, n) come from pinned host memory every step, the mask is
+    #     generated on the device from n, the action matrix goes back to pinned host memory.
+    # c3: the replay buffer lives in HBM (DeviceGraphReplayBuffer).  Every step one new transition
+    #     arrives from pinned host memory (what an environment step produces), a minibatch is drawn
+    #     with the reference's host RNG and gathered on the device, the update runs, and both losses
+    #     are read back.
+    from gsc_b200.buffer import BufferSample, DeviceGraphReplayBuffer
+    from gsc_b200.graph import GraphData
+    st0 = w["cur"]
+    if w["kind"] == "c2":
+        h_n = torch.from_numpy(st0.n.astype(np.int32)).pin_memory()
+        e2e_in = [host["cur"].x, host["cur"].edge_index, host["cur"].batch, h_n]
+
+        def e2e_step():
+            mv = lambda t_: t_.to(dev, non_blocking=True)
+            n_dev = mv(h_n)
+            gb = GraphBatch(mv(host["cur"].x), mv(host["cur"].edge_index), mv(host["cur"].batch),
+                            ops.build_mask(n_dev, n_max, 3), B, host["cur"].max_nodes)
+            out_host.copy_(ddpg.predict(actor, gb), non_blocking=True)
+        h2d = sum(t_.numel() * t_.element_size() for t_ in e2e_in)
+    else:
+        cap = max(2 * B, 2048)
+        rb = DeviceGraphReplayBuffer(cap, spec.env.action_space, device=dev, n_max=n_max, e_max=2 * 150 + 4)
+        for _ in range(cap // B - 1):                                   # leave room for the streamed adds
+            rb.bulk_load(w["cur"], w["nxt"], w["actions"], w["rewards"], w["dones"])
+        g0 = st0.graph(0)
+        new_obs = GraphData(torch.from_numpy(g0["x"]).pin_memory(), torch.from_numpy(g0["edge_index"]).pin_memory(), None)
+        new_act = torch.from_numpy(w["actions"][0]).pin_memory()
+        static = None
+        if graphed is not None:
+            static = BufferSample(graphed.cur, graphed.actions, graphed.nxt, graphed.dones, graphed.rewards)
+
+        def e2e_step():
+            if rb.pos + 1 >= rb.buffer_size:
+                rb.pos = rb.buffer_size - B                              # keep cycling inside the buffer
+            rb.add(new_obs, new_obs, new_act, 0.5, False)
+            if static is not None:
+                rb.sample(B, out=static)
+                r = graphed.replay()
+            else:
+                smp = rb.sample(B)
+                r = upd.update(smp.observations, smp.next_observations, smp.actions, smp.rewards, smp.dones)
             out_host[0:1].copy_(r[1], non_blocking=True)
             out_host[1:2].copy_(r[2], non_blocking=True)
+        h2d = 2 * (new_obs.x.numel() * 4 + new_obs.edge_index.numel() * 4) + new_act.numel() * 4 + 8 * B + 2 * 2 * (B + 1) * 4
 
+    np.random.seed(1234 + rank)
     for _ in range(min(args.warmup, 3)):
         e2e_step()
     barrier()
@@ -275,10 +318,6 @@ def run_ours(args):
         total_states = B * world * args.steps
         value = total_states / (dev_ms / 1e3)
         e2e_value = total_states / (e2e_ms / 1e3)
-        hb = host["cur"]
-        h2d = sum(t_.numel() * t_.element_size() for t_ in (hb.x, hb.edge_index, hb.batch, hb.mask))
-        if w["kind"] == "c3":
-            h2d += host["nxt"].x.numel() * 4 + sum(host[k].numel() * 4 for k in ("actions", "rewards", "dones"))
         d2h = out_host.numel() * 4
         # dominant kernel + roofline
         top = max(per_op, key=per_op.get)
@@ -303,7 +342,11 @@ def run_ours(args):
                        "l2": "flushed between timed steps (256 MiB write)",
                        "parallelism": f"dp{world}" if w["kind"] == "c3" else f"replicas{world}"},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                    "ms_per_step": e2e_ms / args.steps},
+                    "ms_per_step": e2e_ms / args.steps,
+                    "path": ("pinned host states -> H2D -> mask from n on device -> packer+embedder+actor -> D2H actions"
+                             if w["kind"] == "c2" else
+                             "DeviceGraphReplayBuffer.add(1 transition from pinned host) -> sample(B) (host RNG, device gather) "
+                             "-> DDPG update -> D2H losses")},
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "cpu_baseline": cpu,
             "per_op_ms": {k: round(v, 4) for k, v in sorted(per_op.items(), key=lambda kv: -kv[1])[:12]},
             "wall_ms_per_step_incl_flush": t_wall / args.steps * 1e3,

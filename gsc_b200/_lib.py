@@ -38,6 +38,10 @@ _PROTOS = {
                              c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
     "gsc_pack_csr_noalloc": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_int64, c_void_p, c_void_p,
                                      c_void_p, c_void_p, c_void_p]),
+    "gsc_build_mask": (c_int, [c_void_p, c_int64, c_int, c_int, c_void_p, c_void_p]),
+    "gsc_replay_gather": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64,
+                                  c_int, c_int, c_int, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "gsc_gather_rows": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_void_p, c_void_p]),
     "gsc_gnn_param_floats": (c_int64, [c_int, c_int, c_int]),
     "gsc_gnn_saved_floats": (c_int64, [c_int64, c_int, c_int, c_int]),
     "gsc_gnn_embed_fwd": (c_int, [c_void_p, c_int64, c_int, c_void_p, c_void_p, c_void_p, c_int64,

@@ -68,3 +68,158 @@ class GraphReplayBuffer:
             dones=torch.from_numpy(self.dones[batch_inds]).to(self.device),
             rewards=torch.from_numpy(self.rewards[batch_inds]).to(self.device),
         )
+
+
+class DeviceGraphReplayBuffer:
+    """``GraphReplayBuffer`` with the storage in HBM.
+
+    Same ``add`` / ``sample`` surface and the same numpy RNG draws as the reference buffer, but
+    transitions are kept on the device in padded struct-of-arrays form -- ``x[cap, N_max, F]``,
+    graph-local ``edge_index[cap, 2, E_max]`` (int32), node / edge counts, ``actions[cap, A]`` -- and
+    a minibatch is gathered by index with one kernel straight into ``Batch.from_data_list`` layout.
+    Masks are not stored: an observation's mask is ``mask[:n, :, :, :n] = 1`` (reference
+    src/rlsp/envs/simulator_wrapper.py:302-306), so it is regenerated from ``n`` on the device; ``add``
+    verifies that the mask it is given has that form.  Per gradient step the host only sends the
+    sampled indices and two small prefix-sum arrays instead of re-collating and copying ~2(4A) bytes
+    per state.
+    """
+
+    def __init__(self, buffer_size: int, action_space, device="cuda", n_max: int = None, num_feat: int = 3,
+                 e_max: int = None, groups_per_node: int = None) -> None:
+        from . import ops
+        self.ops = ops
+        self.buffer_size = int(buffer_size)
+        self.device = torch.device(device)
+        self.action_space = int(np.prod(action_space.shape))
+        if n_max is None:
+            raise ValueError("DeviceGraphReplayBuffer needs n_max (EnvironmentLimits.MAX_NODE_COUNT)")
+        self.n_max, self.num_feat = int(n_max), int(num_feat)
+        self.groups = int(groups_per_node) if groups_per_node else self.action_space // (self.n_max * self.n_max)
+        if self.n_max * self.groups * self.n_max != self.action_space:
+            raise ValueError("action dimension is not n_max * groups_per_node * n_max")
+        self.e_max = int(e_max) if e_max else 8 * self.n_max
+        cap, dev = self.buffer_size, self.device
+        z = lambda *s, dt=torch.float32: torch.zeros(*s, dtype=dt, device=dev)
+        self.x, self.next_x = z(cap, self.n_max, self.num_feat), z(cap, self.n_max, self.num_feat)
+        self.ei, self.next_ei = z(cap, 2, self.e_max, dt=torch.int32), z(cap, 2, self.e_max, dt=torch.int32)
+        self.n, self.next_n = z(cap, dt=torch.int32), z(cap, dt=torch.int32)
+        self.ec, self.next_ec = z(cap, dt=torch.int32), z(cap, dt=torch.int32)
+        self.actions = z(cap, self.action_space)
+        self.rewards, self.dones = z(cap), torch.ones(cap, dtype=torch.float32, device=dev)
+        # host mirrors of the counts: minibatch sizes are known without a device round trip
+        self.n_h = np.zeros((2, cap), dtype=np.int32)
+        self.ec_h = np.zeros((2, cap), dtype=np.int32)
+        self.pos, self.full = 0, False
+
+    # ---- add ------------------------------------------------------------------------------------
+    def _check_mask(self, obs, n: int) -> None:
+        mask = getattr(obs, "mask", None)
+        if mask is None:
+            return
+        m = np.asarray(mask.detach().cpu() if isinstance(mask, torch.Tensor) else mask, dtype=np.float32)
+        m = m.reshape(self.n_max, self.groups, self.n_max)
+        ok = m[:n, :, :n].all() and m[n:].sum() == 0 and m[:, :, n:].sum() == 0
+        if not ok:
+            raise ValueError("observation mask is not the structured mask[:n, :, :, :n] = 1; "
+                             "use GraphReplayBuffer for arbitrary masks")
+
+    def _store_obs(self, which: int, obs, x_store, ei_store, n_store, ec_store) -> None:
+        x = torch.as_tensor(obs.x, dtype=torch.float32)
+        ei = torch.as_tensor(obs.edge_index).to(torch.int32)
+        n, e = int(x.shape[0]), int(ei.shape[1])
+        if n > self.n_max or e > self.e_max:
+            raise ValueError(f"observation with {n} nodes / {e} edges exceeds n_max={self.n_max} / e_max={self.e_max}")
+        self._check_mask(obs, n)
+        p = self.pos
+        x_store[p, :n].copy_(x, non_blocking=True)
+        ei_store[p, :, :e].copy_(ei, non_blocking=True)
+        n_store[p:p + 1].fill_(n)
+        ec_store[p:p + 1].fill_(e)
+        self.n_h[which, p], self.ec_h[which, p] = n, e
+
+    def add(self, obs, next_obs, action, reward, done, infos=None) -> None:
+        p = self.pos
+        self._store_obs(0, obs, self.x, self.ei, self.n, self.ec)
+        self._store_obs(1, next_obs, self.next_x, self.next_ei, self.next_n, self.next_ec)
+        self.actions[p].copy_(torch.as_tensor(np.asarray(action), dtype=torch.float32), non_blocking=True)
+        self.rewards[p:p + 1].fill_(float(reward))
+        self.dones[p:p + 1].fill_(float(done))
+        self.pos += 1
+        if self.pos == self.buffer_size:
+            self.pos, self.full = 0, True
+
+    def bulk_load(self, cur, nxt, actions, rewards, dones) -> None:
+        """Fill the buffer from collated ``gsc_b200.synth.StateBatch`` pairs in a few large copies
+        (benchmarks and tests; ``add`` is the per-environment-step path)."""
+        B = cur.num_graphs
+        if self.pos + B > self.buffer_size:
+            raise ValueError("bulk_load would wrap around the buffer")
+        for which, st, xs, eis, ns, ecs in ((0, cur, self.x, self.ei, self.n, self.ec),
+                                            (1, nxt, self.next_x, self.next_ei, self.next_n, self.next_ec)):
+            n = st.n.astype(np.int32)
+            xp = np.zeros((B, self.n_max, self.num_feat), dtype=np.float32)
+            eip = np.zeros((B, 2, self.e_max), dtype=np.int32)
+            ec = np.zeros(B, dtype=np.int32)
+            owner = st.batch[st.edge_index[0]]                       # graph of every edge
+            starts = np.searchsorted(owner, np.arange(B))
+            ends = np.searchsorted(owner, np.arange(B), side="right")
+            for g in range(B):
+                lo, hi = int(st.ptr[g]), int(st.ptr[g + 1])
+                xp[g, :hi - lo] = st.x[lo:hi]
+                e = ends[g] - starts[g]
+                if e > self.e_max:
+                    raise ValueError(f"state with {e} edges exceeds e_max={self.e_max}")
+                eip[g, :, :e] = st.edge_index[:, starts[g]:ends[g]] - lo
+                ec[g] = e
+            sl = slice(self.pos, self.pos + B)
+            xs[sl].copy_(torch.from_numpy(xp))
+            eis[sl].copy_(torch.from_numpy(eip))
+            ns[sl].copy_(torch.from_numpy(n))
+            ecs[sl].copy_(torch.from_numpy(ec))
+            self.n_h[which, sl], self.ec_h[which, sl] = n, ec
+        sl = slice(self.pos, self.pos + B)
+        self.actions[sl].copy_(torch.from_numpy(np.ascontiguousarray(actions, dtype=np.float32)))
+        self.rewards[sl].copy_(torch.from_numpy(np.ascontiguousarray(rewards, dtype=np.float32)))
+        self.dones[sl].copy_(torch.from_numpy(np.ascontiguousarray(dones, dtype=np.float32)))
+        self.pos += B
+        if self.pos == self.buffer_size:
+            self.pos, self.full = 0, True
+
+    # ---- sample ---------------------------------------------------------------------------------
+    def sample_indices(self, batch_size: int) -> np.ndarray:
+        """The reference's index draw (buffer.py:57-62), same global numpy RNG calls."""
+        if self.full:
+            return (np.random.randint(1, self.buffer_size, size=batch_size) + self.pos) % self.buffer_size
+        return np.random.randint(0, self.pos, size=batch_size)
+
+    def _gather_obs(self, which: int, idx_np: np.ndarray, idx_dev: torch.Tensor, out=None) -> GraphBatch:
+        stores = ((self.x, self.ei, self.n, self.ec), (self.next_x, self.next_ei, self.next_n, self.next_ec))[which]
+        n_sel, e_sel = self.n_h[which, idx_np], self.ec_h[which, idx_np]
+        node_ptr = np.zeros(len(idx_np) + 1, dtype=np.int32)
+        edge_ptr = np.zeros(len(idx_np) + 1, dtype=np.int32)
+        np.cumsum(n_sel, out=node_ptr[1:])
+        np.cumsum(e_sel, out=edge_ptr[1:])
+        nt, et = int(node_ptr[-1]), int(edge_ptr[-1])
+        ptrs = torch.from_numpy(np.stack([node_ptr, edge_ptr])).to(self.device, non_blocking=True)
+        if out is not None and (out.x.shape[0] != nt or out.edge_index.shape[1] != et):
+            raise ValueError("static minibatch buffers have a different node / edge count than this sample")
+        x, ei, batch, n_dev = self.ops.replay_gather(
+            *stores, idx_dev, ptrs[0], ptrs[1], nt, et,
+            x_out=None if out is None else out.x, ei_out=None if out is None else out.edge_index,
+            batch_out=None if out is None else out.batch)
+        mask = self.ops.build_mask(n_dev, self.n_max, self.groups, out=None if out is None else out.mask)
+        if out is not None:
+            return out
+        return GraphBatch(x, ei, batch, mask, len(idx_np), int(n_sel.max()) if len(n_sel) else 0)
+
+    def sample(self, batch_size: int, out: "BufferSample" = None) -> BufferSample:
+        """Minibatch on the device.  ``out`` (a previous BufferSample of identical shapes, e.g. the
+        static inputs of a CUDA-graph) is overwritten in place when given."""
+        idx_np = self.sample_indices(batch_size)
+        idx_dev = torch.from_numpy(idx_np.astype(np.int64)).to(self.device, non_blocking=True)
+        cur = self._gather_obs(0, idx_np, idx_dev, None if out is None else out.observations)
+        nxt = self._gather_obs(1, idx_np, idx_dev, None if out is None else out.next_observations)
+        actions = self.ops.gather_rows(self.actions, idx_dev, None if out is None else out.actions)
+        rewards = self.ops.gather_rows(self.rewards, idx_dev, None if out is None else out.rewards)
+        dones = self.ops.gather_rows(self.dones, idx_dev, None if out is None else out.dones)
+        return BufferSample(observations=cur, actions=actions, next_observations=nxt, dones=dones, rewards=rewards)

@@ -164,6 +164,55 @@ def pack_csr_noalloc(edge_index: torch.Tensor, batch: Optional[torch.Tensor], nu
     return rowptr, col, graph_ptr, stats
 
 
+def build_mask(n: torch.Tensor, n_max: int, groups_per_node: int, out: Optional[torch.Tensor] = None):
+    """Structured action mask [B, n_max*groups*n_max] from per-state node counts (int32, device)."""
+    _need_cuda(n)
+    B = int(n.shape[0])
+    A = n_max * groups_per_node * n_max
+    if out is None:
+        out = torch.empty(B, A, dtype=torch.float32, device=n.device)
+    with _Timed(f"build_mask[{B}x{A}]"):
+        check(_lib.load().gsc_build_mask(_ptr(n), B, n_max, groups_per_node, _ptr(out), _stream()), "gsc_build_mask")
+    _count(1)
+    return out
+
+
+def replay_gather(store_x, store_ei, store_n, store_ecount, idx, node_ptr, edge_ptr, num_nodes: int,
+                  num_edges: int, x_out=None, ei_out=None, batch_out=None, n_out=None):
+    """Gather the transitions ``idx`` from padded device storage into Batch layout (see gsc_b200.h)."""
+    lib = _lib.load()
+    dev = store_x.device
+    B = int(idx.shape[0])
+    n_max, F = int(store_x.shape[1]), int(store_x.shape[2])
+    e_max = int(store_ei.shape[2])
+    if x_out is None:
+        x_out = torch.empty(num_nodes, F, dtype=torch.float32, device=dev)
+    if ei_out is None:
+        ei_out = torch.empty(2, num_edges, dtype=torch.int64, device=dev)
+    if batch_out is None:
+        batch_out = torch.empty(num_nodes, dtype=torch.int64, device=dev)
+    if n_out is None:
+        n_out = torch.empty(B, dtype=torch.int32, device=dev)
+    with _Timed("replay_gather"):
+        check(lib.gsc_replay_gather(_ptr(store_x), _ptr(store_ei), _ptr(store_n), _ptr(store_ecount), _ptr(idx),
+                                    _ptr(node_ptr), _ptr(edge_ptr), B, n_max, F, e_max, num_edges, _ptr(x_out),
+                                    _ptr(ei_out), _ptr(batch_out), _ptr(n_out), _stream()), "gsc_replay_gather")
+    _count(1)
+    return x_out, ei_out, batch_out, n_out
+
+
+def gather_rows(src: torch.Tensor, idx: torch.Tensor, out: Optional[torch.Tensor] = None):
+    """out[b] = src[idx[b]] for a [cap, A] (or [cap]) fp32 device tensor."""
+    A = int(src.shape[1]) if src.dim() == 2 else 1
+    B = int(idx.shape[0])
+    if out is None:
+        out = torch.empty((B, A) if src.dim() == 2 else (B,), dtype=torch.float32, device=src.device)
+    with _Timed(f"gather_rows[{B}x{A}]"):
+        check(_lib.load().gsc_gather_rows(_ptr(src), _ptr(idx), B, A, _ptr(out), _stream()), "gsc_gather_rows")
+    _count(1)
+    return out
+
+
 def gnn_param_floats(in_dim: int, hidden: int, num_layers: int) -> int:
     return int(_lib.load().gsc_gnn_param_floats(in_dim, hidden, num_layers))
 

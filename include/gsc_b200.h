@@ -74,6 +74,28 @@ int gsc_pack_csr_noalloc(const int64_t* edge_index, int64_t num_edges, const int
                          int64_t num_nodes, int64_t num_graphs, int32_t* rowptr, int32_t* col,
                          int32_t* graph_ptr, int32_t* stats, void* stream);
 
+/* ---- structured action mask and device-resident replay storage ----------------------------
+ * mask[b, ((i*G + q)*n_max + j)] = (i < n[b]) && (j < n[b]), G = groups_per_node (sfcs x sfs):
+ * the mask every observation carries in the reference (src/rlsp/envs/simulator_wrapper.py:302-306),
+ * generated from the node counts instead of being stored and copied. */
+int gsc_build_mask(const int32_t* n, int64_t B, int n_max, int groups_per_node, float* mask, void* stream);
+
+/* Minibatch gather from padded struct-of-arrays replay storage (replaces the per-step host collate
+ * of reference src/rlsp/agents/buffer.py:56-89): slot idx[b] of store_x[cap, n_max, F],
+ * store_ei[cap, 2, e_max] (int32, graph-local ids), store_n[cap], store_ecount[cap] is written in
+ * Batch.from_data_list layout at node_ptr[b] / edge_ptr[b] (exclusive prefix sums of the selected
+ * n / edge counts, B+1 entries): x_out[Nt, F], edge_index_out[2, Et] int64 with node offsets,
+ * batch_out[Nt] int64, n_out[B] (nullable). */
+int gsc_replay_gather(const float* store_x, const int32_t* store_ei, const int32_t* store_n,
+                      const int32_t* store_ecount, const int64_t* idx, const int32_t* node_ptr,
+                      const int32_t* edge_ptr, int64_t B, int n_max, int num_feat, int e_max,
+                      int64_t num_edges_total, float* x_out, int64_t* edge_index_out, int64_t* batch_out,
+                      int32_t* n_out, void* stream);
+
+/* out[b, :] = src[idx[b], :] -- actions[cap, A] (and rewards / dones with A = 1) of a minibatch
+ * (reference buffer.py:71,83-84: self.actions[batch_inds] ...). */
+int gsc_gather_rows(const float* src, const int64_t* idx, int64_t B, int64_t A, float* out, void* stream);
+
 /* ---- GNN embedder ------------------------------------------------------------------------
  * Replaces GNNEmbedder.forward (reference src/rlsp/agents/models.py:37-53): encoder GATv2Conv,
  * ReLU, num_iter x (num_layers-1) process GATv2Conv applications, global_mean_pool -- one launch.

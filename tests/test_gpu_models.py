@@ -210,6 +210,48 @@ def test_replay_buffer_to_update_pipeline_runs():
     assert not torch.equal(before, nets[0].flat)
 
 
+def test_device_replay_buffer_samples_what_the_host_buffer_samples():
+    from gsc_b200.buffer import DeviceGraphReplayBuffer
+    n_max = 8
+    spec = AgentSpec(n_max)
+    host = GraphReplayBuffer(16, spec.env.action_space, device=DEV)
+    dev = DeviceGraphReplayBuffer(16, spec.env.action_space, device=DEV, n_max=n_max)
+    st = synth.make_states(21, n_max, 2, 8, seed=4, num_topologies=4)
+    acts = synth.make_actions(st)
+    for gi in range(21):                                             # wraps around
+        d, nd = st.graph(gi), st.graph((gi * 7 + 3) % 21)            # next state on another topology
+        o, no = GraphData(d["x"], d["edge_index"], d["mask"]), GraphData(nd["x"], nd["edge_index"], nd["mask"])
+        host.add(o, no, acts[gi], 0.25 * gi, gi % 5 == 0, {})
+        dev.add(o, no, acts[gi], 0.25 * gi, gi % 5 == 0, {})
+    assert dev.full and dev.pos == host.pos
+    for B in (1, 6):
+        np.random.seed(B)
+        a = host.sample(B)
+        np.random.seed(B)
+        b = dev.sample(B)
+        for ga, gb in ((a.observations, b.observations), (a.next_observations, b.next_observations)):
+            assert torch.equal(ga.x, gb.x) and torch.equal(ga.batch, gb.batch) and torch.equal(ga.mask, gb.mask)
+            assert torch.equal(ga.edge_index, gb.edge_index)
+            assert gb.num_graphs == B and gb.max_nodes == ga.max_nodes
+        assert torch.equal(a.actions, b.actions) and torch.equal(a.rewards, b.rewards) and torch.equal(a.dones, b.dones)
+        # in-place refill of a previous sample (static CUDA-graph inputs) gives the same batch
+        np.random.seed(B)
+        c = dev.sample(B, out=b)
+        assert c.observations is b.observations and torch.equal(c.observations.x, a.observations.x)
+    bad = GraphData(st.graph(0)["x"], st.graph(0)["edge_index"], np.ones((1, st.action_dim), np.float32))
+    if int(st.n[0]) < n_max:
+        with pytest.raises(ValueError):
+            dev.add(bad, bad, acts[0], 0.0, False, {})
+
+
+def test_build_mask_matches_structured_mask():
+    n = np.array([1, 5, 8, 3, 8], dtype=np.int32)
+    got = ops.build_mask(torch.from_numpy(n).to(DEV), 8, 3).cpu().numpy()
+    assert np.array_equal(got, synth.structured_mask(n, 8))
+    got = ops.build_mask(torch.from_numpy(n[:2]).to(DEV), 5, 1).cpu().numpy()      # A = 25: scalar kernel
+    assert np.array_equal(got, synth.structured_mask(np.minimum(n[:2], 5), 5, 1, 1))
+
+
 def test_post_process_and_choose_action_entry_points(golden_ddpg):
     g = golden_ddpg
     spec, (actor, _, _, _) = _nets(g)
