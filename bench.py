@@ -153,21 +153,24 @@ def run_ours(args):
                                world_size=world)
 
     def host_batch(st):
-        return GraphBatch.from_states(st, pin=True)
+        return GraphBatch.from_states(st, pin=True, dense_mask=args.dense_mask)
 
     h_cur = host_batch(w["cur"])
     host = {"cur": h_cur}
     if w["kind"] == "c3":
         host["nxt"] = host_batch(w["nxt"])
-        host["nxt"].edge_index, host["nxt"].batch, host["nxt"].mask = h_cur.edge_index, h_cur.batch, h_cur.mask
+        host["nxt"].edge_index, host["nxt"].batch, host["nxt"]._mask = h_cur.edge_index, h_cur.batch, h_cur._mask
         for k in ("actions", "rewards", "dones"):
             host[k] = torch.from_numpy(w[k]).pin_memory()
 
     def to_dev(hb, share=None):
         mv = lambda t: t.to(dev, non_blocking=True)
+        mo = lambda t: None if t is None else mv(t)
         if share is None:
-            return GraphBatch(mv(hb.x), mv(hb.edge_index), mv(hb.batch), mv(hb.mask), hb.num_graphs, hb.max_nodes)
-        return GraphBatch(mv(hb.x), share.edge_index, share.batch, share.mask, hb.num_graphs, hb.max_nodes)
+            return GraphBatch(mv(hb.x), mv(hb.edge_index), mv(hb.batch), mo(hb._mask), hb.num_graphs, hb.max_nodes,
+                              None, None if args.dense_mask else mv(hb.n_nodes), hb.n_max, hb.groups)
+        return GraphBatch(mv(hb.x), share.edge_index, share.batch, share._mask, hb.num_graphs, hb.max_nodes,
+                          None, share.n_nodes, hb.n_max, hb.groups)
 
     def h2d_all():
         d = {"cur": to_dev(host["cur"])}
@@ -178,7 +181,7 @@ def run_ours(args):
         return d
 
     def fresh(gb):   # same device tensors, CSR not packed yet: the packer is part of every step
-        return GraphBatch(gb.x, gb.edge_index, gb.batch, gb.mask, gb.num_graphs, gb.max_nodes)
+        return gb.view()
 
     def step(d):
         if w["kind"] == "c2":
@@ -265,7 +268,8 @@ def run_ours(args):
             mv = lambda t_: t_.to(dev, non_blocking=True)
             n_dev = mv(h_n)
             gb = GraphBatch(mv(host["cur"].x), mv(host["cur"].edge_index), mv(host["cur"].batch),
-                            ops.build_mask(n_dev, n_max, 3), B, host["cur"].max_nodes)
+                            ops.build_mask(n_dev, n_max, 3) if args.dense_mask else None, B,
+                            host["cur"].max_nodes, None, n_dev, n_max, 3)
             out_host.copy_(ddpg.predict(actor, gb), non_blocking=True)
         h2d = sum(t_.numel() * t_.element_size() for t_ in e2e_in)
     else:
@@ -352,7 +356,9 @@ def run_ours(args):
             "dtype": "f32" if args.precision == "fp32" else "tf32 tensor-core GEMMs (fp32 accumulate), f32 elsewhere",
             "data": "synthetic",
             "config": {"workload": workload_name(w), "states_per_gpu": B, "n_max": n_max,
-                       "precision": args.precision, "cuda_graph": bool(graphed is not None),
+                       "precision": args.precision,
+                       "mask": "dense [B, A] tensor" if args.dense_mask else "structured: mask[:n,:,:,:n] from node counts",
+                       "cuda_graph": bool(graphed is not None),
                        "weights": "reference init (PyG glorot / torch Linear), torch.manual_seed(1234)",
                        "l2": "flushed between timed steps (256 MiB write)",
                        "parallelism": f"dp{world}" if w["kind"] == "c3" else f"replicas{world}"},
@@ -390,6 +396,12 @@ def op_bytes(name: str, w, Pa, Pc) -> float:
         return 36.0 * n
     if name.startswith("pack_csr"):
         return 2 * 16.0 * E + 8.0 * Nt + 4.0 * (E + Nt) + 4.0 * Nt
+    if name.startswith("mask_table"):      # reads the [N1, A] mask block of the weight, writes the table
+        N1, A = (int(v) for v in name[name.index("[") + 1:name.index("]")].split("x"))
+        return 4.0 * N1 * A + 4.0 * N1 * (w["n_max"] + 1)
+    if name.startswith("mask_wgrad"):      # reads dY [B, N1] and n, writes the [N1, A] gradient block
+        N1, A = (int(v) for v in name[name.index("[") + 1:name.index("]")].split("x"))
+        return 4.0 * N1 * A + 4.0 * B * N1 + 4.0 * B
     if name.startswith("colsum"):
         M, N = (int(v) for v in name[name.index("[") + 1:name.index("]")].split("x"))
         return 4.0 * M * N
@@ -482,6 +494,8 @@ def main():
                     help="c3 (default): full DDPG update, the fwd+bwd+Adam step BASELINE.json's metric names; "
                          "c2: embedder + actor inference")
     ap.add_argument("--batch", type=int, default=0)
+    ap.add_argument("--dense-mask", action="store_true",
+                    help="carry the dense [B, A] mask tensor instead of the per-state node counts")
     ap.add_argument("--no-graph", dest="graph", action="store_false",
                     help="c3: launch the update kernel by kernel instead of replaying its CUDA graph")
     ap.add_argument("--precision", default=os.environ.get("GSC_BENCH_PRECISION", "tf32"), choices=["fp32", "tf32"],

@@ -15,6 +15,7 @@ LIB_PATH = os.path.join(_HERE, "libgsc_b200.so")
 _lib = None
 
 EPI_BIAS, EPI_RELU, EPI_MUL, EPI_GATE, EPI_CLAMP1 = 1, 2, 4, 8, 16
+EPI_ROWTABLE, EPI_SMASK = 64, 128
 MAX_HIDDEN = 32
 PACK_NOALLOC_MAX_NODES = 1 << 20
 
@@ -23,7 +24,9 @@ class GemmArgs(Structure):
     _fields_ = [("A", c_void_p * 3), ("B", c_void_p * 3), ("K", c_int64 * 3),
                 ("a_rs", c_int64 * 3), ("a_cs", c_int64 * 3), ("b_rs", c_int64 * 3),
                 ("b_cs", c_int64 * 3), ("num_seg", c_int), ("flags", c_int), ("bias", c_void_p),
-                ("mul", c_void_p), ("ld_mul", c_int64), ("gate", c_void_p), ("ld_gate", c_int64)]
+                ("mul", c_void_p), ("ld_mul", c_int64), ("gate", c_void_p), ("ld_gate", c_int64),
+                ("row_table", c_void_p), ("ld_table", c_int64), ("row_n", c_void_p), ("n_max", c_int32),
+                ("groups", c_int32)]
 
 
 class GscError(RuntimeError):
@@ -53,6 +56,10 @@ _PROTOS = {
     "gsc_gemm_workspace_bytes": (c_size_t, [c_int64, c_int64, c_int64]),
     "gsc_gemm": (c_int, [POINTER(GemmArgs), c_int64, c_int64, c_void_p, c_int64, c_void_p, c_size_t,
                          c_void_p]),
+    "gsc_mask_table": (c_int, [c_void_p, c_int64, c_int64, c_int, c_int, c_void_p, c_int64, c_void_p]),
+    "gsc_mask_wgrad_workspace_bytes": (c_size_t, [c_int64, c_int]),
+    "gsc_mask_wgrad": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_int64, c_int, c_int, c_void_p, c_int64,
+                               c_void_p, c_size_t, c_void_p]),
     "gsc_mul_gate": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_int64, c_int64,
                              c_void_p, c_int64, c_void_p]),
     "gsc_colsum": (c_int, [c_void_p, c_int64, c_int64, c_int64, c_void_p, c_void_p]),

@@ -206,11 +206,14 @@ class DeviceGraphReplayBuffer:
         x, ei, batch, n_dev = self.ops.replay_gather(
             *stores, idx_dev, ptrs[0], ptrs[1], nt, et,
             x_out=None if out is None else out.x, ei_out=None if out is None else out.edge_index,
-            batch_out=None if out is None else out.batch)
-        mask = self.ops.build_mask(n_dev, self.n_max, self.groups, out=None if out is None else out.mask)
+            batch_out=None if out is None else out.batch, n_out=None if out is None else out.n_nodes)
         if out is not None:
+            if out._mask is not None:                 # a dense mask was materialised for this buffer: refresh it
+                self.ops.build_mask(n_dev, self.n_max, self.groups, out=out._mask)
             return out
-        return GraphBatch(x, ei, batch, mask, len(idx_np), int(n_sel.max()) if len(n_sel) else 0)
+        # structured batch: the [B, A] mask is generated from n only if somebody asks for .mask
+        return GraphBatch(x, ei, batch, None, len(idx_np), int(n_sel.max()) if len(n_sel) else 0, None,
+                          n_dev, self.n_max, self.groups)
 
     def sample(self, batch_size: int, out: "BufferSample" = None) -> BufferSample:
         """Minibatch on the device.  ``out`` (a previous BufferSample of identical shapes, e.g. the

@@ -29,6 +29,10 @@ struct GemmDev {
   const float* mul;
   const float* gate;
   int64_t ld_mul, ld_gate;
+  const float* row_table;
+  const int32_t* row_n;
+  int64_t ld_table;
+  int n_max, groups;
   int64_t M, N, ldc;
   float* C;
   float* partial;        // [splits][M][N] when splits > 1
@@ -36,9 +40,16 @@ struct GemmDev {
 };
 
 __device__ __forceinline__ float apply_epilogue(const GemmDev& g, float v, int64_t i, int64_t j) {
+  if (g.flags & GSC_EPI_ROWTABLE) v += g.row_table[(int64_t)g.row_n[i] * g.ld_table + j];
   if (g.flags & GSC_EPI_BIAS) v += g.bias[j];
   if (g.flags & GSC_EPI_RELU) v = fmaxf(v, 0.f);
   if (g.flags & GSC_EPI_MUL) v *= g.mul[i * g.ld_mul + j];
+  if (g.flags & GSC_EPI_SMASK) {
+    const int nb = g.row_n[i];
+    const uint32_t ju = (uint32_t)j;            // N < 2^31 is checked on entry
+    const int src = (int)(ju / ((uint32_t)g.groups * (uint32_t)g.n_max)), dst = (int)(ju % (uint32_t)g.n_max);
+    v = (src < nb && dst < nb) ? v : 0.f;
+  }
   if (g.flags & GSC_EPI_GATE) v = g.gate[i * g.ld_gate + j] > 0.f ? v : 0.f;
   if (g.flags & GSC_EPI_CLAMP1) v = fminf(fmaxf(v, -1.f), 1.f);
   return v;
@@ -235,6 +246,10 @@ extern "C" int gsc_gemm(const gsc_gemm_args* a, int64_t M, int64_t N, float* C, 
   }
   g.num_seg = a->num_seg; g.flags = a->flags;
   g.bias = a->bias; g.mul = a->mul; g.gate = a->gate; g.ld_mul = a->ld_mul; g.ld_gate = a->ld_gate;
+  g.row_table = a->row_table; g.row_n = a->row_n; g.ld_table = a->ld_table; g.n_max = a->n_max; g.groups = a->groups;
+  GSC_REQUIRE(!(g.flags & GSC_EPI_ROWTABLE) || (g.row_table && g.row_n), "gsc_gemm: GSC_EPI_ROWTABLE without table/row_n");
+  GSC_REQUIRE(!(g.flags & GSC_EPI_SMASK) || (g.row_n && g.n_max > 0 && g.groups > 0), "gsc_gemm: GSC_EPI_SMASK without row_n/shape");
+  GSC_REQUIRE(!(g.flags & GSC_EPI_SMASK) || N < (int64_t)1 << 31, "gsc_gemm: GSC_EPI_SMASK needs N < 2^31");
   GSC_REQUIRE(!(g.flags & GSC_EPI_BIAS) || g.bias, "gsc_gemm: GSC_EPI_BIAS without bias");
   GSC_REQUIRE(!(g.flags & GSC_EPI_MUL) || g.mul, "gsc_gemm: GSC_EPI_MUL without mul");
   GSC_REQUIRE(!(g.flags & GSC_EPI_GATE) || g.gate, "gsc_gemm: GSC_EPI_GATE without gate");

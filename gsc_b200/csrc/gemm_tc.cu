@@ -41,6 +41,10 @@ struct TcParams {
   const float* bias;
   const float* mul;
   const float* gate;
+  const float* row_table;
+  const int32_t* row_n;
+  int64_t ld_table;
+  int n_max, groups;
   int flags, num_seg;
   int kb_end[3];          // exclusive prefix of 32-wide k-blocks per segment
   int kb_total, kb_per_split, splits, tiles_m, tiles_n;
@@ -48,10 +52,38 @@ struct TcParams {
   int epi_kind;           // operand streamed in by TMA for the epilogue: 0 none, 1 mul, 2 gate
 };
 
+__device__ __forceinline__ float smask_apply(const TcParams& p, float v, int nb, int64_t j) {
+  const uint32_t ju = (uint32_t)j;
+  const int src = (int)(ju / ((uint32_t)p.groups * (uint32_t)p.n_max)), dst = (int)(ju % (uint32_t)p.n_max);
+  return (src < nb && dst < nb) ? v : 0.f;
+}
+
+// Walks consecutive columns of one row of the structured mask without a division per element:
+// column k = (src*G + g)*n_max + dst is inside the mask of an nb-node state iff src < nb && dst < nb.
+struct SmaskWalk {
+  int src, rem, dst, gn, nm;
+  __device__ __forceinline__ void seek(const TcParams& p, int64_t col) {
+    nm = p.n_max;
+    gn = p.groups * p.n_max;
+    const uint32_t c = (uint32_t)col;
+    src = (int)(c / (uint32_t)gn);
+    rem = (int)(c - (uint32_t)src * (uint32_t)gn);
+    dst = (int)((uint32_t)rem % (uint32_t)nm);
+  }
+  __device__ __forceinline__ bool next(int nb) {
+    const bool in = src < nb && dst < nb;
+    if (++dst == nm) dst = 0;
+    if (++rem == gn) { rem = 0; ++src; }
+    return in;
+  }
+};
+
 __device__ __forceinline__ float tc_epilogue(const TcParams& p, float v, int64_t i, int64_t j) {
+  if (p.flags & GSC_EPI_ROWTABLE) v += p.row_table[(int64_t)p.row_n[i] * p.ld_table + j];
   if (p.flags & GSC_EPI_BIAS) v += p.bias[j];
   if (p.flags & GSC_EPI_RELU) v = fmaxf(v, 0.f);
   if (p.flags & GSC_EPI_MUL) v *= p.mul[i * p.ld_mul + j];
+  if (p.flags & GSC_EPI_SMASK) v = smask_apply(p, v, p.row_n[i], j);
   if (p.flags & GSC_EPI_GATE) v = p.gate[i * p.ld_gate + j] > 0.f ? v : 0.f;
   if (p.flags & GSC_EPI_CLAMP1) v = fminf(fmaxf(v, -1.f), 1.f);
   return v;
@@ -203,12 +235,15 @@ gemm_tc_kernel(const __grid_constant__ TcParams p, const __grid_constant__ CUten
         if (p.epi_kind) mbar_wait(efull_bar, (uint32_t)iter & 1u);
         const int lrow = quad * 32 + lane;
         const int64_t grow = (int64_t)it.m0 + lrow;
+        const int nb = ((p.flags & (GSC_EPI_ROWTABLE | GSC_EPI_SMASK)) && grow < p.M) ? p.row_n[grow] : 0;
 #pragma unroll 1
         for (int c = 0; c < kTcBN / 32; ++c) {
           float v[32];
           tc_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(as * kTcBN + c * 32), v);
           const uint32_t rbase = ebuf + c * 16384 + lrow * 128;
           const int64_t col0 = (int64_t)it.n0 + c * 32;
+          SmaskWalk walk;
+          if (p.flags & GSC_EPI_SMASK) walk.seek(p, col0);
 #pragma unroll
           for (int q = 0; q < 8; ++q) {
             const uint32_t addr = rbase + (uint32_t)((q ^ (lrow & 7)) << 4);          // 128 B swizzle
@@ -220,9 +255,11 @@ gemm_tc_kernel(const __grid_constant__ TcParams p, const __grid_constant__ CUten
             for (int u = 0; u < 4; ++u) {
               const int64_t col = col0 + 4 * q + u;
               float t = o[u];
+              if ((p.flags & GSC_EPI_ROWTABLE) && col < p.N) t += p.row_table[(int64_t)nb * p.ld_table + col];
               if ((p.flags & GSC_EPI_BIAS) && col < p.N) t += p.bias[col];
               if (p.flags & GSC_EPI_RELU) t = fmaxf(t, 0.f);
               if (p.epi_kind == 1) t *= ev[u];
+              if (p.flags & GSC_EPI_SMASK) t = walk.next(nb) ? t : 0.f;
               if (p.flags & GSC_EPI_GATE) {
                 if (p.epi_kind == 2) t = ev[u] > 0.f ? t : 0.f;
                 else if (grow < p.M && col < p.N) t = p.gate[grow * p.ld_gate + col] > 0.f ? t : 0.f;
@@ -389,6 +426,7 @@ int gemm_tc_launch(const gsc_gemm_args* a, int64_t M, int64_t N, float* C, int64
   for (int s = a->num_seg; s < 3; ++s) { maps[s] = maps[0]; maps[3 + s] = maps[3]; p.kb_end[s] = kb; }
   p.M = M; p.N = N; p.ldc = ldc; p.C = C; p.flags = a->flags; p.num_seg = a->num_seg;
   p.bias = a->bias; p.mul = a->mul; p.gate = a->gate; p.ld_mul = a->ld_mul; p.ld_gate = a->ld_gate;
+  p.row_table = a->row_table; p.row_n = a->row_n; p.ld_table = a->ld_table; p.n_max = a->n_max; p.groups = a->groups;
   p.kb_total = kb;
   p.tiles_m = (int)ceil_div(M, kTcBM);
   p.tiles_n = (int)ceil_div(N, kTcBN);

@@ -57,7 +57,7 @@ class DDPGUpdater:
         B = cur.num_graphs
         scale = 1.0 / (B * self.world_size)
         ta, tq, q = self.target_actor, self.qf1_target, self.qf1
-        a2, _ = net_forward(ta, ta.flat, nxt, None, save=False, out_mul=nxt.mask, clamp1=True)
+        a2, _ = net_forward(ta, ta.flat, nxt, None, save=False, mask_output=True, clamp1=True)
         q2, _ = net_forward(tq, tq.flat, nxt, a2, save=False)
         qv, ctx = net_forward(q, q.flat, cur, actions, save=True)
         _, dq, loss = ops.td_mse(rewards, dones, q2, qv, self.gamma, scale)
@@ -74,14 +74,14 @@ class DDPGUpdater:
         B = cur.num_graphs
         scale = 1.0 / (B * self.world_size)
         ac, q, ta = self.actor, self.qf1, self.target_actor
-        a, ctx_a = net_forward(ac, ac.flat, cur, None, save=True, out_mul=cur.mask)
+        a, ctx_a = net_forward(ac, ac.flat, cur, None, save=True, mask_output=True)
         q_pi, ctx_q = net_forward(q, q.flat, cur, a, save=True, save_gnn=False)
         if self._neg is None or self._neg.shape[0] != B or float(self._neg_scale) != scale:
             self._neg = torch.full((B, 1), -scale, dtype=torch.float32, device=a.device)
             self._neg_scale = scale
         # d(-mean q)/dq = -1/B_global ; back through the critic into the action, times mask
         dz = net_backward(q, q.flat, cur, ctx_q, self._neg, None, want_action_grad=True,
-                          action_grad_mul=cur.mask)
+                          action_grad_masked=True)
         net_backward(ac, ac.flat, cur, ctx_a, dz, self.g_actor)
         self._allreduce(self.g_actor)
         self.step_actor += 1
@@ -112,10 +112,13 @@ class GraphedUpdate:
     def __init__(self, upd: DDPGUpdater, cur: GraphBatch, nxt: GraphBatch, actions, rewards, dones,
                  warmup: int = 2):
         self.upd = upd
+        cl = lambda t: None if t is None else t.clone()
         mk = lambda gb, share=None: GraphBatch(
             gb.x.clone(), gb.edge_index.clone() if share is None else share.edge_index,
             gb.batch.clone() if share is None else share.batch,
-            gb.mask.clone() if share is None else share.mask, gb.num_graphs, gb.max_nodes)
+            (cl(gb._mask) if not gb.structured else None) if share is None else share._mask,
+            gb.num_graphs, gb.max_nodes, None,
+            cl(gb.n_nodes) if share is None else share.n_nodes, gb.n_max, gb.groups)
         self.cur = mk(cur)
         self.nxt = mk(nxt, self.cur if nxt.edge_index is cur.edge_index else None)
         self.actions, self.rewards, self.dones = actions.clone(), rewards.clone(), dones.clone()
@@ -144,8 +147,7 @@ class GraphedUpdate:
         restore()
 
     def _run(self):
-        fresh = lambda gb: GraphBatch(gb.x, gb.edge_index, gb.batch, gb.mask, gb.num_graphs, gb.max_nodes)
-        return self.upd.update(fresh(self.cur), fresh(self.nxt), self.actions, self.rewards, self.dones)
+        return self.upd.update(self.cur.view(), self.nxt.view(), self.actions, self.rewards, self.dones)
 
     def load(self, cur: GraphBatch, nxt: GraphBatch, actions, rewards, dones, non_blocking: bool = True):
         """Copy a minibatch (host or device tensors of the captured shapes) into the static inputs."""
@@ -153,12 +155,18 @@ class GraphedUpdate:
         self.cur.x.copy_(cur.x, non_blocking=nb)
         self.cur.edge_index.copy_(cur.edge_index, non_blocking=nb)
         self.cur.batch.copy_(cur.batch, non_blocking=nb)
-        self.cur.mask.copy_(cur.mask, non_blocking=nb)
+        if self.cur.structured:
+            self.cur.n_nodes.copy_(cur.n_nodes, non_blocking=nb)
+        else:
+            self.cur._mask.copy_(cur.mask, non_blocking=nb)
         self.nxt.x.copy_(nxt.x, non_blocking=nb)
         if self.nxt.edge_index is not self.cur.edge_index:
             self.nxt.edge_index.copy_(nxt.edge_index, non_blocking=nb)
             self.nxt.batch.copy_(nxt.batch, non_blocking=nb)
-            self.nxt.mask.copy_(nxt.mask, non_blocking=nb)
+            if self.nxt.structured:
+                self.nxt.n_nodes.copy_(nxt.n_nodes, non_blocking=nb)
+            else:
+                self.nxt._mask.copy_(nxt.mask, non_blocking=nb)
         self.actions.copy_(actions, non_blocking=nb)
         self.rewards.copy_(rewards, non_blocking=nb)
         self.dones.copy_(dones, non_blocking=nb)
@@ -176,7 +184,7 @@ class GraphedUpdate:
 def predict(actor: Actor, obs) -> torch.Tensor:
     """reference SimpleDDPG.predict (simple_ddpg.py:331-336) / inference.predict (inference.py:11-15)."""
     gb = GraphBatch.wrap(obs)
-    y, _ = net_forward(actor, actor._check_flat(), gb, None, save=False, out_mul=gb.mask)
+    y, _ = net_forward(actor, actor._check_flat(), gb, None, save=False, mask_output=True)
     return y
 
 

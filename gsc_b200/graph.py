@@ -59,12 +59,39 @@ class GraphBatch:
     src/rlsp/agents/buffer.py:65-81) plus the packed CSR used by the kernels."""
 
     def __init__(self, x, edge_index, batch, mask, num_graphs: int, max_nodes: Optional[int] = None,
-                 ptr=None):
-        self.x, self.edge_index, self.batch, self.mask = x, edge_index, batch, mask
+                 ptr=None, n_nodes=None, n_max: Optional[int] = None, groups: Optional[int] = None):
+        self.x, self.edge_index, self.batch = x, edge_index, batch
+        self._mask = mask
         self.ptr = ptr
         self.num_graphs = int(num_graphs)
         self.max_nodes = None if max_nodes is None else int(max_nodes)
+        # Structured mask: when the per-state node counts are known, mask[b] is mask[:n_b,:,:,:n_b] = 1
+        # over the scheduling shape (n_max, groups, n_max) and never has to be stored or read.
+        self.n_nodes = n_nodes            # int32 [B] on the same device as x, or None
+        self.n_max = None if n_max is None else int(n_max)
+        self.groups = None if groups is None else int(groups)
         self._csr = None
+
+    @property
+    def structured(self) -> bool:
+        return self.n_nodes is not None and self.n_max is not None and self.groups is not None
+
+    @property
+    def mask(self):
+        """Dense [B, A] mask; generated on the device from ``n_nodes`` on first use if not given."""
+        if self._mask is None and self.structured and self.n_nodes.is_cuda:
+            from . import ops
+            self._mask = ops.build_mask(self.n_nodes, self.n_max, self.groups)
+        return self._mask
+
+    @mask.setter
+    def mask(self, value):
+        self._mask = value
+
+    def view(self) -> "GraphBatch":
+        """Same tensors, no cached CSR (the packer runs again: used to time it as part of a step)."""
+        return GraphBatch(self.x, self.edge_index, self.batch, self._mask, self.num_graphs, self.max_nodes,
+                          self.ptr, self.n_nodes, self.n_max, self.groups)
 
     # ---- construction -----------------------------------------------------------------------
     @staticmethod
@@ -89,21 +116,26 @@ class GraphBatch:
                           max(sizes) if sizes else 0, ptr)
 
     @staticmethod
-    def from_arrays(x, edge_index, batch, mask, num_graphs, max_nodes=None, ptr=None, pin=False):
+    def from_arrays(x, edge_index, batch, mask, num_graphs, max_nodes=None, ptr=None, pin=False,
+                    n_nodes=None, n_max=None, groups=None):
         def conv(a, dt):
             if a is None:
                 return None
             t = _t(a, dt)
             return t.pin_memory() if pin and not t.is_cuda else t
         return GraphBatch(conv(x, torch.float32), conv(edge_index, torch.int64), conv(batch, torch.int64),
-                          conv(mask, torch.float32), num_graphs, max_nodes, conv(ptr, torch.int64))
+                          conv(mask, torch.float32), num_graphs, max_nodes, conv(ptr, torch.int64),
+                          conv(n_nodes, torch.int32), n_max, groups)
 
     @staticmethod
-    def from_states(states, pin: bool = False) -> "GraphBatch":
-        """From a ``gsc_b200.synth.StateBatch``."""
-        return GraphBatch.from_arrays(states.x, states.edge_index, states.batch, states.mask,
+    def from_states(states, pin: bool = False, dense_mask: bool = True) -> "GraphBatch":
+        """From a ``gsc_b200.synth.StateBatch`` (carries the node counts, so the mask is structured;
+        ``dense_mask=False`` leaves the [B, A] mask to be generated on the device when needed)."""
+        return GraphBatch.from_arrays(states.x, states.edge_index, states.batch,
+                                      states.mask if dense_mask else None,
                                       states.num_graphs, int(states.n.max()) if len(states.n) else 0,
-                                      states.ptr, pin=pin)
+                                      states.ptr, pin=pin, n_nodes=states.n, n_max=states.n_max,
+                                      groups=states.num_sfcs * states.num_sfs)
 
     @staticmethod
     def wrap(obs) -> "GraphBatch":
@@ -141,8 +173,8 @@ class GraphBatch:
         if self.x.device == device:
             return self
         mv = lambda t: None if t is None else t.to(device, non_blocking=non_blocking)
-        gb = GraphBatch(mv(self.x), mv(self.edge_index), mv(self.batch), mv(self.mask),
-                        self.num_graphs, self.max_nodes, mv(self.ptr))
+        gb = GraphBatch(mv(self.x), mv(self.edge_index), mv(self.batch), mv(self._mask),
+                        self.num_graphs, self.max_nodes, mv(self.ptr), mv(self.n_nodes), self.n_max, self.groups)
         return gb
 
     # ---- CUDA path --------------------------------------------------------------------------

@@ -269,61 +269,91 @@ class _FlatNet(nn.Module):
 # ------------------------------------------------------------------------------------------------
 # Functional forward / backward shared by the autograd Functions and the fused DDPG updater
 # ------------------------------------------------------------------------------------------------
+def _structured(gb: GraphBatch) -> bool:
+    return ops.use_structured_mask and gb.structured and gb.n_nodes.is_cuda
+
+
 def net_forward(net: _FlatNet, flat: torch.Tensor, gb: GraphBatch, action: Optional[torch.Tensor],
-                save: bool, out_mul: Optional[torch.Tensor] = None, clamp1: bool = False,
+                save: bool, mask_output: bool = False, clamp1: bool = False,
                 save_gnn: Optional[bool] = None):
-    """emb = GNN(gb); z = MLP(cat[emb, mask(, action)]); returns (z [* out_mul] [clamped], ctx).
+    """emb = GNN(gb); z = MLP(cat[emb, mask(, action)]); returns (z [* mask] [clamped], ctx).
 
     ``save`` keeps what ``net_backward`` needs; ``save_gnn=False`` skips the embedder activations
     when only the gradient w.r.t. the action input will be asked for.  The embedding is written
     straight into a ``[B, pad + H]`` buffer whose leading ``pad`` columns are zero and line up with
-    the pad columns of the first weight, so every K-segment of the first layer is 16-byte aligned."""
+    the pad columns of the first weight, so every K-segment of the first layer is 16-byte aligned.
+
+    When the batch carries its node counts (``gb.structured``) the mask is never read: its column
+    block of the first layer becomes a per-``n`` table lookup and the output mask is computed from
+    ``n`` in the GEMM epilogue."""
     gnn, lins = net.views(flat)
     H = net.embedder.hidden_dim
     pad0 = lins[0][3]
+    st = _structured(gb)
     embp = torch.zeros(gb.num_graphs, pad0 + H, dtype=torch.float32, device=flat.device)
     rowptr, col, gptr = gb.csr()
     _, saved = ops.gnn_embed_fwd(gb.x, rowptr, col, gptr, gb.num_graphs, gb.max_nodes, gnn, H,
                                  net.embedder.num_layers, net.embedder.num_iter,
                                  save=save if save_gnn is None else save_gnn, out=embp[:, pad0:])
-    inputs = [embp, gb.mask] + ([action] if action is not None else [])
+    A = net.action_dim
+    smask = (gb.n_nodes, gb.n_max, gb.groups) if st else None
+    inputs = [embp, None if st else gb.mask] + ([action] if action is not None else [])
     hs = []
     h = None
     n = len(lins)
     for i, (W, b, Wp, pad) in enumerate(lins):
         last = i == n - 1
-        h = ops.linear_fwd(inputs if i == 0 else [h], Wp if i == 0 else W, b, relu=not last,
-                           mul=out_mul if last else None, clamp1=clamp1 and last)
+        out_mul = gb.mask if (mask_output and last and not st) else None
+        out_smask = smask if (mask_output and last and st) else None
+        if i == 0 and st:
+            table = ops.mask_table(Wp[:, pad + H:pad + H + A], gb.n_max, gb.groups)
+            ins = [embp] + ([action] if action is not None else [])
+            offs = [0] + ([pad + H + A] if action is not None else [])
+            h = ops.linear_fwd(ins, Wp, b, relu=not last, mul=out_mul, clamp1=clamp1 and last,
+                               col_offsets=offs, row_table=(table, gb.n_nodes), smask=out_smask)
+        else:
+            h = ops.linear_fwd(inputs if i == 0 else [h], Wp if i == 0 else W, b, relu=not last,
+                               mul=out_mul, clamp1=clamp1 and last, smask=out_smask)
         if not last:
             hs.append(h)
-    ctx = (embp, saved, inputs, hs) if save else None
+    ctx = (embp, saved, inputs, hs, st) if save else None
     return h, ctx
 
 
 def net_backward(net: _FlatNet, flat: torch.Tensor, gb: GraphBatch, ctx, dz: torch.Tensor,
                  grad_flat: Optional[torch.Tensor], want_action_grad: bool = False,
-                 action_grad_mul: Optional[torch.Tensor] = None):
+                 action_grad_masked: bool = False):
     """Back-propagate ``dz`` (gradient w.r.t. the pre-mask MLP output).
 
     Writes parameter gradients into ``grad_flat`` (same layout as ``flat``) unless it is None, and
-    returns the gradient w.r.t. the action input (times ``action_grad_mul``) when requested."""
-    embp, saved, inputs, hs = ctx
+    returns the gradient w.r.t. the action input (times the mask if ``action_grad_masked``) when
+    requested."""
+    embp, saved, inputs, hs, st = ctx
     gnn, lins = net.views(flat)
     g_gnn, g_lins = net.views(grad_flat) if grad_flat is not None else (None, None)
     H = net.embedder.hidden_dim
+    A = net.action_dim
     d_action = None
     d = dz
     for i in range(len(lins) - 1, -1, -1):
         W, _, Wp, pad = lins[i]
         if grad_flat is not None:
-            ops.linear_wgrad(d, inputs if i == 0 else [hs[i - 1]], g_lins[i][2] if i == 0 else g_lins[i][0])
+            if i == 0 and st:
+                gWp = g_lins[0][2]
+                ops.linear_wgrad(d, [embp], gWp[:, :pad + H])
+                ops.mask_wgrad(d, gb.n_nodes, gb.n_max, gb.groups, gWp[:, pad + H:pad + H + A])
+                if len(inputs) > 2:
+                    ops.linear_wgrad(d, [inputs[2]], gWp[:, pad + H + A:pad + H + 2 * A])
+            else:
+                ops.linear_wgrad(d, inputs if i == 0 else [hs[i - 1]], g_lins[i][2] if i == 0 else g_lins[i][0])
             ops.colsum(d, out=g_lins[i][1])
         if i > 0:
             d = ops.linear_dgrad(d, W, 0, int(W.shape[1]), gate=hs[i - 1])
         else:
             if want_action_grad:
-                A = int(inputs[2].shape[1])
-                d_action = ops.linear_dgrad(d, Wp, pad + H + int(inputs[1].shape[1]), A, mul=action_grad_mul)
+                mul = gb.mask if (action_grad_masked and not st) else None
+                sm = (gb.n_nodes, gb.n_max, gb.groups) if (action_grad_masked and st) else None
+                d_action = ops.linear_dgrad(d, Wp, pad + H + A, A, mul=mul, smask=sm)
             if grad_flat is not None:
                 d_embp = ops.linear_dgrad(d, Wp, 0, pad + H)
                 rowptr, col, gptr = gb.csr()
@@ -340,8 +370,7 @@ class _NetFn(torch.autograd.Function):
     def forward(ctx, net: _FlatNet, gb: GraphBatch, action, apply_mask: bool, *params):
         flat = net._check_flat()
         need = any(ctx.needs_input_grad)
-        z, saved_ctx = net_forward(net, flat, gb, action, save=need,
-                                   out_mul=gb.mask if apply_mask else None,
+        z, saved_ctx = net_forward(net, flat, gb, action, save=need, mask_output=apply_mask,
                                    save_gnn=need and any(ctx.needs_input_grad[4:]))
         ctx.net, ctx.gb, ctx.saved_ctx, ctx.apply_mask = net, gb, saved_ctx, apply_mask
         ctx.has_action = action is not None

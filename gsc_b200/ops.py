@@ -20,6 +20,8 @@ launch_count = 0          # kernels enqueued through this module (bench.py repor
 # TMA-mappable.  Tolerances of the two modes are stated separately in tests/ and DESIGN.md.
 precision = "fp32"
 EPI_TF32 = 32
+# Use the node counts instead of the dense mask whenever a batch carries them (GraphBatch.structured).
+use_structured_mask = True
 
 
 class use_precision:
@@ -263,8 +265,10 @@ def gnn_embed_bwd(x, rowptr, col, graph_ptr, num_graphs: int, max_nodes: int, pa
 
 # ---------------------------------------------------------------------------------------------
 def gemm_raw(segs: Sequence[tuple], M: int, N: int, out: torch.Tensor, flags: int = 0,
-             bias=None, mul=None, gate=None, tag: str = "gemm"):
-    """segs: (A_tensor, a_rs, a_cs, B_tensor, b_rs, b_cs, K) with A/B giving the base pointers."""
+             bias=None, mul=None, gate=None, tag: str = "gemm", row_table=None, smask=None):
+    """segs: (A_tensor, a_rs, a_cs, B_tensor, b_rs, b_cs, K) with A/B giving the base pointers.
+    ``row_table``: (table [n_max+1, N], row_n int32 [M]) adds table[row_n[i]] to row i;
+    ``smask``: (row_n, n_max, groups) zeroes the columns outside the structured mask of row i."""
     lib = _lib.load()
     args = GemmArgs()
     ktot = 0
@@ -281,9 +285,18 @@ def gemm_raw(segs: Sequence[tuple], M: int, N: int, out: torch.Tensor, flags: in
         args.mul, args.ld_mul = mul.data_ptr(), _ld(mul)
     if gate is not None:
         args.gate, args.ld_gate = gate.data_ptr(), _ld(gate)
+    if row_table is not None:
+        table, row_n = row_table
+        args.row_table, args.ld_table, args.row_n = table.data_ptr(), _ld(table), row_n.data_ptr()
+        args.flags |= _lib.EPI_ROWTABLE
+    if smask is not None:
+        row_n, n_max, groups = smask
+        args.row_n, args.n_max, args.groups = row_n.data_ptr(), n_max, groups
+        args.flags |= _lib.EPI_SMASK
     need = lib.gsc_gemm_workspace_bytes(M, N, ktot)
     ws, wsn = workspace(need, out.device, "gemm")
-    with _Timed(f"{tag}[{M}x{N}x{ktot}{'+m' if mul is not None else ''}{'+g' if gate is not None else ''}]"):
+    with _Timed(f"{tag}[{M}x{N}x{ktot}{'+m' if mul is not None else ''}{'+g' if gate is not None else ''}]"
+                + ("T" if row_table is not None else "") + ("S" if smask is not None else "")):
         check(lib.gsc_gemm(args, M, N, out.data_ptr(), _ld(out), _ptr(ws), wsn, _stream()), "gsc_gemm")
     _count(2 if need else 1)
     return out
@@ -291,31 +304,36 @@ def gemm_raw(segs: Sequence[tuple], M: int, N: int, out: torch.Tensor, flags: in
 
 def linear_fwd(inputs: List[torch.Tensor], weight: torch.Tensor, bias: Optional[torch.Tensor],
                relu: bool = False, mul: Optional[torch.Tensor] = None, clamp1: bool = False,
-               out: Optional[torch.Tensor] = None) -> torch.Tensor:
+               out: Optional[torch.Tensor] = None, col_offsets: Optional[Sequence[int]] = None,
+               row_table=None, smask=None) -> torch.Tensor:
     """act(cat(inputs, 1) @ weight.T + bias) [* mul] without materialising the concatenation.
 
-    weight: [N, sum K_s] fp32, may be a strided row view (its row stride is used)."""
+    weight: [N, sum K_s] fp32, may be a strided row view (its row stride is used).
+    ``col_offsets`` places input s at weight columns [col_offsets[s], +K_s) instead of back to back
+    (used when the mask column block is replaced by ``row_table``)."""
     weight = _row_major(weight, "linear_fwd weight")
     M, N = int(inputs[0].shape[0]), int(weight.shape[0])
     ldw = _ld(weight)
     segs, off = [], 0
-    for x in inputs:
+    for si, x in enumerate(inputs):
         x = _row_major(x, "linear_fwd input")
         K = int(x.shape[1])
+        if col_offsets is not None:
+            off = int(col_offsets[si])
         segs.append((x, _ld(x), 1, weight[:, off:], 1, ldw, K))
         off += K
-    if off != weight.shape[1]:
+    if col_offsets is None and off != weight.shape[1]:
         raise _lib.GscError(f"linear_fwd: inputs have {off} columns, weight expects {weight.shape[1]}")
     if out is None:
         out = torch.empty(M, N, dtype=torch.float32, device=weight.device)
     flags = (EPI_BIAS if bias is not None else 0) | (EPI_RELU if relu else 0) | \
             (EPI_MUL if mul is not None else 0) | (EPI_CLAMP1 if clamp1 else 0)
-    return gemm_raw(segs, M, N, out, flags, bias=bias, mul=mul, tag="linear_fwd")
+    return gemm_raw(segs, M, N, out, flags, bias=bias, mul=mul, tag="linear_fwd", row_table=row_table, smask=smask)
 
 
 def linear_dgrad(dY: torch.Tensor, weight: torch.Tensor, col_off: int, K: int,
                  mul: Optional[torch.Tensor] = None, gate: Optional[torch.Tensor] = None,
-                 out: Optional[torch.Tensor] = None) -> torch.Tensor:
+                 out: Optional[torch.Tensor] = None, smask=None) -> torch.Tensor:
     """dX[M, K] = dY[M, N] @ weight[:, col_off:col_off+K]  (* mul) (gated by gate > 0)."""
     dY = _row_major(dY, "linear_dgrad dY")
     weight = _row_major(weight, "linear_dgrad weight")
@@ -324,7 +342,7 @@ def linear_dgrad(dY: torch.Tensor, weight: torch.Tensor, col_off: int, K: int,
         out = torch.empty(M, K, dtype=torch.float32, device=dY.device)
     flags = (EPI_MUL if mul is not None else 0) | (EPI_GATE if gate is not None else 0)
     seg = (dY, _ld(dY), 1, weight[:, col_off:], _ld(weight), 1, N)
-    return gemm_raw([seg], M, K, out, flags, mul=mul, gate=gate, tag="linear_dgrad")
+    return gemm_raw([seg], M, K, out, flags, mul=mul, gate=gate, tag="linear_dgrad", smask=smask)
 
 
 def linear_wgrad(dY: torch.Tensor, inputs: List[torch.Tensor], dW: torch.Tensor) -> torch.Tensor:
@@ -351,6 +369,33 @@ def mul_gate(x: torch.Tensor, mul: Optional[torch.Tensor] = None, gate: Optional
                                    int(x.shape[1]), _ptr(out), _ld(out), _stream()), "gsc_mul_gate")
     _count(1)
     return out
+
+
+def mask_table(w_mask: torch.Tensor, n_max: int, groups: int) -> torch.Tensor:
+    """table[n, o] = sum of ``w_mask[o, k]`` over the columns the structured mask of an n-node state
+    selects; ``w_mask`` is the mask column block [N1, n_max*groups*n_max] of a first-layer weight."""
+    w_mask = _row_major(w_mask, "mask_table weight")
+    N1 = int(w_mask.shape[0])
+    table = torch.empty(n_max + 1, N1, dtype=torch.float32, device=w_mask.device)
+    with _Timed(f"mask_table[{N1}x{int(w_mask.shape[1])}]"):
+        check(_lib.load().gsc_mask_table(_ptr(w_mask), _ld(w_mask), N1, n_max, groups, _ptr(table), N1, _stream()),
+              "gsc_mask_table")
+    _count(1)
+    return table
+
+
+def mask_wgrad(dY: torch.Tensor, n_nodes: torch.Tensor, n_max: int, groups: int, dW: torch.Tensor) -> torch.Tensor:
+    """dW[o, k] = sum over {b: k in mask(n_b)} dY[b, o], written into the mask column block ``dW``."""
+    dY = _row_major(dY, "mask_wgrad dY")
+    dW = _row_major(dW, "mask_wgrad dW")
+    lib = _lib.load()
+    N1 = int(dY.shape[1])
+    ws, wsn = workspace(lib.gsc_mask_wgrad_workspace_bytes(N1, n_max), dY.device, "mask_wgrad")
+    with _Timed(f"mask_wgrad[{N1}x{int(dW.shape[1])}]"):
+        check(lib.gsc_mask_wgrad(_ptr(dY), _ld(dY), _ptr(n_nodes), int(dY.shape[0]), N1, n_max, groups, _ptr(dW),
+                                 _ld(dW), _ptr(ws), wsn, _stream()), "gsc_mask_wgrad")
+    _count(2)
+    return dW
 
 
 def colsum(X: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:

@@ -29,12 +29,15 @@ extern "C" {
 #define GSC_MAX_HIDDEN 32    /* GNN_features supported by the embedder kernels (reference: 22) */
 #define GSC_MAX_APPS 16      /* 1 + num_iter*(num_layers-1) GATv2 applications per forward */
 
-/* Epilogue flags of gsc_gemm (applied in this order). */
+/* Epilogue flags of gsc_gemm (applied in the order: ROWTABLE, BIAS, RELU, MUL, SMASK, GATE, CLAMP1). */
 #define GSC_EPI_BIAS 1       /* v += bias[j]                                  */
 #define GSC_EPI_RELU 2       /* v = max(v, 0)                                 */
 #define GSC_EPI_MUL 4        /* v *= mul[i, j]     (mask product)             */
 #define GSC_EPI_GATE 8       /* v = gate[i, j] > 0 ? v : 0  (ReLU backward)   */
 #define GSC_EPI_CLAMP1 16    /* v = min(max(v, -1), 1)                        */
+#define GSC_EPI_ROWTABLE 64  /* v += row_table[row_n[i], j]  (structured-mask block of layer 1) */
+#define GSC_EPI_SMASK 128    /* v = 0 unless src(j) < row_n[i] and dst(j) < row_n[i]: the structured
+                                mask[:n,:,:,:n] computed from n instead of read; j = (src*G+g)*N+dst */
 #define GSC_EPI_TF32 32      /* allow the tensor-core path: tcgen05 kind::tf32, fp32 accumulate.
                                 Without it the GEMM is exact fp32 (FMA).  Falls back to fp32 when
                                 the operands are not TMA-mappable (16 B bases, strides % 4 floats). */
@@ -148,11 +151,25 @@ typedef struct {
   int64_t ld_mul;
   const float* gate;     /* [M, ld_gate] */
   int64_t ld_gate;
+  const float* row_table;   /* [n_max + 1, ld_table]  (GSC_EPI_ROWTABLE)                 */
+  int64_t ld_table;
+  const int32_t* row_n;     /* [M] node count of the state in row i (ROWTABLE, SMASK)    */
+  int32_t n_max, groups;    /* scheduling shape (N_max, G, N_max) of the SMASK columns   */
 } gsc_gemm_args;
 
 size_t gsc_gemm_workspace_bytes(int64_t M, int64_t N, int64_t K_total);
 int gsc_gemm(const gsc_gemm_args* args, int64_t M, int64_t N, float* C, int64_t ldc,
              void* workspace, size_t workspace_bytes, void* stream);
+
+/* Structured-mask block of the first dense layer (see GSC_EPI_ROWTABLE): table[n, o] = sum of
+ * W[o, k] over the columns k that mask(n) selects, for n = 0..n_max; W is the mask column block
+ * [N1, n_max*G*n_max] of the layer's weight (row stride ldw). */
+int gsc_mask_table(const float* W, int64_t ldw, int64_t N1, int n_max, int groups, float* table,
+                   int64_t ld_table, void* stream);
+/* Its weight gradient dW[o, k] = sum over {b: k in mask(n_b)} dY[b, o], written in W's layout. */
+size_t gsc_mask_wgrad_workspace_bytes(int64_t N1, int n_max);
+int gsc_mask_wgrad(const float* dY, int64_t ldy, const int32_t* n, int64_t B, int64_t N1, int n_max,
+                   int groups, float* dW, int64_t ldw, void* workspace, size_t workspace_bytes, void* stream);
 
 /* out = x * mul (if mul != NULL), zeroed where gate <= 0 (if gate != NULL): the mask product of
  * Actor.forward (reference src/rlsp/agents/models.py:153) and ReLU backward, for callers that hold

@@ -174,10 +174,10 @@ def test_cuda_graph_replay_equals_eager_updates():
     assert torch.equal(nets_e[0].flat, nets_g[0].flat)
     graphed = ddpg.GraphedUpdate(upd_g, cur, nxt, t(actions), t(rewards), t(dones))
     assert torch.equal(nets_e[0].flat, nets_g[0].flat), "capture must not change the weights"
-    fresh = lambda gb: GraphBatch(gb.x, gb.edge_index, gb.batch, gb.mask, gb.num_graphs, gb.max_nodes)
+    fresh = lambda gb: gb.view()
     for step in range(3):
-        x2 = torch.rand_like(cur.x)                              # a new minibatch each step
-        cur_k = GraphBatch(x2, cur.edge_index, cur.batch, cur.mask, cur.num_graphs, cur.max_nodes)
+        cur_k = cur.view()
+        cur_k.x = torch.rand_like(cur.x)                         # a new minibatch each step
         qe, le, ae = upd_e.update(cur_k, fresh(nxt), t(actions), t(rewards) + step, t(dones))
         graphed.load(cur_k, nxt, t(actions), t(rewards) + step, t(dones))
         qg, lg, ag = graphed.replay()
