@@ -150,7 +150,7 @@ def run_ours(args):
         ta.load_state_dict(actor.state_dict())
         tq.load_state_dict(qf1.state_dict())
         upd = ddpg.DDPGUpdater(actor, qf1, ta, tq, lr=1e-3, gamma=0.99, tau=1e-4,
-                               world_size=world)
+                               world_size=world, rank=rank, shard_optimizer=args.shard_optimizer)
 
     def host_batch(st):
         return GraphBatch.from_states(st, pin=True, dense_mask=args.dense_mask)
@@ -361,7 +361,8 @@ def run_ours(args):
                        "cuda_graph": bool(graphed is not None),
                        "weights": "reference init (PyG glorot / torch Linear), torch.manual_seed(1234)",
                        "l2": "flushed between timed steps (256 MiB write)",
-                       "parallelism": f"dp{world}" if w["kind"] == "c3" else f"replicas{world}"},
+                       "parallelism": (f"dp{world}" + ("+sharded-optimizer" if args.shard_optimizer and world > 1 else ""))
+                       if w["kind"] == "c3" else f"replicas{world}"},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                     "ms_per_step": e2e_ms / args.steps,
                     "path": ("pinned host states -> H2D -> mask from n on device -> packer+embedder+actor -> D2H actions"
@@ -494,6 +495,8 @@ def main():
                     help="c3 (default): full DDPG update, the fwd+bwd+Adam step BASELINE.json's metric names; "
                          "c2: embedder + actor inference")
     ap.add_argument("--batch", type=int, default=0)
+    ap.add_argument("--shard-optimizer", action="store_true",
+                    help="N > 1: reduce-scatter gradients, Adam + soft update on a 1/N parameter shard, all-gather")
     ap.add_argument("--dense-mask", action="store_true",
                     help="carry the dense [B, A] mask tensor instead of the per-state node counts")
     ap.add_argument("--no-graph", dest="graph", action="store_false",

@@ -32,6 +32,7 @@ struct GnnArgs {
   float* saved;           // fwd: written (nullable); bwd: read
   const float* d_emb;     // bwd only
   float* partials;        // bwd only: [gridDim.x][param_floats]
+  float* rows_ws;         // bwd, large graphs only: [gridDim.x][5][cap][HP] node-row scratch in global memory
   float* dbg;             // optional phase timers (debug hook), nullptr in production
   const int32_t* stats;   // bwd: packer stats (stats[3] == 0 <=> symmetric graph), nullable
   int gather_kernel_launched;   // bwd: the out-edge gather kernel handles symmetric graphs
@@ -535,13 +536,17 @@ __global__ void __launch_bounds__(kGnnThreads, 2) gnn_fwd_tc_kernel(const GnnArg
 //   d_W{l,r} += d_x{l,r}_i (x) h_in_i ; d_b{l,r} += d_x{l,r}_i ; d_h_in_i = Wl^T d_xl_i + Wr^T d_xr_i
 // Weight gradients are accumulated per CTA in shared memory over all its chunks and applications,
 // written to partials[blockIdx.x][*] and summed in a fixed order by gnn_bwd_reduce_kernel.
-template <int HP>
+// kGlobalRows: graphs whose five node-row arrays do not fit in shared memory (e.g. 1000-node
+// topologies) keep them in a per-CTA slice of the workspace instead (L2-resident; the scatter then
+// uses native global float reductions).  Same code, same summation order per node.
+template <int HP, bool kGlobalRows>
 __global__ void __launch_bounds__(kGnnThreads, 1) gnn_bwd_kernel(const GnnArgs p) {
   using L = ConvLayout<HP>;
   extern __shared__ float4 smem4[];
   float* wsm = reinterpret_cast<float*>(smem4);             // weights   [num_convs][kFloats]
   float* gsm = wsm + p.num_convs * L::kFloats;              // gradients [num_convs][kFloats]
-  float* xl_s = gsm + p.num_convs * L::kFloats;             // [cap][HP] xl, later d_h_in scratch
+  float* xl_s = kGlobalRows ? p.rows_ws + (size_t)blockIdx.x * 5 * p.cap * HP
+                            : gsm + p.num_convs * L::kFloats;   // [cap][HP] xl, later d_h_in scratch
   float* xr_s = xl_s + (size_t)p.cap * HP;                  // [cap][HP] xr, later d_xr
   float* dxl_s = xr_s + (size_t)p.cap * HP;                 // [cap][HP] d_xl (atomic target)
   float* dout_s = dxl_s + (size_t)p.cap * HP;               // [cap][HP] d_out of the current app
@@ -1113,6 +1118,7 @@ __global__ void __launch_bounds__(kGnnThreads, 1) gnn_bwd_tc_kernel(const GnnArg
       }
       }
       __syncthreads();
+      GSC_TICK(8);
       // ---- 4S. source side: d_xl_j = sum over out-edges j->i of (alpha_ij g_i + d_u_ij); the graph is
       //      symmetric, so the out-neighbours of j are the entries of its own CSR row ----
       for (int t = tid; t < nc; t += kGnnThreads) {
@@ -1427,8 +1433,9 @@ static bool plan_bwd_tc(const GnnArgs& a, int max_nodes, int* cap, int* cols, si
 template <int HP>
 static int launch_bwd_both(GnnArgs a, int max_nodes, float* d_params, cudaStream_t st) {
   // atomic (any graph) kernel geometry
-  const size_t smem_f = (2 * (size_t)a.num_convs * ConvLayout<HP>::kFloats + 5 * (size_t)a.cap * HP) * 4;
-  GSC_REQUIRE(smem_f <= 227 * 1024, "gnn bwd: max_nodes=%d needs %zu B of shared memory (> 227 KB)", a.cap, smem_f);
+  size_t smem_f = (2 * (size_t)a.num_convs * ConvLayout<HP>::kFloats + 5 * (size_t)a.cap * HP) * 4;
+  const bool global_rows = smem_f > 227 * 1024;
+  if (global_rows) smem_f = 2 * (size_t)a.num_convs * ConvLayout<HP>::kFloats * 4;
   const int grid_f = bwd_grid(a.B, a.G);
   int cap_t = 0, cols = 0;
   size_t smem_t = 0;
@@ -1445,8 +1452,12 @@ static int launch_bwd_both(GnnArgs a, int max_nodes, float* d_params, cudaStream
     GSC_LAUNCH_CHECK("gnn_bwd_tc_kernel");
     a.gather_kernel_launched = 1;
   }
-  GSC_CUDA_TRY(cudaFuncSetAttribute(gnn_bwd_kernel<HP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_f));
-  gnn_bwd_kernel<HP><<<grid, kGnnThreads, smem_f, st>>>(a);              // returns at once if the other one ran
+  if (global_rows) {
+    gnn_bwd_kernel<HP, true><<<grid, kGnnThreads, smem_f, st>>>(a);
+  } else {
+    GSC_CUDA_TRY(cudaFuncSetAttribute(gnn_bwd_kernel<HP, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_f));
+    gnn_bwd_kernel<HP, false><<<grid, kGnnThreads, smem_f, st>>>(a);     // returns at once if the other one ran
+  }
   GSC_LAUNCH_CHECK("gnn_bwd_kernel");
   const int64_t P = conv_param_offset(a.num_convs, a.in_dim, a.H);
   gnn_bwd_reduce_kernel<<<(int)ceil_div(P, 256), 256, 0, st>>>(a.partials, grid, P, d_params);
@@ -1501,9 +1512,27 @@ extern "C" int gsc_gnn_embed_fwd(const float* x, int64_t Nt, int in_dim, const i
   }
 }
 
-extern "C" size_t gsc_gnn_bwd_workspace_bytes(int64_t B, int in_dim, int H, int num_layers) {
+// Partial gradients of every CTA, plus (graphs too large for shared memory) the node-row scratch.
+static size_t bwd_partials_bytes(int in_dim, int H, int num_layers) {
+  return ((size_t)kNumSMs * (size_t)conv_param_offset(num_layers, in_dim, H) * 4 + 255) / 256 * 256;
+}
+static bool bwd_rows_in_global(int max_nodes, int H, int num_layers) {
+  const int hp = pick_hp(H);
+  const size_t cap = max_nodes <= kGnnThreads ? kGnnThreads : ((size_t)max_nodes + 31) / 32 * 32;
+  const size_t conv_floats = hp == 8 ? ConvLayout<8>::kFloats : hp == 16 ? ConvLayout<16>::kFloats
+                           : hp == 24 ? ConvLayout<24>::kFloats : ConvLayout<32>::kFloats;
+  return (2 * (size_t)num_layers * conv_floats + 5 * cap * hp) * 4 > 227 * 1024;
+}
+
+extern "C" size_t gsc_gnn_bwd_workspace_bytes(int64_t B, int max_nodes, int in_dim, int H, int num_layers) {
   (void)B;
-  return (size_t)kNumSMs * (size_t)conv_param_offset(num_layers, in_dim, H) * 4;
+  if (max_nodes < 1 || H < 1 || H > GSC_MAX_HIDDEN || num_layers < 1) return 0;
+  size_t bytes = bwd_partials_bytes(in_dim, H, num_layers);
+  if (bwd_rows_in_global(max_nodes, H, num_layers)) {
+    const size_t cap = ((size_t)max_nodes + 31) / 32 * 32;
+    bytes += (size_t)kNumSMs * 5 * cap * pick_hp(H) * 4;
+  }
+  return bytes;
 }
 
 extern "C" int gsc_gnn_embed_bwd(const float* x, int64_t Nt, int in_dim, const int32_t* rowptr,
@@ -1517,10 +1546,11 @@ extern "C" int gsc_gnn_embed_bwd(const float* x, int64_t Nt, int in_dim, const i
   if (rc) return rc;
   GSC_REQUIRE(saved && d_emb && d_params && workspace && d_emb_ld >= H, "gnn bwd: null pointer or d_emb_ld < hidden");
   a.emb_ld = d_emb_ld;
-  if (workspace_bytes < gsc_gnn_bwd_workspace_bytes(B, in_dim, H, num_layers))
+  if (workspace_bytes < gsc_gnn_bwd_workspace_bytes(B, max_nodes, in_dim, H, num_layers))
     return fail(GSC_EWORKSPACE, "gnn bwd: workspace %zu < %zu", workspace_bytes,
-                gsc_gnn_bwd_workspace_bytes(B, in_dim, H, num_layers));
+                gsc_gnn_bwd_workspace_bytes(B, max_nodes, in_dim, H, num_layers));
   a.saved = const_cast<float*>(saved); a.d_emb = d_emb; a.partials = (float*)workspace;
+  a.rows_ws = reinterpret_cast<float*>(static_cast<uint8_t*>(workspace) + bwd_partials_bytes(in_dim, H, num_layers));
   a.dbg = g_gnn_debug;
   a.stats = pack_stats;
   cudaStream_t st = (cudaStream_t)stream;

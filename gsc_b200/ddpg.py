@@ -23,7 +23,7 @@ import numpy as np
 import torch
 
 from . import ops
-from .dp import allreduce_flat
+from .dp import all_gather_flat, allreduce_flat, reduce_scatter_flat, shard_range
 from .graph import GraphBatch
 from .models import Actor, QNetwork, net_backward, net_forward
 
@@ -31,15 +31,27 @@ from .models import Actor, QNetwork, net_backward, net_forward
 class DDPGUpdater:
     def __init__(self, actor: Actor, qf1: QNetwork, target_actor: Actor, qf1_target: QNetwork,
                  lr: float = 1e-3, gamma: float = 0.99, tau: float = 1e-4, betas=(0.9, 0.999),
-                 eps: float = 1e-8, process_group=None, world_size: int = 1):
+                 eps: float = 1e-8, process_group=None, world_size: int = 1, rank: int = 0,
+                 shard_optimizer: bool = False, global_batch: Optional[int] = None):
         self.actor, self.qf1, self.target_actor, self.qf1_target = actor, qf1, target_actor, qf1_target
         self.lr, self.gamma, self.tau, self.betas, self.eps = lr, gamma, tau, betas, eps
         self.pg, self.world_size = process_group, int(world_size)
+        # Losses are means over the GLOBAL minibatch: with uneven shards the ranks must agree on its size
+        # (default: every rank holds the same number of states).
+        self.global_batch = None if global_batch is None else int(global_batch)
         for net in (actor, qf1, target_actor, qf1_target):
             net._check_flat()
+        # shard_optimizer: reduce-scatter the gradient, Adam + soft update on this rank's 1/W slice
+        # (moments exist for that slice only), all-gather the updated online and target weights.
+        self.shard = bool(shard_optimizer) and self.world_size > 1
+        self.rank = int(rank)
         z = lambda net: torch.zeros_like(net.flat)
-        self.g_actor, self.m_actor, self.v_actor = z(actor), z(actor), z(actor)
-        self.g_critic, self.m_critic, self.v_critic = z(qf1), z(qf1), z(qf1)
+        zs = lambda net: torch.zeros(net.flat.numel() // self.world_size, dtype=torch.float32,
+                                     device=net.flat.device) if self.shard else z(net)
+        self.g_actor, self.m_actor, self.v_actor = z(actor), zs(actor), zs(actor)
+        self.g_critic, self.m_critic, self.v_critic = z(qf1), zs(qf1), zs(qf1)
+        self.gs_actor = zs(actor) if self.shard else None
+        self.gs_critic = zs(qf1) if self.shard else None
         self.step_actor = 0
         self.step_critic = 0
         self._neg = None
@@ -52,27 +64,39 @@ class DDPGUpdater:
         if self.world_size > 1:
             allreduce_flat(flat_grad, self.pg)
 
+    def _optimizer_step(self, net, target, g, gs, m, v, step_dev) -> None:
+        """Gradient exchange + fused Adam + soft target update of one network."""
+        if not self.shard:
+            self._allreduce(g)
+            ops.adam_soft_update_dev(net.flat, g, m, v, target.flat, self.lr, self.betas[0], self.betas[1],
+                                     self.eps, step_dev, self.tau)
+            return
+        lo, hi = shard_range(net.flat.numel(), self.rank, self.world_size)
+        reduce_scatter_flat(g, gs, self.pg)
+        ops.adam_soft_update_dev(net.flat[lo:hi], gs, m, v, target.flat[lo:hi], self.lr, self.betas[0],
+                                 self.betas[1], self.eps, step_dev, self.tau)
+        all_gather_flat(net.flat, self.pg)
+        all_gather_flat(target.flat, self.pg)
+
     def update_critic(self, nxt: GraphBatch, cur: GraphBatch, dones, rewards, actions):
         """reference _update_critic (simple_ddpg.py:204-219)."""
         B = cur.num_graphs
-        scale = 1.0 / (B * self.world_size)
+        scale = 1.0 / (self.global_batch or B * self.world_size)
         ta, tq, q = self.target_actor, self.qf1_target, self.qf1
         a2, _ = net_forward(ta, ta.flat, nxt, None, save=False, mask_output=True, clamp1=True)
         q2, _ = net_forward(tq, tq.flat, nxt, a2, save=False)
         qv, ctx = net_forward(q, q.flat, cur, actions, save=True)
         _, dq, loss = ops.td_mse(rewards, dones, q2, qv, self.gamma, scale)
         net_backward(q, q.flat, cur, ctx, dq.view(B, 1), self.g_critic)
-        self._allreduce(self.g_critic)
         self.step_critic += 1
-        ops.adam_soft_update_dev(q.flat, self.g_critic, self.m_critic, self.v_critic, tq.flat, self.lr,
-                                 self.betas[0], self.betas[1], self.eps, self.steps_dev[0:1], self.tau)
+        self._optimizer_step(q, tq, self.g_critic, self.gs_critic, self.m_critic, self.v_critic, self.steps_dev[0:1])
         return qv.view(-1), loss
 
     def update_actor(self, cur: GraphBatch):
         """reference _update_actor (simple_ddpg.py:221-227) + the actor half of
         _update_target_networks (:229-234)."""
         B = cur.num_graphs
-        scale = 1.0 / (B * self.world_size)
+        scale = 1.0 / (self.global_batch or B * self.world_size)
         ac, q, ta = self.actor, self.qf1, self.target_actor
         a, ctx_a = net_forward(ac, ac.flat, cur, None, save=True, mask_output=True)
         q_pi, ctx_q = net_forward(q, q.flat, cur, a, save=True, save_gnn=False)
@@ -83,10 +107,8 @@ class DDPGUpdater:
         dz = net_backward(q, q.flat, cur, ctx_q, self._neg, None, want_action_grad=True,
                           action_grad_masked=True)
         net_backward(ac, ac.flat, cur, ctx_a, dz, self.g_actor)
-        self._allreduce(self.g_actor)
         self.step_actor += 1
-        ops.adam_soft_update_dev(ac.flat, self.g_actor, self.m_actor, self.v_actor, ta.flat, self.lr,
-                                 self.betas[0], self.betas[1], self.eps, self.steps_dev[1:2], self.tau)
+        self._optimizer_step(ac, ta, self.g_actor, self.gs_actor, self.m_actor, self.v_actor, self.steps_dev[1:2])
         actor_loss = ops.colsum(q_pi) * (-scale)
         return actor_loss
 
@@ -111,6 +133,8 @@ class GraphedUpdate:
 
     def __init__(self, upd: DDPGUpdater, cur: GraphBatch, nxt: GraphBatch, actions, rewards, dones,
                  warmup: int = 2):
+        if upd.world_size > 1:
+            raise RuntimeError("GraphedUpdate: single-process updates only (the data-parallel step runs eagerly)")
         self.upd = upd
         cl = lambda t: None if t is None else t.clone()
         mk = lambda gb, share=None: GraphBatch(

@@ -46,7 +46,7 @@ def shard_states(st: StateBatch, rank: int, world: int) -> StateBatch:
     sel = (st.edge_index[0] >= n0) & (st.edge_index[0] < n1)
     return StateBatch(x=st.x[n0:n1], edge_index=np.ascontiguousarray(st.edge_index[:, sel] - n0),
                       batch=st.batch[n0:n1] - lo, ptr=st.ptr[lo:hi + 1] - n0, n=st.n[lo:hi],
-                      mask=st.mask[lo:hi], n_max=st.n_max, num_sfcs=st.num_sfcs, num_sfs=st.num_sfs)
+                      mask=None if st._mask is None else st._mask[lo:hi], n_max=st.n_max, num_sfcs=st.num_sfcs, num_sfs=st.num_sfs)
 
 
 def shard_transitions(cur, nxt, actions, rewards, dones, rank: int, world: int):
@@ -60,3 +60,45 @@ def allreduce_flat(flat_grad: torch.Tensor, group=None) -> torch.Tensor:
     if dist.is_initialized() and dist.get_world_size(group) > 1:
         dist.all_reduce(flat_grad, op=dist.ReduceOp.SUM, group=group)
     return flat_grad
+
+
+# ---- sharded optimizer (scaling caveat) -----------------------------------
+# Optimizer traffic (Adam state + target network, 36 B/param) is replicated work under plain data
+# parallelism; at N_max = 1000 it dwarfs the per-sample work.  Instead of all-reduce + full Adam,
+# every rank reduce-scatters the flat gradient, runs the fused Adam/soft-update on its 1/W slice of
+# the parameters, Adam moments and target network, and all-gathers the updated slices: the same
+# bytes on the wire as the all-reduce, optimizer traffic and moment memory divided by W.
+def shard_range(numel: int, rank: int, world: int) -> Tuple[int, int]:
+    """Equal contiguous slices of a flat buffer (its length is a multiple of the world size)."""
+    if numel % world:
+        raise ValueError(f"flat buffer of {numel} floats does not split into {world} equal shards")
+    chunk = numel // world
+    return rank * chunk, (rank + 1) * chunk
+
+
+def reduce_scatter_flat(flat_grad: torch.Tensor, out: torch.Tensor, group=None) -> torch.Tensor:
+    """out = this rank's slice of the sum of ``flat_grad`` over all ranks."""
+    world = dist.get_world_size(group)
+    rank = dist.get_rank(group)
+    lo, hi = shard_range(flat_grad.numel(), rank, world)
+    if flat_grad.is_cuda:
+        dist.reduce_scatter_tensor(out, flat_grad, op=dist.ReduceOp.SUM, group=group)
+    else:                       # gloo has no reduce-scatter: same result through an all-reduce
+        dist.all_reduce(flat_grad, op=dist.ReduceOp.SUM, group=group)
+        out.copy_(flat_grad[lo:hi])
+    return out
+
+
+def all_gather_flat(flat: torch.Tensor, group=None) -> torch.Tensor:
+    """Every rank's slice of ``flat`` (updated in place) is broadcast into the others' copies."""
+    world = dist.get_world_size(group)
+    rank = dist.get_rank(group)
+    lo, hi = shard_range(flat.numel(), rank, world)
+    if flat.is_cuda:
+        dist.all_gather_into_tensor(flat, flat[lo:hi], group=group)     # in place: slice r of the output is the input
+    else:
+        parts = [torch.empty(hi - lo, dtype=flat.dtype) for _ in range(world)]
+        dist.all_gather(parts, flat[lo:hi].clone(), group=group)
+        for r, part in enumerate(parts):
+            flat[r * (hi - lo):(r + 1) * (hi - lo)].copy_(part)
+    return flat

@@ -26,6 +26,9 @@ from . import ops
 from .graph import GraphBatch
 
 _ALIGN = 64  # floats; every region of a flat buffer starts 256-byte aligned
+# A flat buffer's length is a multiple of this, so that it splits into equal, 16-byte aligned shards
+# on any world size from 1 to 8 (sharded optimizer: reduce-scatter / all-gather need equal chunks).
+_FLAT_MULTIPLE = 6720   # lcm(64, 2^5 * 3 * 5 * 7)
 
 
 def _round_up(a: int, b: int) -> int:
@@ -206,7 +209,7 @@ class _FlatNet(nn.Module):
             off = _round_up(off + n_out * ld, _ALIGN)
             items.append((lin.bias, off, (n_out,), None, 0))
             off = _round_up(off + n_out, _ALIGN)
-        return items, off
+        return items, _round_up(off, _FLAT_MULTIPLE)
 
     def _flatten(self) -> None:
         items, total = self._layout()

@@ -251,7 +251,7 @@ def gnn_embed_bwd(x, rowptr, col, graph_ptr, num_graphs: int, max_nodes: int, pa
     Nt, in_dim = int(x.shape[0]), int(x.shape[1])
     if d_params is None:
         d_params = torch.empty_like(params)
-    ws, wsn = workspace(lib.gsc_gnn_bwd_workspace_bytes(num_graphs, in_dim, hidden, num_layers),
+    ws, wsn = workspace(lib.gsc_gnn_bwd_workspace_bytes(num_graphs, max_nodes, in_dim, hidden, num_layers),
                         x.device, "gnn_bwd")
     with _Timed("gnn_bwd"):
         check(lib.gsc_gnn_embed_bwd(_ptr(x), Nt, in_dim, _ptr(rowptr), _ptr(col), _ptr(graph_ptr),

@@ -9,7 +9,6 @@ with numpy only; the bundled GraphML topologies are not needed at run time.
 """
 from __future__ import annotations
 
-from dataclasses import dataclass
 from typing import List, Optional
 
 import numpy as np
@@ -48,18 +47,29 @@ def structured_mask(n: np.ndarray, n_max: int, num_sfcs: int = 1, num_sfs: int =
     return np.ascontiguousarray(m.reshape(n.shape[0], -1), dtype=np.float32)
 
 
-@dataclass
 class StateBatch:
-    """A collated minibatch in the reference's ``Batch.from_data_list`` layout (buffer.py:65-81)."""
-    x: np.ndarray            # [Nt, F] f32
-    edge_index: np.ndarray   # [2, E]  i64, node ids offset per graph
-    batch: np.ndarray        # [Nt]    i64
-    ptr: np.ndarray          # [B+1]   i64
-    n: np.ndarray            # [B]     i64 real node count of every state
-    mask: np.ndarray         # [B, A]  f32
-    n_max: int
-    num_sfcs: int = 1
-    num_sfs: int = 3
+    """A collated minibatch in the reference's ``Batch.from_data_list`` layout (buffer.py:65-81).
+
+    ``mask`` ([B, A] f32) is a function of ``n`` (simulator_wrapper.py:302-306); it is materialised on
+    first use only, so that very large batches (65 536 states) can be generated without it."""
+
+    def __init__(self, x, edge_index, batch, ptr, n, mask=None, n_max: int = 0, num_sfcs: int = 1,
+                 num_sfs: int = 3):
+        self.x = x                        # [Nt, F] f32
+        self.edge_index = edge_index      # [2, E]  i64, node ids offset per graph
+        self.batch = batch                # [Nt]    i64
+        self.ptr = ptr                    # [B+1]   i64
+        self.n = n                        # [B]     i64 real node count of every state
+        self._mask = mask
+        self.n_max = int(n_max)
+        self.num_sfcs = int(num_sfcs)
+        self.num_sfs = int(num_sfs)
+
+    @property
+    def mask(self) -> np.ndarray:
+        if self._mask is None:
+            self._mask = structured_mask(self.n, self.n_max, self.num_sfcs, self.num_sfs)
+        return self._mask
 
     @property
     def num_graphs(self) -> int:
@@ -101,8 +111,7 @@ def make_states(B: int, n_max: int, n_low: int, n_high: int, link_ratio: float =
     edge_index = np.ascontiguousarray(np.concatenate(edges, axis=1)) if B else np.zeros((2, 0), np.int64)
     batch = np.repeat(np.arange(B, dtype=np.int64), n)
     x = rng.random((int(ptr[-1]), num_feat), dtype=np.float32)
-    mask = structured_mask(n, n_max, num_sfcs, num_sfs)
-    return StateBatch(x=x, edge_index=edge_index, batch=batch, ptr=ptr, n=n, mask=mask, n_max=n_max,
+    return StateBatch(x=x, edge_index=edge_index, batch=batch, ptr=ptr, n=n, mask=None, n_max=n_max,
                       num_sfcs=num_sfcs, num_sfs=num_sfs)
 
 
@@ -132,7 +141,7 @@ def make_transitions(B: int, n_max: int, n_low: int, n_high: int, seed: int = 12
     cur = make_states(B, n_max, n_low, n_high, seed=seed, **kw)
     rng = np.random.default_rng(seed + 1)
     nxt = StateBatch(x=rng.random(cur.x.shape, dtype=np.float32), edge_index=cur.edge_index,
-                     batch=cur.batch, ptr=cur.ptr, n=cur.n, mask=cur.mask, n_max=cur.n_max,
+                     batch=cur.batch, ptr=cur.ptr, n=cur.n, mask=cur._mask, n_max=cur.n_max,
                      num_sfcs=cur.num_sfcs, num_sfs=cur.num_sfs)
     actions = make_actions(cur, seed)
     rewards = (rng.random(B, dtype=np.float32) * 2 - 1).astype(np.float32)

@@ -122,8 +122,11 @@ int gsc_gnn_embed_fwd(const float* x, int64_t num_nodes, int in_dim, const int32
  * The per-CTA partial sums live in the workspace and are reduced in a fixed order.
  * pack_stats: the packer's stats array (device) or NULL.  When stats[3] says the graph is symmetric
  * the kernel gathers along out-edges (no atomics, bit-reproducible); otherwise, or with NULL, it
- * scatters with shared-memory atomics. */
-size_t gsc_gnn_bwd_workspace_bytes(int64_t num_graphs, int in_dim, int hidden, int num_layers);
+ * scatters with shared-memory atomics.
+ * Graphs whose node rows do not fit in shared memory (about > 450 nodes at hidden = 22, e.g. the
+ * 1000-node topologies of the data-parallel configuration) keep them in the workspace, which is why
+ * its size depends on max_nodes. */
+size_t gsc_gnn_bwd_workspace_bytes(int64_t num_graphs, int max_nodes, int in_dim, int hidden, int num_layers);
 int gsc_gnn_embed_bwd(const float* x, int64_t num_nodes, int in_dim, const int32_t* rowptr,
                       const int32_t* col, const int32_t* graph_ptr, int64_t num_graphs,
                       int max_nodes, const float* params, int hidden, int num_layers, int num_iter,

@@ -70,3 +70,63 @@ def test_shard_bounds_and_rebasing():
         if p.num_graphs:
             assert p.ptr[0] == 0 and p.ptr[-1] == p.x.shape[0] and p.batch.min() == 0
             assert p.edge_index.min() >= 0 and p.edge_index.max() < p.x.shape[0]
+
+
+def _adam(p, g, m, v, step, lr=1e-3, b1=0.9, b2=0.999, eps=1e-8):
+    m.mul_(b1).add_(g, alpha=1 - b1)
+    v.mul_(b2).addcmul_(g, g, value=1 - b2)
+    denom = (v.sqrt() / (1 - b2 ** step) ** 0.5).add_(eps)
+    p.addcdiv_(m, denom, value=-lr / (1 - b1 ** step))
+
+
+def _shard_worker(rank, world, port, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world),
+                      LOCAL_RANK=str(rank))
+    dp.init_from_env(backend="gloo")
+    P = 6720                                                   # one flat-buffer quantum (models._FLAT_MULTIPLE)
+    gen = torch.Generator().manual_seed(3)
+    p0 = torch.randn(P, generator=gen, dtype=torch.float64)
+    grads = [torch.randn(world, P, generator=gen, dtype=torch.float64) for _ in range(3)]   # per step, per rank
+    # sharded optimizer: moments exist for this rank's slice only
+    p, tgt = p0.clone(), p0.clone()
+    lo, hi = dp.shard_range(P, rank, world)
+    m, v, gs = torch.zeros(hi - lo, dtype=torch.float64), torch.zeros(hi - lo, dtype=torch.float64), torch.zeros(hi - lo, dtype=torch.float64)
+    for step, g in enumerate(grads, 1):
+        dp.reduce_scatter_flat(g[rank].clone(), gs)
+        _adam(p[lo:hi], gs, m, v, step)
+        tgt[lo:hi].mul_(0.99).add_(p[lo:hi], alpha=0.01)
+        dp.all_gather_flat(p)
+        dp.all_gather_flat(tgt)
+    if rank == 0:
+        q, qt = p0.clone(), p0.clone()
+        mf, vf = torch.zeros(P, dtype=torch.float64), torch.zeros(P, dtype=torch.float64)
+        for step, g in enumerate(grads, 1):
+            _adam(q, g.sum(0), mf, vf, step)
+            qt.mul_(0.99).add_(q, alpha=0.01)
+        out.put((float((p - q).abs().max()), float((tgt - qt).abs().max())))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_sharded_optimizer_exchange_equals_allreduce_and_full_adam():
+    ctx = mp.get_context("spawn")
+    out = ctx.Queue()
+    port = 31500 + os.getpid() % 2000
+    procs = [ctx.Process(target=_shard_worker, args=(r, 2, port, out)) for r in range(2)]
+    for p in procs:
+        p.start()
+    e_p, e_t = out.get(timeout=120)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert e_p < 1e-14 and e_t < 1e-14
+
+
+def test_shard_range_needs_divisible_buffers_and_flat_buffers_are_divisible():
+    import pytest
+    from gsc_b200.models import _FLAT_MULTIPLE
+    assert [dp.shard_range(24, r, 4) for r in range(4)] == [(0, 6), (6, 12), (12, 18), (18, 24)]
+    with pytest.raises(ValueError):
+        dp.shard_range(25, 0, 4)
+    for w in range(1, 9):
+        assert _FLAT_MULTIPLE % w == 0 and (_FLAT_MULTIPLE // w) % 4 == 0      # equal, 16-byte aligned shards

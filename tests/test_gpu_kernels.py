@@ -109,7 +109,7 @@ def test_gnn_embed_fwd_matches_oracle(B, n_max, lo, hi, H, F, num_layers, num_it
     assert rel_err(emb.cpu().numpy(), ref.numpy()) < 2e-5
 
 
-BWD_CASES = [c for c in CASES if c[1] <= 300]
+BWD_CASES = CASES + [(5, 600, 450, 600, 22, 3, 2, 2)]   # > ~450 nodes: node rows in the workspace
 
 
 @pytest.mark.parametrize("B,n_max,lo,hi,H,F,num_layers,num_iter", BWD_CASES)
@@ -127,7 +127,7 @@ def test_gnn_embed_bwd_matches_autograd_of_oracle(B, n_max, lo, hi, H, F, num_la
     emb, saved = ops.gnn_embed_fwd(gb.x, rowptr, col, gptr, B, gb.max_nodes, flat, H, num_layers, num_iter, save=True)
     d = ops.gnn_embed_bwd(gb.x, rowptr, col, gptr, B, gb.max_nodes, flat, H, num_layers, num_iter, saved,
                           d_emb.float().to(DEV), pack_stats=gb.pack_stats())
-    assert int(gb.pack_stats()[3]) == 0                       # undirected topology -> gather kernel
+    assert int(gb.pack_stats()[3]) == 0                       # undirected topology -> gather kernel (if it fits)
     want = _flat({k: v.grad for k, v in sd.items()}, num_layers).cpu().numpy()
     got = d.cpu().numpy()
     assert rel_err(got, want) < 1e-4

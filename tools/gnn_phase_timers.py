@@ -11,7 +11,7 @@ for (B,nm,lo,hi,links) in [(4096,24,16,24,None),(1024,100,100,100,150)]:
     actor=Actor(AgentSpec(nm)).to('cuda')
     gnn,_=actor.views(actor.flat)
     rp,col,gp=gb.csr()
-    dbg=torch.zeros(8,device='cuda')
+    dbg=torch.zeros(16,device='cuda')
     for it in range(3):
         ops.gnn_embed_fwd(gb.x,rp,col,gp,B,gb.max_nodes,gnn,22,2,2)
     torch.cuda.synchronize()
@@ -27,4 +27,4 @@ for (B,nm,lo,hi,links) in [(4096,24,16,24,None),(1024,100,100,100,150)]:
     lib.gsc_debug_set_gnn_timers(dbg.data_ptr())
     e0.record(); ops.gnn_embed_bwd(gb.x,rp,col,gp,B,gb.max_nodes,gnn,22,2,2,saved,d_emb,pack_stats=gb.pack_stats()); e1.record(); torch.cuda.synchronize()
     lib.gsc_debug_set_gnn_timers(None)
-    print(B,nm,"bwd kernel ms",e0.elapsed_time(e1),"cycles {chunk,hrows,R,rows,edgeT+S,W,split,H}:",dbg.tolist()[:8])
+    print(B,nm,"bwd kernel ms",e0.elapsed_time(e1),"cycles {chunk,hrows,R,rows,edgeS,W,split,H,edgeT}:",dbg.tolist()[:9])
