@@ -5,11 +5,13 @@
 // all three roles -- forward (both operands K-major), dgrad (B MN-major) and wgrad (both MN-major)
 // -- with the same K-segment / epilogue contract as the exact-fp32 SIMT kernel in gemm.cu.
 //
-// CTA = 192 threads, persistent over (m-tile, n-tile, k-split) work items:
+// CTA = 320 threads, persistent over (m-tile, n-tile, k-split) work items:
 //   warp 0      TMA producer   one elected lane issues cp.async.bulk.tensor per stage
 //   warp 1      MMA issuer     one elected lane issues 4 x tcgen05.mma (K = 8 each) per 32-wide
 //                              k-block; tcgen05.commit frees the stage / publishes the accumulator
-//   warps 2..5  epilogue       tcgen05.ld (32 lanes x 32 columns per warp), bias/ReLU/mask/gate/
+//   warps 2..9  epilogue       two warps per TMEM lane quadrant, 64 of the tile's 128 columns each
+//                              (a lone warp per scheduler cannot hide its own latencies):
+//                              tcgen05.ld (32 lanes x 32 columns), bias/ReLU/mask/gate/
 //                              clamp.  The mask (or gate) tile is prefetched by TMA into a 64 KB
 //                              swizzled buffer, combined in place with the accumulators and
 //                              written out with TMA stores: both streams are fully coalesced and
@@ -27,11 +29,18 @@
 namespace gsc {
 
 constexpr int kTcBM = 128, kTcBN = 128, kTcBK = 32;          // fp32 elements; BK * 4 B = one 128 B swizzle row
-constexpr int kTcStages = 4;
-constexpr int kTcThreads = 192;
+// Shared memory: six 32 KB ring slots.  Launches whose output leaves through the 64 KB TMA epilogue
+// tile use four of them as the operand ring and the last two as that tile; split-K launches (direct
+// partial stores, long K streams) use all six as the ring: bytes in flight per SM are what bounds a
+// K-streaming GEMM (latency x bandwidth), not the tensor pipe.
+constexpr int kTcMaxStages = 6;
+constexpr int kTcEpiStages = 4;                              // ring depth next to the epilogue tile
+constexpr int kTcEpiWarps = 8;                               // two warps per TMEM lane quadrant, 64 columns each
+constexpr int kTcThreads = 64 + 32 * kTcEpiWarps;            // 320
 constexpr int kTcStageBytes = (kTcBM + kTcBN) * kTcBK * 4;   // 32 KB
 constexpr int kTcEpiBytes = kTcBM * kTcBN * 4;                 // 64 KB: epilogue operand in, output tile out (in place)
-constexpr int kTcSmemBytes = kTcStages * kTcStageBytes + kTcEpiBytes + 1024 /*align*/ + 256 /*barriers*/;
+constexpr int kTcSmemBytes = kTcMaxStages * kTcStageBytes + 1024 /*align*/ + 256 /*barriers*/;
+static_assert(kTcEpiStages * kTcStageBytes + kTcEpiBytes == kTcMaxStages * kTcStageBytes, "ring/epilogue split");
 constexpr int kTmemCols = 2 * kTcBN;                          // 256
 
 struct TcParams {
@@ -48,6 +57,7 @@ struct TcParams {
   int flags, num_seg;
   int kb_end[3];          // exclusive prefix of 32-wide k-blocks per segment
   int kb_total, kb_per_split, splits, tiles_m, tiles_n;
+  int stages;             // operand ring depth: kTcEpiStages with the TMA epilogue, kTcMaxStages without
   int epi_tma;            // 1: output tile leaves through shared memory + TMA store (coalesced, asynchronous)
   int epi_kind;           // operand streamed in by TMA for the epilogue: 0 none, 1 mul, 2 gate
 };
@@ -114,8 +124,10 @@ gemm_tc_kernel(const __grid_constant__ TcParams p, const __grid_constant__ CUten
                const __grid_constant__ CUtensorMap mapE) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;       // 1024 B: swizzle-128B atoms
-  const uint32_t ebuf = smem_base + kTcStages * kTcStageBytes;             // epilogue tile, 4 x [128 rows x 128 B]
-  const uint32_t bar_base = ebuf + kTcEpiBytes;
+  const uint32_t ebuf = smem_base + kTcEpiStages * kTcStageBytes;          // epilogue tile, 4 x [128 rows x 128 B]
+  const uint32_t bar_base = smem_base + kTcMaxStages * kTcStageBytes;
+  constexpr int kTcStages = kTcMaxStages;                                  // barrier slots
+  const int num_stages = p.stages;
   // barriers: full[S], empty[S], tmem_full[2], tmem_empty[2], then the TMEM base address slot
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto empty_bar = [&](int s) { return bar_base + 8u * (kTcStages + s); };
@@ -131,7 +143,7 @@ gemm_tc_kernel(const __grid_constant__ TcParams p, const __grid_constant__ CUten
 
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < kTcStages; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
-    for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), 4); }
+    for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), kTcEpiWarps); }
     mbar_init(efull_bar, 1);
     mbar_init(eempty_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -176,7 +188,7 @@ gemm_tc_kernel(const __grid_constant__ TcParams p, const __grid_constant__ CUten
             for (int b = 0; b < kTcBN / 32; ++b)                                    // box {32 n, 32 k}
               tma_load_2d(sb + b * 4096, mB, full_bar(stage), it.n0 + 32 * b, k0);
           }
-          if (++stage == kTcStages) { stage = 0; phase ^= 1u; }
+          if (++stage == num_stages) { stage = 0; phase ^= 1u; }
         }
         if (p.epi_tma && p.epi_kind) {             // prefetch the mask / gate tile of this work item
           mbar_wait(eempty_bar, ephase ^ 1u);
@@ -216,14 +228,15 @@ gemm_tc_kernel(const __grid_constant__ TcParams p, const __grid_constant__ CUten
             tc_mma_tf32(tmem_d, da, db, idesc, (kb > it.kb_begin || j > 0) ? 1u : 0u);
           }
           tc_commit(empty_bar(stage));            // frees the smem stage once these MMAs retire
-          if (++stage == kTcStages) { stage = 0; phase ^= 1u; }
+          if (++stage == num_stages) { stage = 0; phase ^= 1u; }
         }
         tc_commit(tfull_bar(as));                 // accumulator complete -> epilogue
       }
     }
   } else {
-    // ===================== epilogue warps (2..5) =====================
+    // ===================== epilogue warps (2..9) =====================
     const int quad = warp & 3;                    // TMEM lane quadrant this warp may access
+    const int c_begin = ((warp - 2) >> 2) * (kTcBN / 64), c_end = c_begin + kTcBN / 64;   // its 32-column chunks
     int iter = 0;
     for (int w = blockIdx.x; w < total_work; w += gridDim.x, ++iter) {
       const WorkItem it = decode_work(p, w);
@@ -236,8 +249,11 @@ gemm_tc_kernel(const __grid_constant__ TcParams p, const __grid_constant__ CUten
         const int lrow = quad * 32 + lane;
         const int64_t grow = (int64_t)it.m0 + lrow;
         const int nb = ((p.flags & (GSC_EPI_ROWTABLE | GSC_EPI_SMASK)) && grow < p.M) ? p.row_n[grow] : 0;
+        const float* trow = (p.flags & GSC_EPI_ROWTABLE) ? p.row_table + (int64_t)nb * p.ld_table : nullptr;
+        const bool vec_ok = (!(p.flags & GSC_EPI_ROWTABLE) || ((reinterpret_cast<uintptr_t>(trow) & 15) == 0)) &&
+                            (!(p.flags & GSC_EPI_BIAS) || ((reinterpret_cast<uintptr_t>(p.bias) & 15) == 0));
 #pragma unroll 1
-        for (int c = 0; c < kTcBN / 32; ++c) {
+        for (int c = c_begin; c < c_end; ++c) {
           float v[32];
           tc_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(as * kTcBN + c * 32), v);
           const uint32_t rbase = ebuf + c * 16384 + lrow * 128;
@@ -251,12 +267,32 @@ gemm_tc_kernel(const __grid_constant__ TcParams p, const __grid_constant__ CUten
             if (p.epi_kind) asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(e.x), "=f"(e.y), "=f"(e.z), "=f"(e.w) : "r"(addr));
             float o[4] = {v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]};
             const float ev[4] = {e.x, e.y, e.z, e.w};
+            // additive per-column terms (bias, per-n table row): one 128-bit load per four columns
+            float add[4] = {0.f, 0.f, 0.f, 0.f};
+            if (p.flags & (GSC_EPI_ROWTABLE | GSC_EPI_BIAS)) {
+              const int64_t cq = col0 + 4 * q;
+              if (vec_ok && cq + 4 <= p.N) {
+                if (p.flags & GSC_EPI_ROWTABLE) {
+                  const float4 t4 = *reinterpret_cast<const float4*>(trow + cq);
+                  add[0] += t4.x; add[1] += t4.y; add[2] += t4.z; add[3] += t4.w;
+                }
+                if (p.flags & GSC_EPI_BIAS) {
+                  const float4 b4 = *reinterpret_cast<const float4*>(p.bias + cq);
+                  add[0] += b4.x; add[1] += b4.y; add[2] += b4.z; add[3] += b4.w;
+                }
+              } else {
+#pragma unroll
+                for (int u = 0; u < 4; ++u)
+                  if (cq + u < p.N) {
+                    if (p.flags & GSC_EPI_ROWTABLE) add[u] += trow[cq + u];
+                    if (p.flags & GSC_EPI_BIAS) add[u] += p.bias[cq + u];
+                  }
+              }
+            }
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
               const int64_t col = col0 + 4 * q + u;
-              float t = o[u];
-              if ((p.flags & GSC_EPI_ROWTABLE) && col < p.N) t += p.row_table[(int64_t)nb * p.ld_table + col];
-              if ((p.flags & GSC_EPI_BIAS) && col < p.N) t += p.bias[col];
+              float t = o[u] + add[u];
               if (p.flags & GSC_EPI_RELU) t = fmaxf(t, 0.f);
               if (p.epi_kind == 1) t *= ev[u];
               if (p.flags & GSC_EPI_SMASK) t = walk.next(nb) ? t : 0.f;
@@ -274,7 +310,7 @@ gemm_tc_kernel(const __grid_constant__ TcParams p, const __grid_constant__ CUten
         __syncwarp();
         if (lane == 0) mbar_arrive(tempty_bar(as));                 // accumulator buffer is free again
         fence_proxy_async_smem();                                    // st.shared -> visible to the TMA store
-        asm volatile("bar.sync 1, 128;" ::: "memory");
+        asm volatile("bar.sync 1, 256;" ::: "memory");
         if (warp == 2 && lane == 0) {
 #pragma unroll
           for (int c = 0; c < kTcBN / 32; ++c)
@@ -285,12 +321,12 @@ gemm_tc_kernel(const __grid_constant__ TcParams p, const __grid_constant__ CUten
           asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // smem tile may be overwritten
           if (p.epi_kind) mbar_arrive(eempty_bar);
         }
-        asm volatile("bar.sync 1, 128;" ::: "memory");
+        asm volatile("bar.sync 1, 256;" ::: "memory");
         continue;
       }
       const int64_t row = (int64_t)it.m0 + quad * 32 + lane;
 #pragma unroll 1
-      for (int c = 0; c < kTcBN / 32; ++c) {
+      for (int c = c_begin; c < c_end; ++c) {
         float v[32];
         tc_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(as * kTcBN + c * 32), v);
         const int64_t col0 = (int64_t)it.n0 + c * 32;
@@ -457,6 +493,7 @@ int gemm_tc_launch(const gsc_gemm_args* a, int64_t M, int64_t N, float* C, int64
       p.epi_tma = 1; p.epi_kind = kind;
     }
   }
+  p.stages = p.epi_tma ? kTcEpiStages : kTcMaxStages;
   const int64_t work = tiles * p.splits;
   const int grid = (int)(work < kNumSMs ? work : kNumSMs);
 
