@@ -173,21 +173,30 @@ __global__ void gemm_finalize_kernel(const GemmDev g) {
   }
 }
 
-__global__ void colsum_kernel(const float* __restrict__ X, int64_t ld, int64_t M, int64_t N,
-                              float* __restrict__ out) {
-  // block = 32 columns x 8 row-lanes; rows strided by 8, reduced through shared memory.
-  __shared__ float red[8][33];
+__global__ void __launch_bounds__(1024) colsum_kernel(const float* __restrict__ X, int64_t ld, int64_t M, int64_t N,
+                                                      float* __restrict__ out) {
+  // block = 32 columns x 32 row-lanes; every thread keeps four independent partial sums (the loop is
+  // latency-bound otherwise), the 32 row-lanes are reduced through shared memory in a fixed order.
+  __shared__ float red[32][33];
   const int c = threadIdx.x & 31, r = threadIdx.x >> 5;
   const int64_t j = (int64_t)blockIdx.x * 32 + c;
-  float s = 0.f;
-  if (j < N)
-    for (int64_t i = r; i < M; i += 8) s += X[i * ld + j];
-  red[r][c] = s;
+  float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+  if (j < N) {
+    int64_t i = r;
+    for (; i + 96 < M; i += 128) {
+      s0 += X[i * ld + j];
+      s1 += X[(i + 32) * ld + j];
+      s2 += X[(i + 64) * ld + j];
+      s3 += X[(i + 96) * ld + j];
+    }
+    for (; i < M; i += 32) s0 += X[i * ld + j];
+  }
+  red[r][c] = (s0 + s1) + (s2 + s3);
   __syncthreads();
   if (r == 0 && j < N) {
     float tot = 0.f;
 #pragma unroll
-    for (int k = 0; k < 8; ++k) tot += red[k][c];
+    for (int k = 0; k < 32; ++k) tot += red[k][c];
     out[j] = tot;
   }
 }
@@ -295,7 +304,7 @@ extern "C" int gsc_gemm(const gsc_gemm_args* a, int64_t M, int64_t N, float* C, 
 
 extern "C" int gsc_colsum(const float* X, int64_t ld, int64_t M, int64_t N, float* out, void* stream) {
   GSC_REQUIRE(X && out && M >= 0 && N >= 1, "gsc_colsum: bad arguments");
-  colsum_kernel<<<(int)ceil_div(N, 32), 256, 0, (cudaStream_t)stream>>>(X, ld, M, N, out);
+  colsum_kernel<<<(int)ceil_div(N, 32), 1024, 0, (cudaStream_t)stream>>>(X, ld, M, N, out);
   GSC_LAUNCH_CHECK("colsum_kernel");
   return GSC_OK;
 }

@@ -1311,13 +1311,29 @@ __global__ void __launch_bounds__(kGnnThreads, 1) gnn_bwd_tc_kernel(const GnnArg
   }
 }
 
-__global__ void gnn_bwd_reduce_kernel(const float* __restrict__ partials, int num_partials, int64_t P,
-                                      float* __restrict__ d_params) {
-  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < P;
-       t += (int64_t)gridDim.x * blockDim.x) {
-    float s = 0.f;
-    for (int b = 0; b < num_partials; ++b) s += partials[(size_t)b * P + t];
-    d_params[t] = s;
+// d_params[t] = sum of the CTA partials, in a fixed order: block = 32 parameters x 8 partial-lanes,
+// lane r adds the partials r, r + 8, ... (independent loads in flight), then the lanes are added.
+__global__ void __launch_bounds__(256)
+gnn_bwd_reduce_kernel(const float* __restrict__ partials, int num_partials, int64_t P, float* __restrict__ d_params) {
+  __shared__ float red[8][33];
+  const int c = threadIdx.x & 31, r = threadIdx.x >> 5;
+  const int64_t t = (int64_t)blockIdx.x * 32 + c;
+  float s0 = 0.f, s1 = 0.f;
+  if (t < P) {
+    int b = r;
+    for (; b + 8 < num_partials; b += 16) {
+      s0 += partials[(size_t)b * P + t];
+      s1 += partials[(size_t)(b + 8) * P + t];
+    }
+    if (b < num_partials) s0 += partials[(size_t)b * P + t];
+  }
+  red[r][c] = s0 + s1;
+  __syncthreads();
+  if (r == 0 && t < P) {
+    float tot = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) tot += red[k][c];
+    d_params[t] = tot;
   }
 }
 
@@ -1460,7 +1476,7 @@ static int launch_bwd_both(GnnArgs a, int max_nodes, float* d_params, cudaStream
   }
   GSC_LAUNCH_CHECK("gnn_bwd_kernel");
   const int64_t P = conv_param_offset(a.num_convs, a.in_dim, a.H);
-  gnn_bwd_reduce_kernel<<<(int)ceil_div(P, 256), 256, 0, st>>>(a.partials, grid, P, d_params);
+  gnn_bwd_reduce_kernel<<<(int)ceil_div(P, 32), 256, 0, st>>>(a.partials, grid, P, d_params);
   GSC_LAUNCH_CHECK("gnn_bwd_reduce_kernel");
   return GSC_OK;
 }

@@ -84,34 +84,55 @@ mask_table_kernel(const float* __restrict__ W, int64_t ldw, int n_max, int group
   if (threadIdx.x == 0) table[blockIdx.x] = 0.f;
 }
 
-// S[o][t] = sum over {b: n_b > t} dY[b, o]  for t = 0..n_max-1 (row-major [N1][n_max]).  One thread
-// per (o, t): lanes run over o (coalesced dY rows, shared by the CTA's warps through L1), warps over t.
-__global__ void __launch_bounds__(256)
-mask_wgrad_bins_kernel(const float* __restrict__ dY, int64_t ldy, const int32_t* __restrict__ n,
-                       int64_t B, int64_t N1, int n_max, float* __restrict__ S) {
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+// S_part[z][o][t] = sum over {b in row slice z: n_b > t} dY[b, o],  t = 0..n_max-1.
+// A CTA owns 32 columns and one slice of the batch; warp w adds its rows b = w (mod warps) into
+// private shared-memory bins[w][n_b][lane] (B additions per column instead of B * n_max, no atomics);
+// the bins are summed over the warps and suffix-summed over n.  The slices are added by the expand
+// kernel in a fixed order, so the result is bit-reproducible.
+__global__ void mask_wgrad_bins_kernel(const float* __restrict__ dY, int64_t ldy, const int32_t* __restrict__ n,
+                                       int64_t B, int64_t N1, int n_max, int64_t rows_per_slice,
+                                       float* __restrict__ S_part) {
+  extern __shared__ float bins[];        // [warps][n_max + 1][32]
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, warps = blockDim.x >> 5;
   const int64_t o = (int64_t)blockIdx.x * 32 + lane;
-  const int t = blockIdx.y * 8 + warp;
-  if (o >= N1 || t >= n_max) return;
-  float acc[4] = {0.f, 0.f, 0.f, 0.f};
-  int64_t b = 0;
-  for (; b + 4 <= B; b += 4) {
-#pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      const float v = dY[(b + u) * ldy + o];
-      acc[u] += n[b + u] > t ? v : 0.f;
+  const int64_t b0 = (int64_t)blockIdx.y * rows_per_slice;
+  const int64_t b1 = b0 + rows_per_slice < B ? b0 + rows_per_slice : B;
+  float* mine = bins + (size_t)warp * (n_max + 1) * 32;
+  for (int t = 0; t <= n_max; ++t) mine[t * 32 + lane] = 0.f;
+  if (o < N1)
+    for (int64_t b = b0 + warp; b < b1; b += warps) {
+      int nb = n[b];
+      nb = nb < 0 ? 0 : (nb > n_max ? n_max : nb);
+      mine[nb * 32 + lane] += dY[b * ldy + o];
+    }
+  __syncthreads();
+  // sum over the warps: thread (warp, lane) takes the bins t = warp, warp + warps, ...
+  for (int t = warp; t <= n_max; t += warps) {
+    float v = 0.f;
+    for (int w = 0; w < warps; ++w) v += bins[((size_t)w * (n_max + 1) + t) * 32 + lane];
+    bins[(size_t)t * 32 + lane] = v;            // into warp 0's bins (its own slot t is read before it is written)
+  }
+  __syncthreads();
+  if (warp == 0 && o < N1) {
+    float* out = S_part + ((int64_t)blockIdx.y * N1 + o) * n_max;
+    float run = 0.f;
+    for (int t = n_max - 1; t >= 0; --t) {      // S[t] = sum_{n > t} bins[n]
+      run += bins[(size_t)(t + 1) * 32 + lane];
+      out[t] = run;
     }
   }
-  for (; b < B; ++b) acc[0] += n[b] > t ? dY[b * ldy + o] : 0.f;
-  S[o * n_max + t] = (acc[0] + acc[1]) + (acc[2] + acc[3]);
 }
 
 // dW[o, (i*G + g)*N + j] = S[o][max(i, j)]: blockIdx.x = o, blockIdx.y strides over the i*G + g rows.
 __global__ void __launch_bounds__(256)
-mask_wgrad_expand_kernel(const float* __restrict__ S, int n_max, int groups, float* __restrict__ dW, int64_t ldw) {
-  extern __shared__ float s_col[];                         // S[o][:]
-  const float* So = S + (int64_t)blockIdx.x * n_max;
-  for (int t = threadIdx.x; t < n_max; t += blockDim.x) s_col[t] = So[t];
+mask_wgrad_expand_kernel(const float* __restrict__ S_part, int slices, int64_t N1, int n_max, int groups,
+                         float* __restrict__ dW, int64_t ldw) {
+  extern __shared__ float s_col[];                         // S[o][:] = sum of the batch slices
+  for (int t = threadIdx.x; t < n_max; t += blockDim.x) {
+    float v = 0.f;
+    for (int z = 0; z < slices; ++z) v += S_part[((int64_t)z * N1 + blockIdx.x) * n_max + t];
+    s_col[t] = v;
+  }
   __syncthreads();
   float* out = dW + (int64_t)blockIdx.x * ldw;
   const int rows = n_max * groups;
@@ -140,28 +161,46 @@ extern "C" int gsc_mask_table(const float* W, int64_t ldw, int64_t N1, int n_max
   return GSC_OK;
 }
 
-extern "C" size_t gsc_mask_wgrad_workspace_bytes(int64_t N1, int n_max) { return (size_t)N1 * (size_t)n_max * 4; }
+// Batch slices of the binning pass: enough CTAs to cover the SMs, at least 64 rows each.
+static int mask_wgrad_slices(int64_t B, int64_t N1) {
+  int64_t z = ceil_div((int64_t)kNumSMs, ceil_div(N1, 32));
+  const int64_t by_rows = ceil_div(B > 0 ? B : 1, 64);
+  if (z > by_rows) z = by_rows;
+  if (z > 32) z = 32;
+  return z < 1 ? 1 : (int)z;
+}
+
+extern "C" size_t gsc_mask_wgrad_workspace_bytes(int64_t N1, int n_max) {
+  return (size_t)32 * (size_t)N1 * (size_t)n_max * 4;       // up to 32 batch slices of S
+}
 
 extern "C" int gsc_mask_wgrad(const float* dY, int64_t ldy, const int32_t* n, int64_t B, int64_t N1, int n_max,
                               int groups, float* dW, int64_t ldw, void* workspace, size_t workspace_bytes,
                               void* stream) {
   GSC_REQUIRE(dY && n && dW && workspace && B >= 0 && N1 >= 1 && n_max >= 1 && groups >= 1,
               "gsc_mask_wgrad: bad arguments");
-  GSC_REQUIRE(N1 <= 65535LL * 32 && n_max <= 48 * 1024 / 4, "gsc_mask_wgrad: N1=%lld / n_max=%d too large",
-              (long long)N1, n_max);
+  GSC_REQUIRE(n_max <= 48 * 1024 / 4, "gsc_mask_wgrad: n_max=%d too large", n_max);
   if (workspace_bytes < gsc_mask_wgrad_workspace_bytes(N1, n_max))
     return fail(GSC_EWORKSPACE, "gsc_mask_wgrad: workspace %zu < %zu", workspace_bytes,
                 gsc_mask_wgrad_workspace_bytes(N1, n_max));
+  int warps = (int)((200 * 1024) / ((size_t)(n_max + 1) * 32 * 4));
+  if (warps > 8) warps = 8;
+  GSC_REQUIRE(warps >= 1, "gsc_mask_wgrad: n_max=%d too large", n_max);
+  const size_t smem = (size_t)warps * (n_max + 1) * 32 * 4;
+  if (smem > 48 * 1024)
+    GSC_CUDA_TRY(cudaFuncSetAttribute(mask_wgrad_bins_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   float* S = (float*)workspace;
-  const dim3 gb((unsigned)ceil_div(N1, 32), (unsigned)ceil_div(n_max, 8));
-  mask_wgrad_bins_kernel<<<gb, 256, 0, (cudaStream_t)stream>>>(dY, ldy, n, B, N1, n_max, S);
+  const int slices = mask_wgrad_slices(B, N1);
+  const int64_t rows_per_slice = ceil_div(B > 0 ? B : 1, (int64_t)slices);
+  const dim3 gb((unsigned)ceil_div(N1, 32), (unsigned)slices);
+  mask_wgrad_bins_kernel<<<gb, warps * 32, smem, (cudaStream_t)stream>>>(dY, ldy, n, B, N1, n_max, rows_per_slice, S);
   GSC_LAUNCH_CHECK("mask_wgrad_bins_kernel");
   int64_t ysplit = ceil_div(4LL * kNumSMs, N1);             // ~4 CTAs per SM in total
   const int64_t row_groups = ceil_div((int64_t)n_max * groups, 8);
   if (ysplit > row_groups) ysplit = row_groups;
   if (ysplit < 1) ysplit = 1;
   const dim3 ge((unsigned)N1, (unsigned)ysplit);
-  mask_wgrad_expand_kernel<<<ge, 256, (size_t)n_max * 4, (cudaStream_t)stream>>>(S, n_max, groups, dW, ldw);
+  mask_wgrad_expand_kernel<<<ge, 256, (size_t)n_max * 4, (cudaStream_t)stream>>>(S, slices, N1, n_max, groups, dW, ldw);
   GSC_LAUNCH_CHECK("mask_wgrad_expand_kernel");
   return GSC_OK;
 }
