@@ -20,6 +20,7 @@ namespace gsc {
 
 constexpr int kGnnThreads = 256;
 constexpr int kColPerNode = 8;     // CSR entries staged in shared memory per node slot (else read from global)
+constexpr int kBwdEdgesPerNode = 7;  // gather backward: per-edge arrays (score, gradient, reverse index) per node slot
 constexpr float kNegSlope = 0.2f;  // GATv2Conv default negative_slope
 
 struct GnnArgs {
@@ -35,6 +36,7 @@ struct GnnArgs {
   float* rows_ws;         // bwd, large graphs only: [gridDim.x][5][cap][HP] node-row scratch in global memory
   float* dbg;             // optional phase timers (debug hook), nullptr in production
   const int32_t* stats;   // bwd: packer stats (stats[3] == 0 <=> symmetric graph), nullable
+  const int32_t* flags;   // bwd: flags[0] != 0 <=> some chunk's edges exceed the gather kernel's shared memory
   int gather_kernel_launched;   // bwd: the out-edge gather kernel handles symmetric graphs
   int64_t Nt;
   int64_t emb_ld;         // row stride of emb (fwd) / d_emb (bwd), floats
@@ -503,14 +505,19 @@ __global__ void __launch_bounds__(kGnnThreads, 2) gnn_fwd_tc_kernel(const GnnArg
     __syncthreads();
     // ---- global_mean_pool ----
     const float* hx = reinterpret_cast<const float*>(a_lo);
-    for (int t = tid; t < (g1 - g0) * HP; t += kGnnThreads) {
-      const int g = g0 + t / HP, c = t % HP;
-      if (c < p.H) {
-        const int n0 = p.graph_ptr[g] - nbase, n1 = p.graph_ptr[g + 1] - nbase;
-        float s = 0.f;
-        for (int i = n0; i < n1; ++i) s += hx[(size_t)i * HP + c];
-        p.emb[(size_t)g * p.emb_ld + c] = (n1 > n0) ? s / (float)(n1 - n0) : 0.f;
-      }
+    // eight lanes per (graph, channel): each adds every 8th node row, then a fixed shuffle tree
+    for (int base = 0; base < (g1 - g0) * HP * 8; base += kGnnThreads) {
+      const int pr = (base + tid) >> 3, part = tid & 7;
+      const bool ok = pr < (g1 - g0) * HP;
+      const int g = g0 + (ok ? pr / HP : 0), c = pr % HP;
+      const int n0 = p.graph_ptr[g] - nbase, n1 = p.graph_ptr[g + 1] - nbase;
+      float s = 0.f;
+      if (ok)
+        for (int i = n0 + part; i < n1; i += 8) s += hx[(size_t)i * HP + c];
+      s += __shfl_xor_sync(0xffffffffu, s, 1);
+      s += __shfl_xor_sync(0xffffffffu, s, 2);
+      s += __shfl_xor_sync(0xffffffffu, s, 4);
+      if (ok && part == 0 && c < p.H) p.emb[(size_t)g * p.emb_ld + c] = (n1 > n0) ? s / (float)(n1 - n0) : 0.f;
     }
     __syncthreads();
     GSC_TICK(5);
@@ -552,7 +559,7 @@ __global__ void __launch_bounds__(kGnnThreads, 1) gnn_bwd_kernel(const GnnArgs p
   float* dout_s = dxl_s + (size_t)p.cap * HP;               // [cap][HP] d_out of the current app
   float* hin_s = dout_s + (size_t)p.cap * HP;               // [cap][HP] input of the current app
   // symmetric batches are handled by gnn_bwd_tc_kernel (out-edge gather, no atomics)
-  if (p.gather_kernel_launched && p.stats != nullptr && p.stats[3] == 0) return;
+  if (p.gather_kernel_launched && p.stats != nullptr && p.stats[3] == 0 && p.flags[0] == 0) return;
 
   for (int cv = 0; cv < p.num_convs; ++cv)
     load_conv_weights<HP>(wsm + cv * L::kFloats, p.params + conv_param_offset(cv, p.in_dim, p.H),
@@ -796,6 +803,12 @@ struct TcB {
   __device__ __forceinline__ static int doff(int r, int c) { return (r >> 3) * kDGroup + c * 128 + (r & 7) * 16; }
 };
 
+// ds times the LeakyReLU branch sign of u: +ds for u > 0, -ds for u < 0 (one LOP3; u = +0 counts as
+// positive, which only the zero-padded channels ever hit, and those are multiplied by zero later).
+__device__ __forceinline__ float signed_by(float ds, float u) {
+  return __int_as_float(__float_as_int(ds) ^ (__float_as_int(u) & (int)0x80000000));
+}
+
 __device__ __forceinline__ void split4(const float4 v, float4& hi, float4& lo) {
   hi.x = to_tf32(v.x); lo.x = to_tf32(v.x - hi.x);
   hi.y = to_tf32(v.y); lo.y = to_tf32(v.y - hi.y);
@@ -811,24 +824,28 @@ __global__ void __launch_bounds__(kGnnThreads, 1) gnn_bwd_tc_kernel(const GnnArg
   const int tiles = p.cap / 128;
   uint8_t* convs = sm;
   uint8_t* h_hi = convs + p.num_convs * T::kConvBytes;
-  uint8_t* h_lo = h_hi + tiles * T::kHTile + 1024;
-  uint8_t* d_hi = h_lo + tiles * T::kHTile + 1024;
-  uint8_t* d_lo = d_hi + tiles * T::kDTile + 1024;
-  uint8_t* tail = d_lo + tiles * T::kDTile + 1024;
-  // Needs every edge's reverse in the same CSR: asymmetric batches go to gnn_bwd_kernel instead.
-  if (p.stats == nullptr || p.stats[3] != 0) return;
+  uint8_t* h_lo = h_hi + tiles * T::kHTile;
+  uint8_t* d_hi = h_lo + tiles * T::kHTile;
+  uint8_t* d_lo = d_hi + tiles * T::kDTile;
+  uint8_t* tail = d_lo + tiles * T::kDTile;
+  // Needs every edge's reverse in the same CSR and every chunk's edges in shared memory: other
+  // batches go to gnn_bwd_kernel instead (p.flags[0] is set by gnn_chunk_edges_kernel).
+  if (p.stats == nullptr || p.stats[3] != 0 || p.flags[0] != 0) return;
   // scratch that lives inside the (idle) dx operand buffers during the edge phase
   float* xl_s = reinterpret_cast<float*>(d_lo);                               // [cap][HP] xl, later d_xl
   float* g_s = reinterpret_cast<float*>(d_lo) + (size_t)p.cap * HP;           // [cap][HP] d_out / deg
   float* xr_s = reinterpret_cast<float*>(d_hi);                               // [cap][HP]
   float* dxr_raw = reinterpret_cast<float*>(d_hi) + (size_t)p.cap * HP;       // [cap][HP]
+  const int emax = kBwdEdgesPerNode * p.cap;
   int* gid_s = reinterpret_cast<int*>(tail);                                  // [cap] graph of every node
-  float4* st_s = reinterpret_cast<float4*>(tail + (size_t)p.cap * 4);         // [cap] softmax max, 1/sum, sum alpha*d_alpha
-  float2* pq_s = reinterpret_cast<float2*>(tail + (size_t)p.cap * 20);        // [cap] 0.6 att.xl_j, 0.6 att.xr_i
-  int* rp_s = reinterpret_cast<int*>(tail + (size_t)p.cap * 28);              // [cap + 4] chunk-local CSR row offsets
-  int* col_s = rp_s + p.cap + 4;                                              // [kColPerNode * cap]
-  int* perm_s = col_s + kColPerNode * p.cap;                                  // [cap] nodes by descending degree
-  int* hist_s = perm_s + p.cap;                                               // [64] degree histogram / cursors
+  float2* pq_s = reinterpret_cast<float2*>(gid_s + p.cap);                    // [cap] 0.6 att.xl_j, 0.6 att.xr_i
+  int* rp_s = reinterpret_cast<int*>(pq_s + p.cap);                           // [cap + 4] chunk-local CSR row offsets
+  float* es_s = reinterpret_cast<float*>(rp_s + p.cap + 4);                   // [emax] per edge: score, then alpha
+  float* eda_s = es_s + emax;                                                 // [emax] per edge: g_i.xl_j, then d_score
+  uint16_t* col_s = reinterpret_cast<uint16_t*>(eda_s + emax);                // [emax] chunk-local source of every edge
+  uint16_t* rev_s = col_s + emax;                                             // [emax] position of the reverse edge
+  uint16_t* perm_s = rev_s + emax;                                            // [cap] nodes by descending degree
+  int* hist_s = reinterpret_cast<int*>(perm_s + p.cap);                       // [64] degree histogram / cursors
   uint64_t* bar_ptr = reinterpret_cast<uint64_t*>(hist_s + 64);
   uint32_t* tslot = reinterpret_cast<uint32_t*>(bar_ptr + 1);
   const uint32_t bar = smem_u32(bar_ptr);
@@ -923,13 +940,9 @@ __global__ void __launch_bounds__(kGnnThreads, 1) gnn_bwd_tc_kernel(const GnnArg
     // order for the edge passes: lanes of a warp then run rows of similar length instead of all
     // waiting for the longest one.
     const int ebase = p.rowptr[nbase];
-    const int ne = p.rowptr[nbase + nc] - ebase;
-    const bool staged = ne <= kColPerNode * p.cap;
+    const int ne = p.rowptr[nbase + nc] - ebase;            // <= emax (checked by gnn_chunk_edges_kernel)
     for (int i = tid; i <= nc; i += kGnnThreads) rp_s[i] = p.rowptr[nbase + i] - ebase;
-    if (staged)
-      for (int e = tid; e < ne; e += kGnnThreads) col_s[e] = p.col[ebase + e] - nbase;
-    const int* colp = staged ? col_s : p.col + ebase;
-    const int coff = staged ? 0 : nbase;
+    for (int e = tid; e < ne; e += kGnnThreads) col_s[e] = (uint16_t)(p.col[ebase + e] - nbase);
     if (tid < 64) hist_s[tid] = 0;
     __syncthreads();
     for (int i = tid; i < nc; i += kGnnThreads) atomicAdd(hist_s + 63 - min(rp_s[i + 1] - rp_s[i], 63), 1);
@@ -947,7 +960,22 @@ __global__ void __launch_bounds__(kGnnThreads, 1) gnn_bwd_tc_kernel(const GnnArg
     }
     __syncthreads();
     for (int i = tid; i < nc; i += kGnnThreads)
-      perm_s[atomicAdd(hist_s + 63 - min(rp_s[i + 1] - rp_s[i], 63), 1)] = i;
+      perm_s[atomicAdd(hist_s + 63 - min(rp_s[i + 1] - rp_s[i], 63), 1)] = (uint16_t)i;
+    // Reverse-edge index: the edge j -> i stored at position e of row i has its reverse i -> j in row j
+    // (the graph is symmetric); parallel edges pair up in order of occurrence.  The source pass reads
+    // the attention weight and score gradient the target pass left at that position.
+    for (int i = tid; i < nc; i += kGnnThreads) {
+      const int e0 = rp_s[i], e1 = rp_s[i + 1];
+      for (int e = e0; e < e1; ++e) {
+        const int j = col_s[e];
+        int k = 0;
+        for (int q = e0; q < e; ++q) k += (col_s[q] == j);
+        int r = e;
+        for (int q = rp_s[j]; q < rp_s[j + 1]; ++q)
+          if (col_s[q] == i && k-- == 0) { r = q; break; }
+        rev_s[e] = (uint16_t)r;
+      }
+    }
 
     for (int a = p.num_apps - 1; a >= 0; --a) {
       const int cv = p.app_conv[a];
@@ -1058,99 +1086,108 @@ __global__ void __launch_bounds__(kGnnThreads, 1) gnn_bwd_tc_kernel(const GnnArg
       __syncthreads();
       GSC_TICK(3);
 
-      // ---- 4T. target side: softmax statistics, d_att, d_xr (gather over in-edges) ----
-      {
+      // ---- 4T. target side (gather over in-edges): softmax statistics, attention weight alpha_e and
+      //      score gradient ds_e of every edge (left in es_s / eda_s for the source pass), d_xr.
+      //      With lrelu(u) = (0.6 + 0.4 sgn u) u and w_c = sum_e ds_e (0.6 + 0.4 sgn u_e,c):
+      //        d_xr_i,c = att_c w_in_i,c        d_xl_j,c = sum_e alpha_e g_i,c + att_c w_out_j,c
+      //        d_att_c  = sum_i xr_i,c w_in_i,c + sum_j xl_j,c w_out_j,c
+      //      so the only per-edge, per-channel work of the two gradient loops is the sign sum. ----
       float datt[HP];
 #pragma unroll
       for (int c = 0; c < HP; ++c) datt[c] = 0.f;
       for (int t = tid; t < nc; t += kGnnThreads) {
         const int i = perm_s[t];
-        float xr[HP], g[HP], b[HP], sg[HP];
+        float xr[HP], sg[HP];
         load_row<HP>(xr_s + (size_t)i * HP, xr);
-        load_row<HP>(g_s + (size_t)i * HP, g);
-        load_row<HP>(vec + 2 * HP, b);
-#pragma unroll
-        for (int c = 0; c < HP; ++c) { b[c] *= 0.4f; sg[c] = 0.f; }
         const float q_i = pq_s[i].y;
         const int e0 = rp_s[i], e1 = rp_s[i + 1];
         float m = -INFINITY, l = 0.f, dot = 0.f;
-        for (int e = e0; e < e1; ++e) {
-          const int j = colp[e] - coff;
-          float v[HP];
-          load_row<HP>(xl_s + (size_t)j * HP, v);
-          const float s = pq_s[j].x + q_i + abs_score<HP>(v, xr, b);
-          const float da = dot4<HP>(g, v);
-          const float m_new = fmaxf(m, s);
-          const float sc = __expf(m - m_new);
-          const float pe = __expf(s - m_new);
-          l = fmaf(l, sc, pe);
-          dot = fmaf(dot, sc, pe * da);
-          m = m_new;
+        {
+          float g[HP], b[HP];
+          load_row<HP>(g_s + (size_t)i * HP, g);
+          load_row<HP>(vec + 2 * HP, b);
+#pragma unroll
+          for (int c = 0; c < HP; ++c) b[c] *= 0.4f;
+          for (int e = e0; e < e1; ++e) {
+            const int j = col_s[e];
+            float v[HP];
+            load_row<HP>(xl_s + (size_t)j * HP, v);
+            const float sc_e = pq_s[j].x + q_i + abs_score<HP>(v, xr, b);
+            const float da = dot4<HP>(g, v);
+            es_s[e] = sc_e;
+            eda_s[e] = da;
+            const float m_new = fmaxf(m, sc_e);
+            const float sc = __expf(m - m_new);
+            const float pe = __expf(sc_e - m_new);
+            l = fmaf(l, sc, pe);
+            dot = fmaf(dot, sc, pe * da);
+            m = m_new;
+          }
         }
         const float inv_l = 1.f / (l + 1e-16f);
         dot *= inv_l;
-        st_s[i] = make_float4(m, inv_l, dot, 0.f);
         float ds_sum = 0.f;
+#pragma unroll
+        for (int c = 0; c < HP; ++c) sg[c] = 0.f;
         for (int e = e0; e < e1; ++e) {
-          const int j = colp[e] - coff;
+          const int j = col_s[e];
           float v[HP];
           load_row<HP>(xl_s + (size_t)j * HP, v);
-          const float s = pq_s[j].x + q_i + abs_score<HP>(v, xr, b);
-          const float da = dot4<HP>(g, v);
-          const float ds = __expf(s - m) * inv_l * (da - dot);
+          const float alpha = __expf(es_s[e] - m) * inv_l;
+          const float ds = alpha * (eda_s[e] - dot);
+          es_s[e] = alpha;
+          eda_s[e] = ds;
+          ds_sum += ds;
+#pragma unroll
+          for (int c = 0; c < HP; ++c) sg[c] += signed_by(ds, v[c] + xr[c]);
+        }
+        const float base = 0.6f * ds_sum;
+#pragma unroll
+        for (int c = 0; c < HP; ++c) {
+          const float w = fmaf(0.4f, sg[c], base);
+          datt[c] = fmaf(xr[c], w, datt[c]);
+          sg[c] = vec[2 * HP + c] * w;
+        }
+        store_row<HP>(dxr_raw + (size_t)i * HP, sg);
+      }
+      __syncthreads();
+      GSC_TICK(8);
+      // ---- 4S. source side: d_xl_j over the out-edges j -> i; the graph is symmetric, so they are the
+      //      entries of j's own CSR row and rev_s points at what the target pass computed for them ----
+      for (int t = tid; t < nc; t += kGnnThreads) {
+        const int j = perm_s[t];
+        float v[HP], dxl[HP], sg[HP];
+        load_row<HP>(xl_s + (size_t)j * HP, v);
+#pragma unroll
+        for (int c = 0; c < HP; ++c) { dxl[c] = 0.f; sg[c] = 0.f; }
+        float ds_sum = 0.f;
+        const int e0 = rp_s[j], e1 = rp_s[j + 1];
+        for (int e = e0; e < e1; ++e) {
+          const int i = col_s[e], r = rev_s[e];
+          const float alpha = es_s[r], ds = eda_s[r];
+          float xr[HP], g[HP];
+          load_row<HP>(xr_s + (size_t)i * HP, xr);
+          load_row<HP>(g_s + (size_t)i * HP, g);
           ds_sum += ds;
 #pragma unroll
           for (int c = 0; c < HP; ++c) {
-            const float u = v[c] + xr[c];
-            datt[c] = fmaf(ds, fmaxf(u, kNegSlope * u), datt[c]);         // d_att += ds * lrelu(u)
-            sg[c] += (u > 0.f) ? ds : -ds;                                 // sum of ds * sign(u)
+            dxl[c] = fmaf(alpha, g[c], dxl[c]);
+            sg[c] += signed_by(ds, v[c] + xr[c]);
           }
         }
-        // d_xr_c = att_c * sum_e ds_e * lrelu'(u_e,c),  lrelu' = 0.6 + 0.4 sign   (b = 0.4 att)
+        const float base = 0.6f * ds_sum;
 #pragma unroll
-        for (int c = 0; c < HP; ++c) sg[c] = b[c] * fmaf(1.5f, ds_sum, sg[c]);
-        store_row<HP>(dxr_raw + (size_t)i * HP, sg);
+        for (int c = 0; c < HP; ++c) {
+          const float w = fmaf(0.4f, sg[c], base);
+          datt[c] = fmaf(v[c], w, datt[c]);
+          dxl[c] = fmaf(vec[2 * HP + c], w, dxl[c]);
+        }
+        store_row<HP>(xl_s + (size_t)j * HP, dxl);       // own row: xl_j is not needed any more
       }
 #pragma unroll
       for (int c = 0; c < HP; ++c) {
         const float sa = warp_sum(datt[c]);
         if (lane == (c & 31)) vec[4 * HP + (warp * 2) * HP + c] += sa;          // warp-private slot
-      }
-      }
-      __syncthreads();
-      GSC_TICK(8);
-      // ---- 4S. source side: d_xl_j = sum over out-edges j->i of (alpha_ij g_i + d_u_ij); the graph is
-      //      symmetric, so the out-neighbours of j are the entries of its own CSR row ----
-      for (int t = tid; t < nc; t += kGnnThreads) {
-        const int j = perm_s[t];
-        float v[HP], b[HP], dxl[HP], sg[HP];
-        load_row<HP>(xl_s + (size_t)j * HP, v);
-        load_row<HP>(vec + 2 * HP, b);
-#pragma unroll
-        for (int c = 0; c < HP; ++c) { b[c] *= 0.4f; dxl[c] = 0.f; sg[c] = 0.f; }
-        const float p_j = pq_s[j].x;
-        float ds_sum = 0.f;
-        const int e0 = rp_s[j], e1 = rp_s[j + 1];
-        for (int e = e0; e < e1; ++e) {
-          const int i = colp[e] - coff;
-          float xr[HP], g[HP];
-          load_row<HP>(xr_s + (size_t)i * HP, xr);
-          load_row<HP>(g_s + (size_t)i * HP, g);
-          const float4 st = st_s[i];
-          const float s = p_j + pq_s[i].y + abs_score<HP>(v, xr, b);
-          const float da = dot4<HP>(g, v);
-          const float alpha = __expf(s - st.x) * st.y;
-          const float ds = alpha * (da - st.z);
-          ds_sum += ds;
-#pragma unroll
-          for (int c = 0; c < HP; ++c) {
-            dxl[c] = fmaf(alpha, g[c], dxl[c]);
-            sg[c] += (v[c] + xr[c] > 0.f) ? ds : -ds;
-          }
-        }
-#pragma unroll
-        for (int c = 0; c < HP; ++c) dxl[c] = fmaf(b[c], fmaf(1.5f, ds_sum, sg[c]), dxl[c]);
-        store_row<HP>(xl_s + (size_t)j * HP, dxl);       // own row: xl_j is not needed any more
       }
       __syncthreads();
       GSC_TICK(4);
@@ -1311,6 +1348,17 @@ __global__ void __launch_bounds__(kGnnThreads, 1) gnn_bwd_tc_kernel(const GnnArg
   }
 }
 
+// flags[0] := 1 if some chunk of G graphs holds more edges (self-loops included) than the gather
+// backward can stage in shared memory; both backward kernels read it to decide which of them runs.
+__global__ void gnn_chunk_edges_kernel(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ graph_ptr,
+                                       int B, int G, int emax, int32_t* __restrict__ flags) {
+  const int num_chunks = (B + G - 1) / G;
+  for (int ch = blockIdx.x * blockDim.x + threadIdx.x; ch < num_chunks; ch += gridDim.x * blockDim.x) {
+    const int g0 = ch * G, g1 = min(B, g0 + G);
+    if (rowptr[graph_ptr[g1]] - rowptr[graph_ptr[g0]] > emax) flags[0] = 1;
+  }
+}
+
 // d_params[t] = sum of the CTA partials, in a fixed order: block = 32 parameters x 8 partial-lanes,
 // lane r adds the partials r, r + 8, ... (independent loads in flight), then the lanes are added.
 __global__ void __launch_bounds__(256)
@@ -1437,9 +1485,9 @@ static bool plan_bwd_tc(const GnnArgs& a, int max_nodes, int* cap, int* cols, si
   *cap = max_nodes <= kGnnThreads ? kGnnThreads : (max_nodes + 127) / 128 * 128;
   const int tiles = *cap / 128;
   if (*cap > 384) return false;     // two node slots per thread; the atomic kernel must fit as well
-  *smem = (size_t)a.num_convs * T::kConvBytes + 2 * ((size_t)tiles * T::kHTile + 1024) +
-          2 * ((size_t)tiles * T::kDTile + 1024) + (size_t)*cap * 28 +
-          ((size_t)*cap + 4 + (size_t)kColPerNode * *cap + (size_t)*cap + 64) * 4 + 16;
+  const size_t emax = (size_t)kBwdEdgesPerNode * *cap;
+  *smem = (size_t)a.num_convs * T::kConvBytes + 2 * (size_t)tiles * T::kHTile + 2 * (size_t)tiles * T::kDTile +
+          (size_t)*cap * (4 + 8 + 4 + 2) + 16 + emax * (4 + 4 + 2 + 2) + 64 * 4 + 16;
   const int need_cols = tiles * (T::kN1 + T::kNH);
   *cols = 32;
   while (*cols < need_cols) *cols *= 2;
@@ -1457,10 +1505,15 @@ static int launch_bwd_both(GnnArgs a, int max_nodes, float* d_params, cudaStream
   size_t smem_t = 0;
   const bool tc = gnn_use_tc() && a.stats != nullptr && plan_bwd_tc<HP>(a, max_nodes, &cap_t, &cols, &smem_t);
   int grid = grid_f;
+  GSC_CUDA_TRY(cudaMemsetAsync(const_cast<int32_t*>(a.flags), 0, sizeof(int32_t), st));
   if (tc) {
     GnnArgs t = a;
     t.cap = cap_t;
     t.G = graphs_per_cta(cap_t, max_nodes, t.B, 1);
+    const int chunks_t = (t.B + t.G - 1) / t.G;
+    gnn_chunk_edges_kernel<<<(chunks_t + 255) / 256, 256, 0, st>>>(t.rowptr, t.graph_ptr, t.B, t.G,
+                                                                   kBwdEdgesPerNode * cap_t, const_cast<int32_t*>(a.flags));
+    GSC_LAUNCH_CHECK("gnn_chunk_edges_kernel");
     const int grid_t = bwd_grid(t.B, t.G);
     grid = grid_t > grid_f ? grid_t : grid_f;      // one partial per CTA of either kernel
     GSC_CUDA_TRY(cudaFuncSetAttribute(gnn_bwd_tc_kernel<HP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_t));
@@ -1532,6 +1585,7 @@ extern "C" int gsc_gnn_embed_fwd(const float* x, int64_t Nt, int in_dim, const i
 static size_t bwd_partials_bytes(int in_dim, int H, int num_layers) {
   return ((size_t)kNumSMs * (size_t)conv_param_offset(num_layers, in_dim, H) * 4 + 255) / 256 * 256;
 }
+constexpr size_t kBwdFlagBytes = 256;    // kernel-selection flags, between the partials and the node-row scratch
 static bool bwd_rows_in_global(int max_nodes, int H, int num_layers) {
   const int hp = pick_hp(H);
   const size_t cap = max_nodes <= kGnnThreads ? kGnnThreads : ((size_t)max_nodes + 31) / 32 * 32;
@@ -1543,7 +1597,7 @@ static bool bwd_rows_in_global(int max_nodes, int H, int num_layers) {
 extern "C" size_t gsc_gnn_bwd_workspace_bytes(int64_t B, int max_nodes, int in_dim, int H, int num_layers) {
   (void)B;
   if (max_nodes < 1 || H < 1 || H > GSC_MAX_HIDDEN || num_layers < 1) return 0;
-  size_t bytes = bwd_partials_bytes(in_dim, H, num_layers);
+  size_t bytes = bwd_partials_bytes(in_dim, H, num_layers) + kBwdFlagBytes;
   if (bwd_rows_in_global(max_nodes, H, num_layers)) {
     const size_t cap = ((size_t)max_nodes + 31) / 32 * 32;
     bytes += (size_t)kNumSMs * 5 * cap * pick_hp(H) * 4;
@@ -1566,7 +1620,8 @@ extern "C" int gsc_gnn_embed_bwd(const float* x, int64_t Nt, int in_dim, const i
     return fail(GSC_EWORKSPACE, "gnn bwd: workspace %zu < %zu", workspace_bytes,
                 gsc_gnn_bwd_workspace_bytes(B, max_nodes, in_dim, H, num_layers));
   a.saved = const_cast<float*>(saved); a.d_emb = d_emb; a.partials = (float*)workspace;
-  a.rows_ws = reinterpret_cast<float*>(static_cast<uint8_t*>(workspace) + bwd_partials_bytes(in_dim, H, num_layers));
+  a.flags = reinterpret_cast<const int32_t*>(static_cast<uint8_t*>(workspace) + bwd_partials_bytes(in_dim, H, num_layers));
+  a.rows_ws = reinterpret_cast<float*>(static_cast<uint8_t*>(workspace) + bwd_partials_bytes(in_dim, H, num_layers) + kBwdFlagBytes);
   a.dbg = g_gnn_debug;
   a.stats = pack_stats;
   cudaStream_t st = (cudaStream_t)stream;
