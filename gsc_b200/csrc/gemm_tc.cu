@@ -88,6 +88,34 @@ struct SmaskWalk {
   }
 };
 
+// Bit q of the result: is column col0 + q inside the structured mask of an nb-node state?  For
+// n_max >= 32 a run of 32 columns crosses at most one (source, group) boundary, so two range tests
+// replace 32 walks; smaller n_max walks the run.
+__device__ __forceinline__ uint32_t low_bits(int k) { return k >= 32 ? 0xffffffffu : (k <= 0 ? 0u : ((1u << k) - 1u)); }
+__device__ __forceinline__ uint32_t smask_bits(const TcParams& p, int nb, int col0) {
+  const int nm = p.n_max, gn = p.groups * p.n_max;
+  int src = (int)((uint32_t)col0 / (uint32_t)gn);
+  int rem = col0 - src * gn;
+  int dst = (int)((uint32_t)rem % (uint32_t)nm);
+  if (nm >= 32) {
+    const int first = min(32, nm - dst);                       // columns before the next group boundary
+    uint32_t bits = src < nb ? low_bits(min(nb - dst, first)) : 0u;
+    if (first < 32) {
+      if (rem + first == gn) ++src;                            // the boundary also ends the source row
+      if (src < nb) bits |= low_bits(min(nb, 32 - first)) << first;
+    }
+    return bits;
+  }
+  uint32_t bits = 0;
+#pragma unroll 1
+  for (int q = 0; q < 32; ++q) {
+    bits |= (uint32_t)(src < nb && dst < nb) << q;
+    if (++dst == nm) dst = 0;
+    if (++rem == gn) { rem = 0; ++src; }
+  }
+  return bits;
+}
+
 __device__ __forceinline__ float tc_epilogue(const TcParams& p, float v, int64_t i, int64_t j) {
   if (p.flags & GSC_EPI_ROWTABLE) v += p.row_table[(int64_t)p.row_n[i] * p.ld_table + j];
   if (p.flags & GSC_EPI_BIAS) v += p.bias[j];
@@ -248,59 +276,68 @@ gemm_tc_kernel(const __grid_constant__ TcParams p, const __grid_constant__ CUten
         if (p.epi_kind) mbar_wait(efull_bar, (uint32_t)iter & 1u);
         const int lrow = quad * 32 + lane;
         const int64_t grow = (int64_t)it.m0 + lrow;
-        const int nb = ((p.flags & (GSC_EPI_ROWTABLE | GSC_EPI_SMASK)) && grow < p.M) ? p.row_n[grow] : 0;
-        const float* trow = (p.flags & GSC_EPI_ROWTABLE) ? p.row_table + (int64_t)nb * p.ld_table : nullptr;
-        const bool vec_ok = (!(p.flags & GSC_EPI_ROWTABLE) || ((reinterpret_cast<uintptr_t>(trow) & 15) == 0)) &&
-                            (!(p.flags & GSC_EPI_BIAS) || ((reinterpret_cast<uintptr_t>(p.bias) & 15) == 0));
+        const bool f_table = p.flags & GSC_EPI_ROWTABLE, f_bias = p.flags & GSC_EPI_BIAS;
+        const bool f_relu = p.flags & GSC_EPI_RELU, f_smask = p.flags & GSC_EPI_SMASK;
+        const bool f_clamp = p.flags & GSC_EPI_CLAMP1;
+        const bool f_gate_direct = (p.flags & GSC_EPI_GATE) && p.epi_kind != 2;
+        const int nb = ((f_table || f_smask) && grow < p.M) ? p.row_n[grow] : 0;
+        const float* trow = f_table ? p.row_table + (int64_t)nb * p.ld_table : nullptr;
+        const bool vec_ok = (!f_table || ((reinterpret_cast<uintptr_t>(trow) & 15) == 0)) &&
+                            (!f_bias || ((reinterpret_cast<uintptr_t>(p.bias) & 15) == 0));
+        const int ncols = (int)p.N;                                  // the tensor-core path requires N < 2^31
 #pragma unroll 1
         for (int c = c_begin; c < c_end; ++c) {
+          const int col0 = it.n0 + c * 32;
+          // Columns past N compute garbage that the TMA store clips; only their loads are guarded.
+          // Additive per-column terms (bias, per-n table row) are fetched before waiting for TMEM.
+          float add[32];
+#pragma unroll
+          for (int q = 0; q < 32; ++q) add[q] = 0.f;
+          if (f_table || f_bias) {
+            if (vec_ok && col0 + 32 <= ncols) {
+#pragma unroll
+              for (int q = 0; q < 8; ++q) {
+                if (f_table) {
+                  const float4 t4 = *reinterpret_cast<const float4*>(trow + col0 + 4 * q);
+                  add[4 * q] += t4.x; add[4 * q + 1] += t4.y; add[4 * q + 2] += t4.z; add[4 * q + 3] += t4.w;
+                }
+                if (f_bias) {
+                  const float4 b4 = *reinterpret_cast<const float4*>(p.bias + col0 + 4 * q);
+                  add[4 * q] += b4.x; add[4 * q + 1] += b4.y; add[4 * q + 2] += b4.z; add[4 * q + 3] += b4.w;
+                }
+              }
+            } else {
+#pragma unroll
+              for (int q = 0; q < 32; ++q) {
+                const int cc = min(col0 + q, ncols - 1);
+                if (f_table) add[q] += trow[cc];
+                if (f_bias) add[q] += p.bias[cc];
+              }
+            }
+          }
+          const uint32_t keep = f_smask ? smask_bits(p, nb, col0) : 0xffffffffu;
           float v[32];
           tc_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(as * kTcBN + c * 32), v);
           const uint32_t rbase = ebuf + c * 16384 + lrow * 128;
-          const int64_t col0 = (int64_t)it.n0 + c * 32;
-          SmaskWalk walk;
-          if (p.flags & GSC_EPI_SMASK) walk.seek(p, col0);
 #pragma unroll
           for (int q = 0; q < 8; ++q) {
             const uint32_t addr = rbase + (uint32_t)((q ^ (lrow & 7)) << 4);          // 128 B swizzle
             float4 e = make_float4(0.f, 0.f, 0.f, 0.f);
             if (p.epi_kind) asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(e.x), "=f"(e.y), "=f"(e.z), "=f"(e.w) : "r"(addr));
-            float o[4] = {v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]};
             const float ev[4] = {e.x, e.y, e.z, e.w};
-            // additive per-column terms (bias, per-n table row): one 128-bit load per four columns
-            float add[4] = {0.f, 0.f, 0.f, 0.f};
-            if (p.flags & (GSC_EPI_ROWTABLE | GSC_EPI_BIAS)) {
-              const int64_t cq = col0 + 4 * q;
-              if (vec_ok && cq + 4 <= p.N) {
-                if (p.flags & GSC_EPI_ROWTABLE) {
-                  const float4 t4 = *reinterpret_cast<const float4*>(trow + cq);
-                  add[0] += t4.x; add[1] += t4.y; add[2] += t4.z; add[3] += t4.w;
-                }
-                if (p.flags & GSC_EPI_BIAS) {
-                  const float4 b4 = *reinterpret_cast<const float4*>(p.bias + cq);
-                  add[0] += b4.x; add[1] += b4.y; add[2] += b4.z; add[3] += b4.w;
-                }
-              } else {
-#pragma unroll
-                for (int u = 0; u < 4; ++u)
-                  if (cq + u < p.N) {
-                    if (p.flags & GSC_EPI_ROWTABLE) add[u] += trow[cq + u];
-                    if (p.flags & GSC_EPI_BIAS) add[u] += p.bias[cq + u];
-                  }
-              }
-            }
+            float o[4];
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
-              const int64_t col = col0 + 4 * q + u;
-              float t = o[u] + add[u];
-              if (p.flags & GSC_EPI_RELU) t = fmaxf(t, 0.f);
+              float t = v[4 * q + u] + add[4 * q + u];
+              if (f_relu) t = fmaxf(t, 0.f);
               if (p.epi_kind == 1) t *= ev[u];
-              if (p.flags & GSC_EPI_SMASK) t = walk.next(nb) ? t : 0.f;
-              if (p.flags & GSC_EPI_GATE) {
-                if (p.epi_kind == 2) t = ev[u] > 0.f ? t : 0.f;
-                else if (grow < p.M && col < p.N) t = p.gate[grow * p.ld_gate + col] > 0.f ? t : 0.f;
+              if (f_smask) t = ((keep >> (4 * q + u)) & 1u) ? t : 0.f;
+              if (p.epi_kind == 2) t = ev[u] > 0.f ? t : 0.f;
+              if (f_gate_direct) {
+                const int col = col0 + 4 * q + u;
+                if (grow < p.M && col < ncols) t = p.gate[grow * p.ld_gate + col] > 0.f ? t : 0.f;
               }
-              if (p.flags & GSC_EPI_CLAMP1) t = fminf(fmaxf(t, -1.f), 1.f);
+              if (f_clamp) t = fminf(fmaxf(t, -1.f), 1.f);
               o[u] = t;
             }
             asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(o[0]), "f"(o[1]), "f"(o[2]), "f"(o[3]) : "memory");
@@ -413,7 +450,7 @@ static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 
 // Can this problem run on the TMA-fed tensor-core kernel?  (16-byte aligned bases, row strides
 // that are multiples of 4 floats, a consistent major-ness across segments.)
 bool gemm_tc_supported(const gsc_gemm_args* a, int64_t M, int64_t N, bool* a_mn, bool* b_mn) {
-  if (M < 1 || N < 8) return false;
+  if (M < 1 || N < 8 || N > INT32_MAX - 256 || M > INT32_MAX - 256) return false;   // tile coordinates are ints
   bool amn = false, bmn = false;
   for (int s = 0; s < a->num_seg; ++s) {
     if (a->K[s] <= 0) return false;
