@@ -173,7 +173,7 @@ gemm_tc_kernel(const __grid_constant__ TcParams p, const __grid_constant__ CUten
     for (int s = 0; s < kTcStages; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
     for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), kTcEpiWarps); }
     mbar_init(efull_bar, 1);
-    mbar_init(eempty_bar, 1);
+    mbar_init(eempty_bar, 2);                     // both column halves release the mask/gate tile
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 2) {   // one warp allocates TMEM (256 columns) and later frees it
@@ -290,28 +290,28 @@ gemm_tc_kernel(const __grid_constant__ TcParams p, const __grid_constant__ CUten
           const int col0 = it.n0 + c * 32;
           // Columns past N compute garbage that the TMA store clips; only their loads are guarded.
           // Additive per-column terms (bias, per-n table row) are fetched before waiting for TMEM.
-          float add[32];
+          float tadd[32], badd[32];                          // raw loads: consumed only after the TMEM wait
 #pragma unroll
-          for (int q = 0; q < 32; ++q) add[q] = 0.f;
+          for (int q = 0; q < 32; ++q) { tadd[q] = 0.f; badd[q] = 0.f; }
           if (f_table || f_bias) {
             if (vec_ok && col0 + 32 <= ncols) {
 #pragma unroll
               for (int q = 0; q < 8; ++q) {
                 if (f_table) {
                   const float4 t4 = *reinterpret_cast<const float4*>(trow + col0 + 4 * q);
-                  add[4 * q] += t4.x; add[4 * q + 1] += t4.y; add[4 * q + 2] += t4.z; add[4 * q + 3] += t4.w;
+                  tadd[4 * q] = t4.x; tadd[4 * q + 1] = t4.y; tadd[4 * q + 2] = t4.z; tadd[4 * q + 3] = t4.w;
                 }
                 if (f_bias) {
                   const float4 b4 = *reinterpret_cast<const float4*>(p.bias + col0 + 4 * q);
-                  add[4 * q] += b4.x; add[4 * q + 1] += b4.y; add[4 * q + 2] += b4.z; add[4 * q + 3] += b4.w;
+                  badd[4 * q] = b4.x; badd[4 * q + 1] = b4.y; badd[4 * q + 2] = b4.z; badd[4 * q + 3] = b4.w;
                 }
               }
             } else {
 #pragma unroll
               for (int q = 0; q < 32; ++q) {
                 const int cc = min(col0 + q, ncols - 1);
-                if (f_table) add[q] += trow[cc];
-                if (f_bias) add[q] += p.bias[cc];
+                if (f_table) tadd[q] = trow[cc];
+                if (f_bias) badd[q] = p.bias[cc];
               }
             }
           }
@@ -328,7 +328,7 @@ gemm_tc_kernel(const __grid_constant__ TcParams p, const __grid_constant__ CUten
             float o[4];
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
-              float t = v[4 * q + u] + add[4 * q + u];
+              float t = (v[4 * q + u] + tadd[4 * q + u]) + badd[4 * q + u];
               if (f_relu) t = fmaxf(t, 0.f);
               if (p.epi_kind == 1) t *= ev[u];
               if (f_smask) t = ((keep >> (4 * q + u)) & 1u) ? t : 0.f;
@@ -347,10 +347,13 @@ gemm_tc_kernel(const __grid_constant__ TcParams p, const __grid_constant__ CUten
         __syncwarp();
         if (lane == 0) mbar_arrive(tempty_bar(as));                 // accumulator buffer is free again
         fence_proxy_async_smem();                                    // st.shared -> visible to the TMA store
-        asm volatile("bar.sync 1, 256;" ::: "memory");
-        if (warp == 2 && lane == 0) {
-#pragma unroll
-          for (int c = 0; c < kTcBN / 32; ++c)
+        // the two column halves (warps 2..5 / 6..9) own their half of the tile buffer, their own named
+        // barrier and their own TMA store: one half computes while the other drains
+        const int half = (warp - 2) >> 2;
+        asm volatile("bar.sync %0, 128;" ::"r"(1 + half) : "memory");
+        if (((warp - 2) & 3) == 0 && lane == 0) {
+#pragma unroll 1
+          for (int c = c_begin; c < c_end; ++c)
             if (it.n0 + 32 * c < p.N)
               asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(
                                reinterpret_cast<uint64_t>(&mapC)), "r"(ebuf + c * 16384), "r"(it.n0 + 32 * c), "r"(it.m0) : "memory");
@@ -358,7 +361,7 @@ gemm_tc_kernel(const __grid_constant__ TcParams p, const __grid_constant__ CUten
           asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // smem tile may be overwritten
           if (p.epi_kind) mbar_arrive(eempty_bar);
         }
-        asm volatile("bar.sync 1, 256;" ::: "memory");
+        asm volatile("bar.sync %0, 128;" ::"r"(1 + half) : "memory");
         continue;
       }
       const int64_t row = (int64_t)it.m0 + quad * 32 + lane;
@@ -399,7 +402,7 @@ gemm_tc_kernel(const __grid_constant__ TcParams p, const __grid_constant__ CUten
     }
   }
 
-  if (warp == 2 && lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+  if ((warp == 2 || warp == 6) && lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
   tc_fence_before();
   __syncthreads();
   if (warp == 2) {
