@@ -296,3 +296,17 @@ def test_config2_full_size_properties():
     sub = GraphBatch.from_data_list([GraphData(**st.graph(int(i))) for i in perm]).to(DEV)
     y_sub = ddpg.predict(actor, sub).cpu().numpy()
     assert rel_err(y_sub, yh[perm]) < 1e-5
+
+
+def test_graphed_predict_equals_eager_predict():
+    n_max, B = 24, 96
+    st = synth.make_states(B, n_max, 16, 24, seed=12, num_topologies=6)
+    st2 = synth.make_states(B, n_max, 16, 24, seed=12, num_topologies=6)
+    st2.x = np.random.default_rng(3).random(st.x.shape, dtype=np.float32)     # same topologies, new features
+    actor = Actor(AgentSpec(n_max)).to(DEV)
+    gb = GraphBatch.from_states(st, dense_mask=False).to(DEV)
+    gp = ddpg.GraphedPredict(actor, gb)
+    assert torch.equal(gp.replay(), ddpg.predict(actor, gb.view()))
+    gb2 = GraphBatch.from_states(st2, dense_mask=False).to(DEV)
+    gp.load(gb2)
+    assert torch.equal(gp.replay(), ddpg.predict(actor, gb2))
