@@ -199,7 +199,7 @@ def run_ours(args):
     torch.cuda.synchronize()
     if w["kind"] == "c2" and args.graph:
         gpredict = ddpg.GraphedPredict(actor, resident["cur"])
-    use_graph = w["kind"] == "c3" and args.graph and world == 1
+    use_graph = w["kind"] == "c3" and args.graph
     if use_graph:
         graphed = ddpg.GraphedUpdate(upd, resident["cur"], resident["nxt"], resident["actions"],
                                      resident["rewards"], resident["dones"])
@@ -389,6 +389,14 @@ def run_ours(args):
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()
+        torch.cuda.synchronize()
+        if graphed is not None:
+            # A captured graph keeps the communicator's resources alive and destroy_process_group() then
+            # waits forever (observed with torch 2.11 / NCCL 2.28): everything is printed and every
+            # rank has passed the barrier, so leave without the teardown.
+            sys.stdout.flush()
+            sys.stderr.flush()
+            os._exit(0)
         dist.destroy_process_group()
 
 

@@ -129,12 +129,12 @@ class GraphedUpdate:
     launches, ~60 kernels) becomes one graph launch, which removes the per-launch host overhead that
     dominates at the reference's batch size of 100.  The batch lives in STATIC device tensors
     (``self.cur``, ``self.nxt``, ``self.actions``, ``self.rewards``, ``self.dones``): write the next
-    minibatch into them (``load``) and call ``replay``.  Shapes (B, Nt, E) are frozen at capture."""
+    minibatch into them (``load``) and call ``replay``.  Shapes (B, Nt, E) are frozen at capture.
+    Under data parallelism the NCCL collectives of the update are captured too (every rank must
+    capture and replay in step); destroy the object before ``destroy_process_group()``."""
 
     def __init__(self, upd: DDPGUpdater, cur: GraphBatch, nxt: GraphBatch, actions, rewards, dones,
                  warmup: int = 2):
-        if upd.world_size > 1:
-            raise RuntimeError("GraphedUpdate: single-process updates only (the data-parallel step runs eagerly)")
         self.upd = upd
         cl = lambda t: None if t is None else t.clone()
         mk = lambda gb, share=None: GraphBatch(
