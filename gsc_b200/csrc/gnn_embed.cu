@@ -505,18 +505,24 @@ __global__ void __launch_bounds__(kGnnThreads, 2) gnn_fwd_tc_kernel(const GnnArg
     __syncthreads();
     // ---- global_mean_pool ----
     const float* hx = reinterpret_cast<const float*>(a_lo);
-    // eight lanes per (graph, channel): each adds every 8th node row, then a fixed shuffle tree
-    for (int base = 0; base < (g1 - g0) * HP * 8; base += kGnnThreads) {
-      const int pr = (base + tid) >> 3, part = tid & 7;
-      const bool ok = pr < (g1 - g0) * HP;
+    // few large graphs: eight lanes per (graph, channel), each adds every 8th node row, then a fixed
+    // shuffle tree; many small graphs: one thread per (graph, channel)
+    const int pool_items = (g1 - g0) * HP;
+    const int parts = pool_items * 8 <= 2 * kGnnThreads ? 8 : 1;
+    const int pshift = parts == 8 ? 3 : 0;
+    for (int base = 0; base < pool_items * parts; base += kGnnThreads) {
+      const int pr = (base + tid) >> pshift, part = tid & (parts - 1);
+      const bool ok = pr < pool_items;
       const int g = g0 + (ok ? pr / HP : 0), c = pr % HP;
       const int n0 = p.graph_ptr[g] - nbase, n1 = p.graph_ptr[g + 1] - nbase;
       float s = 0.f;
       if (ok)
-        for (int i = n0 + part; i < n1; i += 8) s += hx[(size_t)i * HP + c];
-      s += __shfl_xor_sync(0xffffffffu, s, 1);
-      s += __shfl_xor_sync(0xffffffffu, s, 2);
-      s += __shfl_xor_sync(0xffffffffu, s, 4);
+        for (int i = n0 + part; i < n1; i += parts) s += hx[(size_t)i * HP + c];
+      if (parts == 8) {
+        s += __shfl_xor_sync(0xffffffffu, s, 1);
+        s += __shfl_xor_sync(0xffffffffu, s, 2);
+        s += __shfl_xor_sync(0xffffffffu, s, 4);
+      }
       if (ok && part == 0 && c < p.H) p.emb[(size_t)g * p.emb_ld + c] = (n1 > n0) ? s / (float)(n1 - n0) : 0.f;
     }
     __syncthreads();
