@@ -354,7 +354,8 @@ def run_ours(args):
         alg_b = fam_bytes[top]
         step_bytes = algorithmic_bytes(w, Pa, Pc)
         roof = {"bound": "hbm", "kernel": top, "achieved": alg_b / (top_ms / 1e3) / 1e9, "peak": hbm,
-                "unit": "GB/s", "frac": alg_b / (top_ms / 1e3) / 1e9 / hbm, "traffic": None,
+                "unit": "GB/s", "frac": alg_b / (top_ms / 1e3) / 1e9 / hbm,
+                "traffic": profiled_traffic(w, args, top),
                 "peak_source": which, "kernel_ms_per_step": top_ms, "kernel_launches_per_step": fam_launch[top],
                 "kernel_share_of_step": top_ms / sum(fam_ms.values()),
                 "algorithmic_bytes_per_step": alg_b,
@@ -398,6 +399,25 @@ def run_ours(args):
             sys.stderr.flush()
             os._exit(0)
         dist.destroy_process_group()
+
+
+def profiled_traffic(w, args, kernel: str):
+    """DRAM bytes (read + written) per launch of the dominant kernel, from the committed ncu --set full
+    capture of this workload (profiles/r1_traffic.json, written from the .ncu-rep by
+    tools/ncu_traffic.py); None when no capture of this workload/precision is committed."""
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r1_traffic.json")
+    try:
+        with open(path) as f:
+            table = json.load(f)
+    except (OSError, ValueError):
+        return None
+    key = f"{w['kind']}_b{w['B']}_{args.precision}"
+    name = kernel.split(" ")[0]
+    for cand in (name, name.replace("_kernel", "_tc_kernel"), name.replace("adam_soft_update", "adam_soft_dev")):
+        entry = table.get(key, {}).get(cand)
+        if entry is not None:
+            return entry.get("dram_bytes_per_launch")
+    return None
 
 
 def op_bytes(name: str, w, Pa, Pc) -> float:
