@@ -150,7 +150,8 @@ def run_ours(args):
         ta.load_state_dict(actor.state_dict())
         tq.load_state_dict(qf1.state_dict())
         upd = ddpg.DDPGUpdater(actor, qf1, ta, tq, lr=1e-3, gamma=0.99, tau=1e-4,
-                               world_size=world, rank=rank, shard_optimizer=args.shard_optimizer)
+                               world_size=world, rank=rank, shard_optimizer=args.shard_optimizer,
+                               fork_streams=args.fork)
 
     def host_batch(st):
         return GraphBatch.from_states(st, pin=True, dense_mask=args.dense_mask)
@@ -371,6 +372,7 @@ def run_ours(args):
             "data": "synthetic",
             "config": {"workload": workload_name(w), "states_per_gpu": B, "n_max": n_max,
                        "precision": args.precision,
+                       "streams": "3 forward chains forked" if (args.fork and w["kind"] == "c3") else "single",
                        "mask": "dense [B, A] tensor" if args.dense_mask else "structured: mask[:n,:,:,:n] from node counts",
                        "cuda_graph": bool(graphed is not None or gpredict is not None),
                        "weights": "reference init (PyG glorot / torch Linear), torch.manual_seed(1234)",
@@ -536,6 +538,8 @@ def main():
                     help="c3 (default): full DDPG update, the fwd+bwd+Adam step BASELINE.json's metric names; "
                          "c2: embedder + actor inference")
     ap.add_argument("--batch", type=int, default=0)
+    ap.add_argument("--no-fork", dest="fork", action="store_false",
+                    help="run the three independent forward chains of the update on one stream")
     ap.add_argument("--shard-optimizer", action="store_true",
                     help="N > 1: reduce-scatter gradients, Adam + soft update on a 1/N parameter shard, all-gather")
     ap.add_argument("--dense-mask", action="store_true",

@@ -32,7 +32,7 @@ class DDPGUpdater:
     def __init__(self, actor: Actor, qf1: QNetwork, target_actor: Actor, qf1_target: QNetwork,
                  lr: float = 1e-3, gamma: float = 0.99, tau: float = 1e-4, betas=(0.9, 0.999),
                  eps: float = 1e-8, process_group=None, world_size: int = 1, rank: int = 0,
-                 shard_optimizer: bool = False, global_batch: Optional[int] = None):
+                 shard_optimizer: bool = False, global_batch: Optional[int] = None, fork_streams: bool = False):
         self.actor, self.qf1, self.target_actor, self.qf1_target = actor, qf1, target_actor, qf1_target
         self.lr, self.gamma, self.tau, self.betas, self.eps = lr, gamma, tau, betas, eps
         self.pg, self.world_size = process_group, int(world_size)
@@ -54,6 +54,8 @@ class DDPGUpdater:
         self.gs_critic = zs(qf1) if self.shard else None
         self.step_actor = 0
         self.step_critic = 0
+        self.fork_streams = bool(fork_streams)
+        self._side = None
         self._neg = None
         # Adam step counters in device memory: [critic, actor].  Always used, so that an eager update
         # and a CUDA-graph replay of it are the same launches.
@@ -117,9 +119,59 @@ class DDPGUpdater:
         (qf1_a_values [B], qf1_loss [1], actor_loss [1]); the losses are this rank's share."""
         cur.csr()
         nxt.share_topology_from(cur)
+        if self.fork_streams:
+            return self._update_forked(cur, nxt, actions, rewards, dones)
         qv, q_loss = self.update_critic(nxt, cur, dones, rewards, actions)
         a_loss = self.update_actor(cur)
         return qv, q_loss, a_loss
+
+    def _update_forked(self, cur: GraphBatch, nxt: GraphBatch, actions, rewards, dones):
+        """The same update with its three independent forward chains on three streams:
+             main   : target actor(nxt) -> target critic(nxt, .)
+             side 0 : critic(cur, actions)                        (the TD side of the critic loss)
+             side 1 : actor(cur)                                  (input of the actor loss; the critic update
+                                                                   in between does not touch the actor)
+        They join before the TD/MSE kernel; everything after it is one dependent chain.  Same kernels on
+        the same data as ``update_critic`` + ``update_actor``, hence bit-identical results; it pays when
+        the kernels are too small to fill the GPU (the reference's batch of 100).  Works eagerly and
+        under CUDA-graph capture (the fork/join events become graph edges)."""
+        B = cur.num_graphs
+        scale = 1.0 / (self.global_batch or B * self.world_size)
+        ac, q, ta, tq = self.actor, self.qf1, self.target_actor, self.qf1_target
+        main = torch.cuda.current_stream()
+        if self._side is None:
+            self._side = [torch.cuda.Stream(), torch.cuda.Stream()]
+        fork = torch.cuda.Event()
+        fork.record(main)
+        joins = []
+        with torch.cuda.stream(self._side[0]):
+            self._side[0].wait_event(fork)
+            qv, ctx = net_forward(q, q.flat, cur.view_shared(), actions, save=True)
+            ev = torch.cuda.Event(); ev.record(self._side[0]); joins.append(ev)
+        with torch.cuda.stream(self._side[1]):
+            self._side[1].wait_event(fork)
+            a, ctx_a = net_forward(ac, ac.flat, cur.view_shared(), None, save=True, mask_output=True)
+            ev = torch.cuda.Event(); ev.record(self._side[1]); joins.append(ev)
+        a2, _ = net_forward(ta, ta.flat, nxt, None, save=False, mask_output=True, clamp1=True)
+        q2, _ = net_forward(tq, tq.flat, nxt, a2, save=False)
+        for ev in joins:
+            main.wait_event(ev)
+        # ---- critic update (reference _update_critic, simple_ddpg.py:204-219) ----
+        _, dq, q_loss = ops.td_mse(rewards, dones, q2, qv, self.gamma, scale)
+        net_backward(q, q.flat, cur, ctx, dq.view(B, 1), self.g_critic)
+        self.step_critic += 1
+        self._optimizer_step(q, tq, self.g_critic, self.gs_critic, self.m_critic, self.v_critic, self.steps_dev[0:1])
+        # ---- actor update (reference _update_actor, :221-227) ----
+        q_pi, ctx_q = net_forward(q, q.flat, cur, a, save=True, save_gnn=False)
+        if self._neg is None or self._neg.shape[0] != B or float(self._neg_scale) != scale:
+            self._neg = torch.full((B, 1), -scale, dtype=torch.float32, device=a.device)
+            self._neg_scale = scale
+        dz = net_backward(q, q.flat, cur, ctx_q, self._neg, None, want_action_grad=True, action_grad_masked=True)
+        net_backward(ac, ac.flat, cur, ctx_a, dz, self.g_actor)
+        self.step_actor += 1
+        self._optimizer_step(ac, ta, self.g_actor, self.gs_actor, self.m_actor, self.v_actor, self.steps_dev[1:2])
+        a_loss = ops.colsum(q_pi) * (-scale)
+        return qv.view(-1), q_loss, a_loss
 
 
 class GraphedUpdate:

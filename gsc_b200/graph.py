@@ -93,6 +93,13 @@ class GraphBatch:
         return GraphBatch(self.x, self.edge_index, self.batch, self._mask, self.num_graphs, self.max_nodes,
                           self.ptr, self.n_nodes, self.n_max, self.groups)
 
+    def view_shared(self) -> "GraphBatch":
+        """Same tensors and the same packed CSR, as a separate object (for use on another stream: the
+        lazily generated dense mask, if any, is then not shared half-built)."""
+        gb = self.view()
+        gb._csr = self._csr
+        return gb
+
     # ---- construction -----------------------------------------------------------------------
     @staticmethod
     def from_data_list(data_list: Sequence) -> "GraphBatch":

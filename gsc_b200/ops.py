@@ -58,10 +58,12 @@ def _need_cuda(*ts):
 
 
 def workspace(nbytes: int, device, tag: str = "main") -> Tuple[Optional[torch.Tensor], int]:
-    """Grow-only scratch buffer per (device, tag); the library itself never allocates."""
+    """Grow-only scratch buffer per (device, tag, stream); the library itself never allocates."""
     if nbytes <= 0:
         return None, 0
-    key = (torch.device(device).index, tag)
+    # one buffer per stream: launches on different streams may run concurrently (DDPGUpdater forks the
+    # independent forward passes of an update onto side streams)
+    key = (torch.device(device).index, tag, _stream())
     ws = _workspaces.get(key)
     if ws is None or ws.numel() < nbytes:
         ws = torch.empty(int(nbytes * 1.25) + 256, dtype=torch.uint8, device=device)

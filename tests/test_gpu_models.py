@@ -310,3 +310,32 @@ def test_graphed_predict_equals_eager_predict():
     gb2 = GraphBatch.from_states(st2, dense_mask=False).to(DEV)
     gp.load(gb2)
     assert torch.equal(gp.replay(), ddpg.predict(actor, gb2))
+
+
+@pytest.mark.parametrize("graphed", [False, True])
+def test_forked_stream_update_is_bit_identical(graphed):
+    """DDPGUpdater(fork_streams=True) runs the same kernels on the same data, on three streams."""
+    n_max, B = 16, 40
+    cur_s, nxt_s, actions, rewards, dones = synth.make_transitions(B, n_max, 6, 16, seed=9, num_topologies=4)
+    spec = AgentSpec(n_max)
+    t = lambda a: torch.from_numpy(a).to(DEV)
+    outs = []
+    for fork in (False, True):
+        torch.manual_seed(21)
+        nets = [cls(spec).to(DEV) for cls in (Actor, QNetwork, Actor, QNetwork)]
+        nets[2].load_state_dict(nets[0].state_dict())
+        nets[3].load_state_dict(nets[1].state_dict())
+        upd = ddpg.DDPGUpdater(*nets, lr=1e-3, gamma=0.99, tau=1e-2, fork_streams=fork)
+        cur = GraphBatch.from_states(cur_s, dense_mask=False).to(DEV)
+        nxt = GraphBatch.from_states(nxt_s, dense_mask=False).to(DEV)
+        if graphed:
+            g = ddpg.GraphedUpdate(upd, cur, nxt, t(actions), t(rewards), t(dones))
+            for _ in range(3):
+                res = g.replay()
+        else:
+            for _ in range(3):
+                res = upd.update(cur.view(), nxt.view(), t(actions), t(rewards), t(dones))
+        torch.cuda.synchronize()
+        outs.append(([r.clone() for r in res], [n.flat.clone() for n in nets]))
+    for a, b in zip(outs[0][0] + outs[0][1], outs[1][0] + outs[1][1]):
+        assert torch.equal(a, b)
