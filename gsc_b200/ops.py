@@ -181,6 +181,23 @@ def build_mask(n: torch.Tensor, n_max: int, groups_per_node: int, out: Optional[
     return out
 
 
+def node_features(ingress: torch.Tensor, usage: torch.Tensor, cap: torch.Tensor, graph_ptr: torch.Tensor,
+                  out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """x[Nt, 3] = [ingress_traffic, node_load, node_cap] of a batch of states, normalised per state as
+    the reference's ``_parse_state_as_graph`` does (include/gsc_b200.h: gsc_node_features)."""
+    _need_cuda(ingress, usage, cap, graph_ptr)
+    Nt, B = int(ingress.shape[0]), int(graph_ptr.shape[0]) - 1
+    if out is None:
+        out = torch.empty(Nt, 3, dtype=torch.float32, device=ingress.device)
+    f32 = lambda t: t.contiguous().to(torch.float32)
+    with _Timed("node_features"):
+        check(_lib.load().gsc_node_features(_ptr(f32(ingress)), _ptr(f32(usage)), _ptr(f32(cap)),
+                                            _ptr(graph_ptr.contiguous().to(torch.int32)), B, _ptr(out), _stream()),
+              "gsc_node_features")
+    _count(1)
+    return out
+
+
 def replay_gather(store_x, store_ei, store_n, store_ecount, idx, node_ptr, edge_ptr, num_nodes: int,
                   num_edges: int, x_out=None, ei_out=None, batch_out=None, n_out=None):
     """Gather the transitions ``idx`` from padded device storage into Batch layout (see gsc_b200.h)."""

@@ -83,6 +83,15 @@ int gsc_pack_csr_noalloc(const int64_t* edge_index, int64_t num_edges, const int
  * generated from the node counts instead of being stored and copied. */
 int gsc_build_mask(const int32_t* n, int64_t B, int n_max, int groups_per_node, float* mask, void* stream);
 
+/* Node features of a batch of network states: what _parse_state_as_graph computes per state on the
+ * host (reference src/rlsp/envs/simulator_wrapper.py:255-294) for the observation space
+ * [ingress_traffic, node_load, node_cap].  ingress/usage/cap: raw per-node quantities [num_nodes]
+ * (ingress traffic of the node's ingress SF, total processed traffic, node resource), graph_ptr:
+ * [B+1] node offsets of the states.  x[num_nodes, 3]: each feature divided by (its per-state maximum
+ * + 1e-3) and clipped to [0, 1]; node_load is usage/cap (1 where cap == 0) before normalising. */
+int gsc_node_features(const float* ingress, const float* usage, const float* cap, const int32_t* graph_ptr,
+                      int64_t num_graphs, float* x, void* stream);
+
 /* Minibatch gather from padded struct-of-arrays replay storage (replaces the per-step host collate
  * of reference src/rlsp/agents/buffer.py:56-89): slot idx[b] of store_x[cap, n_max, F],
  * store_ei[cap, 2, e_max] (int32, graph-local ids), store_n[cap], store_ecount[cap] is written in

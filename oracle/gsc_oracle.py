@@ -308,6 +308,28 @@ def explore_action(y: np.ndarray, noise: np.ndarray, low=0.0, high=1.0) -> np.nd
     return a.clip(low32, high32).astype(np.float32)
 
 
+def node_features(ingress, usage, cap, ptr) -> np.ndarray:
+    """Node features of a batch of states: reference simulator_wrapper.py:255-294 per state.
+
+    The reference computes with float32 arrays under its pinned numpy 1.23.4: ``np.max(arr) + 1e-3``
+    promotes the float32 scalar to float64, and ``arr / that`` casts the scalar back to float32
+    (value-based casting); ``usage / cap`` is a Python-float division stored into a float32 array.
+    Written out explicitly so that the result does not depend on the numpy this file runs on."""
+    ingress, usage, cap = (np.asarray(a, dtype=np.float32) for a in (ingress, usage, cap))
+    x = np.zeros((ingress.shape[0], 3), dtype=np.float32)
+    for g in range(len(ptr) - 1):
+        lo, hi = int(ptr[g]), int(ptr[g + 1])
+        if hi <= lo:
+            continue
+        util = np.ones(hi - lo, dtype=np.float32)
+        nz = cap[lo:hi] != 0
+        util[nz] = (usage[lo:hi][nz].astype(np.float64) / cap[lo:hi][nz].astype(np.float64)).astype(np.float32)
+        for k, arr in enumerate((ingress[lo:hi], util, cap[lo:hi])):
+            denom = np.float32(np.float64(arr.max()) + 1e-3)
+            x[lo:hi, k] = np.clip(arr / denom, np.float32(0), np.float32(1))
+    return x
+
+
 def obs_to(obs: dict, dtype) -> dict:
     out = dict(obs)
     for k in ("x", "mask"):

@@ -142,3 +142,22 @@ def test_normalize_uses_plain_left_to_right_sum():
     assert O._seq_sum(lst) == 0.9999999999999999
     out = O.normalize_scheduling_probabilities(lst)
     assert out[0] == np.float64(0.1) + (1 - 0.9999999999999999)
+
+
+def test_node_features_follow_the_reference_lines():
+    """simulator_wrapper.py:255-294 for one state, written with explicit float32/float64 steps."""
+    ingress = np.array([0.0, 12.5, 0.0, 3.25], dtype=np.float32)
+    usage = np.array([1.0, 0.0, 7.0, 2.0], dtype=np.float32)
+    cap = np.array([4.0, 0.0, 2.0, 8.0], dtype=np.float32)
+    x = O.node_features(ingress, usage, cap, np.array([0, 4]))
+    assert x.dtype == np.float32 and x.shape == (4, 3)
+    d_in = np.float32(np.float64(np.float32(12.5)) + 1e-3)
+    assert np.array_equal(x[:, 0], np.clip(ingress / d_in, 0, 1).astype(np.float32))
+    util = np.array([0.25, 1.0, 3.5, 0.25], dtype=np.float32)        # cap == 0 -> 1
+    d_ut = np.float32(np.float64(np.float32(3.5)) + 1e-3)
+    assert np.array_equal(x[:, 1], np.clip(util / d_ut, 0, 1).astype(np.float32))
+    assert x[1, 2] == 0.0 and abs(float(x[3, 2]) - 8.0 / 8.001) < 1e-6
+    # two states are normalised independently
+    x2 = O.node_features(np.tile(ingress, 2) * np.repeat([1, 3], 4).astype(np.float32), np.tile(usage, 2),
+                         np.tile(cap, 2), np.array([0, 4, 8]))
+    assert np.array_equal(x2[:4, 1:], x[:, 1:]) and np.array_equal(x2[4:, 1:], x[:, 1:])
