@@ -158,7 +158,7 @@ class DDPGUpdater:
             main.wait_event(ev)
         # ---- critic update (reference _update_critic, simple_ddpg.py:204-219) ----
         _, dq, q_loss = ops.td_mse(rewards, dones, q2, qv, self.gamma, scale)
-        net_backward(q, q.flat, cur, ctx, dq.view(B, 1), self.g_critic)
+        net_backward(q, q.flat, cur, ctx, dq.view(B, 1), self.g_critic, side=self._side[0])
         self.step_critic += 1
         self._optimizer_step(q, tq, self.g_critic, self.gs_critic, self.m_critic, self.v_critic, self.steps_dev[0:1])
         # ---- actor update (reference _update_actor, :221-227) ----
@@ -167,7 +167,7 @@ class DDPGUpdater:
             self._neg = torch.full((B, 1), -scale, dtype=torch.float32, device=a.device)
             self._neg_scale = scale
         dz = net_backward(q, q.flat, cur, ctx_q, self._neg, None, want_action_grad=True, action_grad_masked=True)
-        net_backward(ac, ac.flat, cur, ctx_a, dz, self.g_actor)
+        net_backward(ac, ac.flat, cur, ctx_a, dz, self.g_actor, side=self._side[0])
         self.step_actor += 1
         self._optimizer_step(ac, ta, self.g_actor, self.gs_actor, self.m_actor, self.v_actor, self.steps_dev[1:2])
         a_loss = ops.colsum(q_pi) * (-scale)

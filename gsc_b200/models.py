@@ -325,13 +325,31 @@ def net_forward(net: _FlatNet, flat: torch.Tensor, gb: GraphBatch, action: Optio
 
 def net_backward(net: _FlatNet, flat: torch.Tensor, gb: GraphBatch, ctx, dz: torch.Tensor,
                  grad_flat: Optional[torch.Tensor], want_action_grad: bool = False,
-                 action_grad_masked: bool = False):
+                 action_grad_masked: bool = False, side: Optional[torch.cuda.Stream] = None):
     """Back-propagate ``dz`` (gradient w.r.t. the pre-mask MLP output).
 
     Writes parameter gradients into ``grad_flat`` (same layout as ``flat``) unless it is None, and
     returns the gradient w.r.t. the action input (times the mask if ``action_grad_masked``) when
-    requested."""
+    requested.
+
+    ``side``: a second stream for the weight / bias gradients of the dense layers.  They only read
+    the layer's output gradient, while the chain that continues on the current stream (input
+    gradients -> embedder backward) is what everything else waits for; the embedder backward is a
+    persistent kernel whose last wave leaves more than half of the SMs idle, which the side stream's
+    kernels fill.  The streams are joined before returning."""
     embp, saved, inputs, hs, st = ctx
+    main = torch.cuda.current_stream()
+
+    def weight_grads(fn):
+        if side is None or grad_flat is None:
+            fn()
+            return
+        ev = torch.cuda.Event()
+        ev.record(main)                     # the layer's output gradient is complete here
+        with torch.cuda.stream(side):
+            side.wait_event(ev)
+            fn()
+
     gnn, lins = net.views(flat)
     g_gnn, g_lins = net.views(grad_flat) if grad_flat is not None else (None, None)
     H = net.embedder.hidden_dim
@@ -341,15 +359,17 @@ def net_backward(net: _FlatNet, flat: torch.Tensor, gb: GraphBatch, ctx, dz: tor
     for i in range(len(lins) - 1, -1, -1):
         W, _, Wp, pad = lins[i]
         if grad_flat is not None:
-            if i == 0 and st:
-                gWp = g_lins[0][2]
-                ops.linear_wgrad(d, [embp], gWp[:, :pad + H])
-                ops.mask_wgrad(d, gb.n_nodes, gb.n_max, gb.groups, gWp[:, pad + H:pad + H + A])
-                if len(inputs) > 2:
-                    ops.linear_wgrad(d, [inputs[2]], gWp[:, pad + H + A:pad + H + 2 * A])
-            else:
-                ops.linear_wgrad(d, inputs if i == 0 else [hs[i - 1]], g_lins[i][2] if i == 0 else g_lins[i][0])
-            ops.colsum(d, out=g_lins[i][1])
+            def layer_grads(i=i, d=d, pad=pad):
+                if i == 0 and st:
+                    gWp = g_lins[0][2]
+                    ops.linear_wgrad(d, [embp], gWp[:, :pad + H])
+                    ops.mask_wgrad(d, gb.n_nodes, gb.n_max, gb.groups, gWp[:, pad + H:pad + H + A])
+                    if len(inputs) > 2:
+                        ops.linear_wgrad(d, [inputs[2]], gWp[:, pad + H + A:pad + H + 2 * A])
+                else:
+                    ops.linear_wgrad(d, inputs if i == 0 else [hs[i - 1]], g_lins[i][2] if i == 0 else g_lins[i][0])
+                ops.colsum(d, out=g_lins[i][1])
+            weight_grads(layer_grads)
         if i > 0:
             d = ops.linear_dgrad(d, W, 0, int(W.shape[1]), gate=hs[i - 1])
         else:
@@ -363,6 +383,10 @@ def net_backward(net: _FlatNet, flat: torch.Tensor, gb: GraphBatch, ctx, dz: tor
                 ops.gnn_embed_bwd(gb.x, rowptr, col, gptr, gb.num_graphs, gb.max_nodes, gnn, H,
                                   net.embedder.num_layers, net.embedder.num_iter, saved, d_embp[:, pad:],
                                   d_params=g_gnn, pack_stats=gb.pack_stats())
+    if side is not None and grad_flat is not None:
+        done = torch.cuda.Event()
+        done.record(side)
+        main.wait_event(done)               # gradients complete, and nothing read on `side` is released early
     return d_action
 
 
