@@ -25,7 +25,7 @@ import torch
 from . import ops
 from .dp import all_gather_flat, allreduce_flat, reduce_scatter_flat, shard_range
 from .graph import GraphBatch
-from .models import Actor, QNetwork, net_backward, net_forward
+from .models import Actor, QNetwork, first_layer_table, net_backward, net_forward
 
 
 class DDPGUpdater:
@@ -117,10 +117,10 @@ class DDPGUpdater:
     def update(self, cur: GraphBatch, nxt: GraphBatch, actions, rewards, dones):
         """One gradient step of reference simple_ddpg.py:312-322.  Returns
         (qf1_a_values [B], qf1_loss [1], actor_loss [1]); the losses are this rank's share."""
-        cur.csr()
-        nxt.share_topology_from(cur)
         if self.fork_streams:
             return self._update_forked(cur, nxt, actions, rewards, dones)
+        cur.csr()
+        nxt.share_topology_from(cur)
         qv, q_loss = self.update_critic(nxt, cur, dones, rewards, actions)
         a_loss = self.update_actor(cur)
         return qv, q_loss, a_loss
@@ -141,19 +141,32 @@ class DDPGUpdater:
         main = torch.cuda.current_stream()
         if self._side is None:
             self._side = [torch.cuda.Stream(), torch.cuda.Stream()]
+        # the four first-layer tables depend on the weights only: they are built on a side stream while
+        # the main stream packs the batch (ten small launches that leave the GPU mostly idle)
+        start = torch.cuda.Event()
+        start.record(main)
+        with torch.cuda.stream(self._side[1]):
+            self._side[1].wait_event(start)
+            tab = {id(net): first_layer_table(net, net.flat, cur) for net in (ta, tq, q, ac)}
+            tables_ready = torch.cuda.Event()
+            tables_ready.record(self._side[1])
+        cur.csr()
+        nxt.share_topology_from(cur)
         fork = torch.cuda.Event()
         fork.record(main)
         joins = []
         with torch.cuda.stream(self._side[0]):
             self._side[0].wait_event(fork)
-            qv, ctx = net_forward(q, q.flat, cur.view_shared(), actions, save=True)
+            qv, ctx = net_forward(q, q.flat, cur.view_shared(), actions, save=True, table=tab[id(q)],
+                                  table_ready=tables_ready)
             ev = torch.cuda.Event(); ev.record(self._side[0]); joins.append(ev)
         with torch.cuda.stream(self._side[1]):
             self._side[1].wait_event(fork)
-            a, ctx_a = net_forward(ac, ac.flat, cur.view_shared(), None, save=True, mask_output=True)
+            a, ctx_a = net_forward(ac, ac.flat, cur.view_shared(), None, save=True, mask_output=True, table=tab[id(ac)])
             ev = torch.cuda.Event(); ev.record(self._side[1]); joins.append(ev)
-        a2, _ = net_forward(ta, ta.flat, nxt, None, save=False, mask_output=True, clamp1=True)
-        q2, _ = net_forward(tq, tq.flat, nxt, a2, save=False)
+        a2, _ = net_forward(ta, ta.flat, nxt, None, save=False, mask_output=True, clamp1=True, table=tab[id(ta)],
+                            table_ready=tables_ready)
+        q2, _ = net_forward(tq, tq.flat, nxt, a2, save=False, table=tab[id(tq)])
         for ev in joins:
             main.wait_event(ev)
         # ---- critic update (reference _update_critic, simple_ddpg.py:204-219) ----
@@ -162,7 +175,14 @@ class DDPGUpdater:
         self.step_critic += 1
         self._optimizer_step(q, tq, self.g_critic, self.gs_critic, self.m_critic, self.v_critic, self.steps_dev[0:1])
         # ---- actor update (reference _update_actor, :221-227) ----
-        q_pi, ctx_q = net_forward(q, q.flat, cur, a, save=True, save_gnn=False)
+        upd_ev = torch.cuda.Event()
+        upd_ev.record(main)                                   # critic weights updated
+        with torch.cuda.stream(self._side[1]):                # its new table next to its embedder forward
+            self._side[1].wait_event(upd_ev)
+            tab_q = first_layer_table(q, q.flat, cur)
+            tab_q_ready = torch.cuda.Event()
+            tab_q_ready.record(self._side[1])
+        q_pi, ctx_q = net_forward(q, q.flat, cur, a, save=True, save_gnn=False, table=tab_q, table_ready=tab_q_ready)
         if self._neg is None or self._neg.shape[0] != B or float(self._neg_scale) != scale:
             self._neg = torch.full((B, 1), -scale, dtype=torch.float32, device=a.device)
             self._neg_scale = scale

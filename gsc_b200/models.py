@@ -276,9 +276,22 @@ def _structured(gb: GraphBatch) -> bool:
     return ops.use_structured_mask and gb.structured and gb.n_nodes.is_cuda
 
 
+def first_layer_table(net: _FlatNet, flat: torch.Tensor, gb: GraphBatch) -> Optional[torch.Tensor]:
+    """The per-node-count table that replaces the mask column block of the first dense layer for a
+    structured batch (None otherwise).  Depends on the weights only, so it can be computed ahead of
+    the forward pass (``net_forward(..., table=...)``), e.g. while the batch is still being packed."""
+    if not _structured(gb):
+        return None
+    _, lins = net.views(flat)
+    _, _, Wp, pad = lins[0]
+    H, A = net.embedder.hidden_dim, net.action_dim
+    return ops.mask_table(Wp[:, pad + H:pad + H + A], gb.n_max, gb.groups)
+
+
 def net_forward(net: _FlatNet, flat: torch.Tensor, gb: GraphBatch, action: Optional[torch.Tensor],
                 save: bool, mask_output: bool = False, clamp1: bool = False,
-                save_gnn: Optional[bool] = None):
+                save_gnn: Optional[bool] = None, table: Optional[torch.Tensor] = None,
+                table_ready: Optional[torch.cuda.Event] = None):
     """emb = GNN(gb); z = MLP(cat[emb, mask(, action)]); returns (z [* mask] [clamped], ctx).
 
     ``save`` keeps what ``net_backward`` needs; ``save_gnn=False`` skips the embedder activations
@@ -309,7 +322,10 @@ def net_forward(net: _FlatNet, flat: torch.Tensor, gb: GraphBatch, action: Optio
         out_mul = gb.mask if (mask_output and last and not st) else None
         out_smask = smask if (mask_output and last and st) else None
         if i == 0 and st:
-            table = ops.mask_table(Wp[:, pad + H:pad + H + A], gb.n_max, gb.groups)
+            if table is None:
+                table = ops.mask_table(Wp[:, pad + H:pad + H + A], gb.n_max, gb.groups)
+            elif table_ready is not None:          # built on another stream: needed only from here on
+                torch.cuda.current_stream().wait_event(table_ready)
             ins = [embp] + ([action] if action is not None else [])
             offs = [0] + ([pad + H + A] if action is not None else [])
             h = ops.linear_fwd(ins, Wp, b, relu=not last, mul=out_mul, clamp1=clamp1 and last,
