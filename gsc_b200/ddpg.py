@@ -66,10 +66,26 @@ class DDPGUpdater:
         if self.world_size > 1:
             allreduce_flat(flat_grad, self.pg)
 
+    def _bucketed(self) -> bool:
+        """Data parallel with the forked backward: every dense layer's gradient block is all-reduced on
+        the side stream as soon as it is complete (behind the embedder backward); only the small
+        embedder block is left for after it."""
+        return self.fork_streams and self.world_size > 1 and not self.shard
+
+    def _layer_allreduce(self, net, g):
+        if not self._bucketed():
+            return None
+        _, layers = net.grad_regions()
+        return lambda i: allreduce_flat(g[layers[i][0]:layers[i][1]], self.pg)
+
     def _optimizer_step(self, net, target, g, gs, m, v, step_dev) -> None:
         """Gradient exchange + fused Adam + soft target update of one network."""
         if not self.shard:
-            self._allreduce(g)
+            if self._bucketed():
+                lo, hi = net.grad_regions()[0]
+                self._allreduce(g[lo:hi])
+            else:
+                self._allreduce(g)
             ops.adam_soft_update_dev(net.flat, g, m, v, target.flat, self.lr, self.betas[0], self.betas[1],
                                      self.eps, step_dev, self.tau)
             return
@@ -171,7 +187,8 @@ class DDPGUpdater:
             main.wait_event(ev)
         # ---- critic update (reference _update_critic, simple_ddpg.py:204-219) ----
         _, dq, q_loss = ops.td_mse(rewards, dones, q2, qv, self.gamma, scale)
-        net_backward(q, q.flat, cur, ctx, dq.view(B, 1), self.g_critic, side=self._side[0])
+        net_backward(q, q.flat, cur, ctx, dq.view(B, 1), self.g_critic, side=self._side[0],
+                     after_layer=self._layer_allreduce(q, self.g_critic))
         self.step_critic += 1
         self._optimizer_step(q, tq, self.g_critic, self.gs_critic, self.m_critic, self.v_critic, self.steps_dev[0:1])
         # ---- actor update (reference _update_actor, :221-227) ----
@@ -187,7 +204,8 @@ class DDPGUpdater:
             self._neg = torch.full((B, 1), -scale, dtype=torch.float32, device=a.device)
             self._neg_scale = scale
         dz = net_backward(q, q.flat, cur, ctx_q, self._neg, None, want_action_grad=True, action_grad_masked=True)
-        net_backward(ac, ac.flat, cur, ctx_a, dz, self.g_actor, side=self._side[0])
+        net_backward(ac, ac.flat, cur, ctx_a, dz, self.g_actor, side=self._side[0],
+                     after_layer=self._layer_allreduce(ac, self.g_actor))
         self.step_actor += 1
         self._optimizer_step(ac, ta, self.g_actor, self.gs_actor, self.m_actor, self.v_actor, self.steps_dev[1:2])
         a_loss = ops.colsum(q_pi) * (-scale)

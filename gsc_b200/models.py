@@ -247,6 +247,17 @@ class _FlatNet(nn.Module):
             lins.append((wp[:, wpad:], self._view(flat, bo, bs, None, 0), wp, wpad))
         return gnn, lins
 
+    def grad_regions(self):
+        """(gnn_region, [layer regions]) as (lo, hi) float offsets into a flat buffer: the embedder block
+        and, per MLP layer, its weight + bias block.  Everything outside them is alignment padding."""
+        n_gnn = len(self.embedder.ordered_params())
+        rest = self._items[n_gnn:]
+        layers = []
+        for i in range(0, len(rest), 2):
+            (wo, _, _, _), (bo, bs, _, _) = rest[i], rest[i + 1]
+            layers.append((wo, bo + int(bs[0])))
+        return (0, rest[0][0]), layers
+
     def param_views(self, flat: torch.Tensor) -> List[torch.Tensor]:
         """Per-parameter views of ``flat`` in ``self.parameters()`` order."""
         return [self._view(flat, off, shape, ld, pad) for off, shape, ld, pad in self._items]
@@ -341,7 +352,8 @@ def net_forward(net: _FlatNet, flat: torch.Tensor, gb: GraphBatch, action: Optio
 
 def net_backward(net: _FlatNet, flat: torch.Tensor, gb: GraphBatch, ctx, dz: torch.Tensor,
                  grad_flat: Optional[torch.Tensor], want_action_grad: bool = False,
-                 action_grad_masked: bool = False, side: Optional[torch.cuda.Stream] = None):
+                 action_grad_masked: bool = False, side: Optional[torch.cuda.Stream] = None,
+                 after_layer=None):
     """Back-propagate ``dz`` (gradient w.r.t. the pre-mask MLP output).
 
     Writes parameter gradients into ``grad_flat`` (same layout as ``flat``) unless it is None, and
@@ -352,7 +364,9 @@ def net_backward(net: _FlatNet, flat: torch.Tensor, gb: GraphBatch, ctx, dz: tor
     the layer's output gradient, while the chain that continues on the current stream (input
     gradients -> embedder backward) is what everything else waits for; the embedder backward is a
     persistent kernel whose last wave leaves more than half of the SMs idle, which the side stream's
-    kernels fill.  The streams are joined before returning."""
+    kernels fill.  The streams are joined before returning.  ``after_layer(i)`` is called on that
+    stream once layer i's weight and bias gradients are enqueued (data parallelism all-reduces them
+    there, behind the embedder backward)."""
     embp, saved, inputs, hs, st = ctx
     main = torch.cuda.current_stream()
 
@@ -385,6 +399,8 @@ def net_backward(net: _FlatNet, flat: torch.Tensor, gb: GraphBatch, ctx, dz: tor
                 else:
                     ops.linear_wgrad(d, inputs if i == 0 else [hs[i - 1]], g_lins[i][2] if i == 0 else g_lins[i][0])
                 ops.colsum(d, out=g_lins[i][1])
+                if after_layer is not None:
+                    after_layer(i)
             weight_grads(layer_grads)
         if i > 0:
             d = ops.linear_dgrad(d, W, 0, int(W.shape[1]), gate=hs[i - 1])

@@ -1,6 +1,7 @@
 """Two-GPU NCCL tests of the data-parallel DDPG update: sharding the replay
-minibatch by graph and (a) all-reducing the flat gradients or (b) reduce-scattering them into a
-1/W-sharded fused Adam + soft update followed by an all-gather must both reproduce the single-GPU
+minibatch by graph and (a) all-reducing the flat gradients, (b) reduce-scattering them into a
+1/W-sharded fused Adam + soft update followed by an all-gather, or (c) the forked-stream update with
+per-layer gradient all-reduces on the side stream must all reproduce the single-GPU
 update of the full minibatch.  Skipped on boxes with one GPU (run with ``gpurun --gpus 2``)."""
 import os
 
@@ -35,10 +36,10 @@ def _worker(rank, world, port, n_max, B, steps, out):
     mine = dp.shard_transitions(*full, rank, world)
     t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
     results = {}
-    for mode in ("allreduce", "sharded"):
+    for mode in ("allreduce", "sharded", "forked"):
         nets = _build(spec, dev)
         upd = ddpg.DDPGUpdater(*nets, lr=1e-3, gamma=0.99, tau=1e-2, world_size=world, rank=rank,
-                               shard_optimizer=mode == "sharded", global_batch=B)
+                               shard_optimizer=mode == "sharded", global_batch=B, fork_streams=mode == "forked")
         cur, nxt = GraphBatch.from_states(mine[0], dense_mask=False).to(dev), GraphBatch.from_states(mine[1], dense_mask=False).to(dev)
         for _ in range(steps):
             qv, ql, al = upd.update(cur.view(), nxt.view(), t(mine[2]), t(mine[3]), t(mine[4]))
