@@ -295,14 +295,26 @@ def run_ours(args):
         new_obs = GraphData(torch.from_numpy(g0["x"]).pin_memory(), torch.from_numpy(g0["edge_index"]).pin_memory(), None)
         new_act = torch.from_numpy(w["actions"][0]).pin_memory()
         static = None
+        g_e2e = None
         if graphed is not None:
             static = BufferSample(graphed.cur, graphed.actions, graphed.nxt, graphed.dones, graphed.rewards)
+            if not args.dense_mask:
+                np.random.seed(99 + rank)
+                smp0 = rb.sample(B)
+                c0, n0 = smp0.observations, smp0.next_observations
+                # an environment step does not change the network: the next state reuses the topology
+                # (and so the packed CSR) of the current one, as in the device-resident timing above
+                n0 = GraphBatch(n0.x, c0.edge_index, c0.batch, None, n0.num_graphs, c0.max_nodes, None,
+                                c0.n_nodes, c0.n_max, c0.groups)
+                g_e2e = ddpg.GraphedUpdate(upd, c0, n0, smp0.actions, smp0.rewards, smp0.dones, replay=rb)
 
         def e2e_step():
             if rb.pos + 1 >= rb.buffer_size:
                 rb.pos = rb.buffer_size - B                              # keep cycling inside the buffer
             rb.add(new_obs, new_obs, new_act, 0.5, False)
-            if static is not None:
+            if g_e2e is not None:            # index draw on the host, gather + update in one graph launch
+                r = g_e2e.replay_sampled()
+            elif static is not None:
                 rb.sample(B, out=static)
                 r = graphed.replay()
             else:
@@ -383,8 +395,9 @@ def run_ours(args):
                     "ms_per_step": e2e_ms / args.steps,
                     "path": ("pinned host states -> H2D -> mask from n on device -> packer+embedder+actor -> D2H actions"
                              if w["kind"] == "c2" else
-                             "DeviceGraphReplayBuffer.add(1 transition from pinned host) -> sample(B) (host RNG, device gather) "
-                             "-> DDPG update -> D2H losses")},
+                             "DeviceGraphReplayBuffer.add(1 transition from pinned host) -> sample(B): index draw with the "
+                             "reference's host RNG, indices H2D, gather from device storage + DDPG update as one "
+                             "CUDA-graph launch -> D2H losses")},
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "cpu_baseline": cpu,
             "per_op_ms": {k: round(v, 4) for k, v in sorted(per_op.items(), key=lambda kv: -kv[1])[:12]},
             "wall_ms_per_step_incl_flush": t_wall / args.steps * 1e3,

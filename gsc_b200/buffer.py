@@ -7,7 +7,7 @@ time a model touches them.  Host-side storage stays Python, as in the reference.
 """
 from __future__ import annotations
 
-from typing import NamedTuple
+from typing import Optional, NamedTuple
 
 import numpy as np
 import torch
@@ -214,6 +214,51 @@ class DeviceGraphReplayBuffer:
         # structured batch: the [B, A] mask is generated from n only if somebody asks for .mask
         return GraphBatch(x, ei, batch, None, len(idx_np), int(n_sel.max()) if len(n_sel) else 0, None,
                           n_dev, self.n_max, self.groups)
+
+    # ---- sampling inside a CUDA graph -------------------------------------------------------------
+    def host_sample_plan(self, batch_size: int, idx_out: np.ndarray, ptrs_out: np.ndarray):
+        """Draw the minibatch indices (reference RNG) and write them and the node / edge offsets of
+        both states into caller-owned (pinned) host arrays: ``idx_out`` int64 [B], ``ptrs_out`` int32
+        [4, B+1] = cur node, cur edge, next node, next edge offsets.  Returns the four totals."""
+        idx_np = self.sample_indices(batch_size)
+        idx_out[:] = idx_np
+        ptrs_out[:, 0] = 0
+        np.cumsum(self.n_h[0, idx_np], out=ptrs_out[0, 1:])
+        np.cumsum(self.ec_h[0, idx_np], out=ptrs_out[1, 1:])
+        np.cumsum(self.n_h[1, idx_np], out=ptrs_out[2, 1:])
+        np.cumsum(self.ec_h[1, idx_np], out=ptrs_out[3, 1:])
+        return tuple(int(ptrs_out[k, -1]) for k in range(4))
+
+    def gather_planned(self, idx_dev: torch.Tensor, ptrs_dev: torch.Tensor, out: "BufferSample",
+                       aux_stream: Optional[torch.cuda.Stream] = None) -> None:
+        """The device half of ``sample``: gather the transitions ``idx_dev`` into the static minibatch
+        ``out`` using offsets that already sit on the device.  No host work, so it can be captured
+        into a CUDA graph in front of the update (``ddpg.GraphedUpdate(..., replay=...)``)."""
+        cur, nxt = out.observations, out.next_observations
+        self.ops.replay_gather(self.x, self.ei, self.n, self.ec, idx_dev, ptrs_dev[0], ptrs_dev[1],
+                               int(cur.x.shape[0]), int(cur.edge_index.shape[1]), x_out=cur.x,
+                               ei_out=cur.edge_index, batch_out=cur.batch, n_out=cur.n_nodes)
+        self.ops.replay_gather(self.next_x, self.next_ei, self.next_n, self.next_ec, idx_dev, ptrs_dev[2], ptrs_dev[3],
+                               int(nxt.x.shape[0]), int(nxt.edge_index.shape[1]), x_out=nxt.x,
+                               ei_out=nxt.edge_index, batch_out=nxt.batch, n_out=nxt.n_nodes)
+        for gb in (cur, nxt):
+            if gb._mask is not None:
+                self.ops.build_mask(gb.n_nodes, self.n_max, self.groups, out=gb._mask)
+        def rows():
+            self.ops.gather_rows(self.actions, idx_dev, out.actions)
+            self.ops.gather_rows(self.rewards, idx_dev, out.rewards)
+            self.ops.gather_rows(self.dones, idx_dev, out.dones)
+        if aux_stream is None:
+            rows()
+            return
+        # the [B, A] action rows are the bulk of the bytes and are first needed by the critic's dense
+        # layer: gather them on the stream that consumes them, next to the packer
+        main = torch.cuda.current_stream()
+        ev = torch.cuda.Event()
+        ev.record(main)
+        with torch.cuda.stream(aux_stream):
+            aux_stream.wait_event(ev)
+            rows()
 
     def sample(self, batch_size: int, out: "BufferSample" = None) -> BufferSample:
         """Minibatch on the device.  ``out`` (a previous BufferSample of identical shapes, e.g. the

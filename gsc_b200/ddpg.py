@@ -141,6 +141,11 @@ class DDPGUpdater:
         a_loss = self.update_actor(cur)
         return qv, q_loss, a_loss
 
+    def side_streams(self):
+        if self._side is None:
+            self._side = [torch.cuda.Stream(), torch.cuda.Stream()]
+        return self._side
+
     def _update_forked(self, cur: GraphBatch, nxt: GraphBatch, actions, rewards, dones):
         """The same update with its three independent forward chains on three streams:
              main   : target actor(nxt) -> target critic(nxt, .)
@@ -155,8 +160,7 @@ class DDPGUpdater:
         scale = 1.0 / (self.global_batch or B * self.world_size)
         ac, q, ta, tq = self.actor, self.qf1, self.target_actor, self.qf1_target
         main = torch.cuda.current_stream()
-        if self._side is None:
-            self._side = [torch.cuda.Stream(), torch.cuda.Stream()]
+        self.side_streams()
         # the four first-layer tables depend on the weights only: they are built on a side stream while
         # the main stream packs the batch (ten small launches that leave the GPU mostly idle)
         start = torch.cuda.Event()
@@ -224,8 +228,35 @@ class GraphedUpdate:
     capture and replay in step); destroy the object before ``destroy_process_group()``."""
 
     def __init__(self, upd: DDPGUpdater, cur: GraphBatch, nxt: GraphBatch, actions, rewards, dones,
-                 warmup: int = 2):
+                 warmup: int = 2, replay=None):
+        """``replay``: a ``DeviceGraphReplayBuffer``.  The gather of the sampled transitions out of its
+        storage is then captured in front of the update (``replay_sampled``): per gradient step the
+        host only draws the indices and copies them (and the node / edge offsets) to the device."""
         self.upd = upd
+        self.rb = replay
+        if replay is not None:
+            if not (cur.structured and nxt.structured):
+                raise ValueError("GraphedUpdate(replay=...) needs structured batches (what the device buffer samples)")
+            B = cur.num_graphs
+            dev = cur.x.device
+            self.idx = torch.zeros(B, dtype=torch.int64, device=dev)
+            self.ptrs = torch.zeros(4, B + 1, dtype=torch.int32, device=dev)
+            self.idx_h = [torch.zeros(B, dtype=torch.int64).pin_memory() for _ in range(2)]
+            self.ptrs_h = [torch.zeros(4, B + 1, dtype=torch.int32).pin_memory() for _ in range(2)]
+            self._copied = [torch.cuda.Event(), torch.cuda.Event()]
+            for ev in self._copied:
+                ev.record()
+            self._flip = 0
+            # a valid plan for the warm-up and the capture (drawn without disturbing the caller's RNG stream)
+            rng_state = np.random.get_state()
+            totals = replay.host_sample_plan(B, self.idx_h[0].numpy(), self.ptrs_h[0].numpy())
+            np.random.set_state(rng_state)
+            want = (cur.x.shape[0], cur.edge_index.shape[1], nxt.x.shape[0], nxt.edge_index.shape[1])
+            if totals != tuple(int(v) for v in want):
+                raise ValueError(f"replay minibatches have node/edge totals {totals}, the given batch has {want}: "
+                                 "a captured update needs minibatches of constant size")
+            self.idx.copy_(self.idx_h[0])
+            self.ptrs.copy_(self.ptrs_h[0])
         cl = lambda t: None if t is None else t.clone()
         mk = lambda gb, share=None: GraphBatch(
             gb.x.clone(), gb.edge_index.clone() if share is None else share.edge_index,
@@ -261,7 +292,27 @@ class GraphedUpdate:
         restore()
 
     def _run(self):
+        if self.rb is not None:
+            from .buffer import BufferSample
+            aux = self.upd.side_streams()[0] if self.upd.fork_streams else None    # the critic chain's stream
+            self.rb.gather_planned(self.idx, self.ptrs, BufferSample(self.cur, self.actions, self.nxt, self.dones,
+                                                                    self.rewards), aux_stream=aux)
         return self.upd.update(self.cur.view(), self.nxt.view(), self.actions, self.rewards, self.dones)
+
+    def replay_sampled(self):
+        """Draw a minibatch from the replay buffer given at construction and run the update on it: index
+        draw on the host (reference RNG), everything else inside the graph."""
+        k = self._flip
+        self._flip ^= 1
+        self._copied[k].synchronize()                      # the pinned pair is free again
+        totals = self.rb.host_sample_plan(self.cur.num_graphs, self.idx_h[k].numpy(), self.ptrs_h[k].numpy())
+        want = (self.cur.x.shape[0], self.cur.edge_index.shape[1], self.nxt.x.shape[0], self.nxt.edge_index.shape[1])
+        if totals != tuple(int(v) for v in want):
+            raise ValueError(f"sampled minibatch has node/edge totals {totals}, the captured graph expects {want}")
+        self.idx.copy_(self.idx_h[k], non_blocking=True)
+        self.ptrs.copy_(self.ptrs_h[k], non_blocking=True)
+        self._copied[k].record()
+        return self.replay()
 
     def load(self, cur: GraphBatch, nxt: GraphBatch, actions, rewards, dones, non_blocking: bool = True):
         """Copy a minibatch (host or device tensors of the captured shapes) into the static inputs."""

@@ -339,3 +339,40 @@ def test_forked_stream_update_is_bit_identical(graphed):
         outs.append(([r.clone() for r in res], [n.flat.clone() for n in nets]))
     for a, b in zip(outs[0][0] + outs[0][1], outs[1][0] + outs[1][1]):
         assert torch.equal(a, b)
+
+
+def test_graphed_update_with_captured_replay_gather_equals_eager_sampling():
+    """GraphedUpdate(replay=rb).replay_sampled() == rb.sample(B) + DDPGUpdater.update on the same draws."""
+    from gsc_b200.buffer import DeviceGraphReplayBuffer
+    n_max, B = 12, 16
+    spec = AgentSpec(n_max)
+    cur_s, nxt_s, actions, rewards, dones = synth.make_transitions(64, n_max, n_max, n_max, seed=31, fixed_links=18,
+                                                                   num_topologies=6)
+
+    def build():
+        torch.manual_seed(5)
+        nets = [cls(spec).to(DEV) for cls in (Actor, QNetwork, Actor, QNetwork)]
+        nets[2].load_state_dict(nets[0].state_dict())
+        nets[3].load_state_dict(nets[1].state_dict())
+        rb = DeviceGraphReplayBuffer(128, spec.env.action_space, device=DEV, n_max=n_max)
+        rb.bulk_load(cur_s, nxt_s, actions, rewards, dones)
+        return nets, ddpg.DDPGUpdater(*nets, lr=1e-3, gamma=0.99, tau=1e-2, fork_streams=True), rb
+
+    nets_e, upd_e, rb_e = build()
+    nets_g, upd_g, rb_g = build()
+    np.random.seed(3)
+    s0 = rb_g.sample(B)
+    g = ddpg.GraphedUpdate(upd_g, s0.observations, s0.next_observations, s0.actions, s0.rewards, s0.dones, replay=rb_g)
+    np.random.seed(11)
+    outs_g = [tuple(t.clone() for t in g.replay_sampled()) for _ in range(3)]
+    np.random.seed(11)
+    outs_e = []
+    for _ in range(3):
+        s = rb_e.sample(B)
+        outs_e.append(tuple(t.clone() for t in upd_e.update(s.observations, s.next_observations, s.actions, s.rewards, s.dones)))
+    torch.cuda.synchronize()
+    for a, b in zip(outs_g, outs_e):
+        for x, y in zip(a, b):
+            assert torch.equal(x.reshape(-1), y.reshape(-1))
+    for ng, ne in zip(nets_g, nets_e):
+        assert torch.equal(ng.flat, ne.flat)
