@@ -165,3 +165,22 @@ def test_embedder_constructor_signature():
     assert e.flat_params().data_ptr() == e.encoder.att.data_ptr()
     with pytest.raises(NotImplementedError):
         GNNEmbedder(3, 22, 2, "add", 2)
+
+
+def test_grad_regions_cover_every_parameter_and_nothing_else():
+    """DDPGUpdater all-reduces the embedder block and one block per dense layer: together they must
+    contain every parameter of the flat buffer, disjointly."""
+    from gsc_b200.models import Actor, AgentSpec, QNetwork
+    for cls in (Actor, QNetwork):
+        net = cls(AgentSpec(8))
+        gnn, layers = net.grad_regions()
+        marks = torch.zeros(net.flat.numel(), dtype=torch.int32)
+        for lo, hi in [gnn] + layers:
+            assert 0 <= lo < hi <= net.flat.numel()
+            marks[lo:hi] += 1
+        assert int(marks.max()) == 1
+        probe = torch.zeros_like(net.flat)
+        for v in net.param_views(probe):
+            v.fill_(1.0)
+        assert bool(((probe > 0) <= (marks > 0)).all()), "a parameter lies outside the all-reduced blocks"
+        assert gnn == (0, sum(p.numel() for p in net.embedder.ordered_params()) + (-sum(p.numel() for p in net.embedder.ordered_params())) % 64)
