@@ -35,6 +35,7 @@ class GscError(RuntimeError):
 
 _PROTOS = {
     "gsc_version": (c_int, []),
+    "gsc_set_sm_reserve": (c_int, [c_int]),
     "gsc_last_error": (c_char_p, []),
     "gsc_pack_csr_workspace_bytes": (c_size_t, [c_int64, c_int64]),
     "gsc_pack_csr": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_int64, c_void_p, c_void_p,

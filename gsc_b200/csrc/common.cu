@@ -1,5 +1,6 @@
 // Error reporting shared by every entry point of libgsc_b200.
 #include "common.cuh"
+#include <atomic>
 
 namespace gsc {
 
@@ -19,4 +20,15 @@ int fail(int code, const char* fmt, ...) {
 }  // namespace gsc
 
 extern "C" int gsc_version(void) { return 100; }
+
+namespace gsc {
+static std::atomic<int> g_sm_reserve{0};
+int sm_reserve() { return g_sm_reserve.load(std::memory_order_relaxed); }
+}  // namespace gsc
+
+extern "C" int gsc_set_sm_reserve(int num_sms) {
+  if (num_sms < 0 || num_sms > gsc::kNumSMs / 2) return gsc::fail(GSC_EINVAL, "gsc_set_sm_reserve: %d outside 0..%d", num_sms, gsc::kNumSMs / 2);
+  gsc::g_sm_reserve.store(num_sms, std::memory_order_relaxed);
+  return GSC_OK;
+}
 extern "C" const char* gsc_last_error(void) { return gsc::err_buf(); }

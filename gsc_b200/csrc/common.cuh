@@ -33,6 +33,8 @@ int fail(int code, const char* fmt, ...);
   } while (0)
 
 constexpr int kNumSMs = 148;  // B200
+// SMs that persistent kernels leave free for concurrently running communication kernels (gsc_set_sm_reserve)
+int sm_reserve();
 
 static inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
 static inline size_t align_up(size_t a, size_t b) { return (a + b - 1) / b * b; }

@@ -1478,9 +1478,13 @@ static bool gnn_use_tc() {
   return mode == 1;
 }
 
+// The backward kernels fill every SM they run on (registers and shared memory), so nothing else can
+// start beside them; under data parallelism a few SMs are left to the NCCL kernels that reduce the
+// dense-layer gradients meanwhile (gsc_set_sm_reserve).
 static int bwd_grid(int B, int G) {
   const int chunks = (B + G - 1) / G;
-  return chunks < kNumSMs ? chunks : kNumSMs;
+  const int sms = kNumSMs - sm_reserve();
+  return chunks < sms ? chunks : sms;
 }
 
 // Launch plan of the tcgen05 / gather backward (symmetric batches): feasible when the two-slot

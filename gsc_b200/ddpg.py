@@ -32,7 +32,8 @@ class DDPGUpdater:
     def __init__(self, actor: Actor, qf1: QNetwork, target_actor: Actor, qf1_target: QNetwork,
                  lr: float = 1e-3, gamma: float = 0.99, tau: float = 1e-4, betas=(0.9, 0.999),
                  eps: float = 1e-8, process_group=None, world_size: int = 1, rank: int = 0,
-                 shard_optimizer: bool = False, global_batch: Optional[int] = None, fork_streams: bool = False):
+                 shard_optimizer: bool = False, global_batch: Optional[int] = None, fork_streams: bool = False,
+                 sm_reserve: int = 8):
         self.actor, self.qf1, self.target_actor, self.qf1_target = actor, qf1, target_actor, qf1_target
         self.lr, self.gamma, self.tau, self.betas, self.eps = lr, gamma, tau, betas, eps
         self.pg, self.world_size = process_group, int(world_size)
@@ -56,6 +57,8 @@ class DDPGUpdater:
         self.step_critic = 0
         self.fork_streams = bool(fork_streams)
         self._side = None
+        if self.fork_streams and self.world_size > 1 and not self.shard:
+            ops.set_sm_reserve(sm_reserve)      # room for the per-layer all-reduces beside the embedder backward
         self._neg = None
         # Adam step counters in device memory: [critic, actor].  Always used, so that an eager update
         # and a CUDA-graph replay of it are the same launches.

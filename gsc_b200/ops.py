@@ -181,6 +181,11 @@ def build_mask(n: torch.Tensor, n_max: int, groups_per_node: int, out: Optional[
     return out
 
 
+def set_sm_reserve(num_sms: int) -> None:
+    """SMs the persistent embedder backward leaves free for concurrent NCCL kernels (data parallel)."""
+    check(_lib.load().gsc_set_sm_reserve(int(num_sms)), "gsc_set_sm_reserve")
+
+
 def node_features(ingress: torch.Tensor, usage: torch.Tensor, cap: torch.Tensor, graph_ptr: torch.Tensor,
                   out: Optional[torch.Tensor] = None) -> torch.Tensor:
     """x[Nt, 3] = [ingress_traffic, node_load, node_cap] of a batch of states, normalised per state as

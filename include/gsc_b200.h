@@ -43,6 +43,10 @@ extern "C" {
                                 the operands are not TMA-mappable (16 B bases, strides % 4 floats). */
 
 int gsc_version(void);
+/* Leave `num_sms` SMs (0..74, default 0) free in the persistent embedder-backward launches, for
+ * communication kernels (NCCL all-reduce of gradient blocks) that run beside them in data-parallel
+ * training.  Process-wide; no counterpart in the reference (it has no multi-GPU path). */
+int gsc_set_sm_reserve(int num_sms);
 const char* gsc_last_error(void);
 
 /* ---- batch packer ------------------------------------------------------------------------
