@@ -151,7 +151,8 @@ def run_ours(args):
         tq.load_state_dict(qf1.state_dict())
         upd = ddpg.DDPGUpdater(actor, qf1, ta, tq, lr=1e-3, gamma=0.99, tau=1e-4,
                                world_size=world, rank=rank, shard_optimizer=args.shard_optimizer,
-                               fork_streams=args.fork, sm_reserve=args.sm_reserve)
+                               fork_streams=args.fork, sm_reserve=args.sm_reserve,
+                               bucket_allreduce=args.bucket_allreduce)
 
     def host_batch(st):
         return GraphBatch.from_states(st, pin=True, dense_mask=args.dense_mask)
@@ -551,6 +552,8 @@ def main():
                     help="c3 (default): full DDPG update, the fwd+bwd+Adam step BASELINE.json's metric names; "
                          "c2: embedder + actor inference")
     ap.add_argument("--batch", type=int, default=0)
+    ap.add_argument("--bucket-allreduce", action="store_true",
+                    help="N > 1: all-reduce every dense layer's gradient block on the side stream behind the backward")
     ap.add_argument("--sm-reserve", type=int, default=8,
                     help="N > 1: SMs the embedder backward leaves free for the concurrent NCCL kernels")
     ap.add_argument("--no-fork", dest="fork", action="store_false",

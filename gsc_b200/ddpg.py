@@ -33,7 +33,7 @@ class DDPGUpdater:
                  lr: float = 1e-3, gamma: float = 0.99, tau: float = 1e-4, betas=(0.9, 0.999),
                  eps: float = 1e-8, process_group=None, world_size: int = 1, rank: int = 0,
                  shard_optimizer: bool = False, global_batch: Optional[int] = None, fork_streams: bool = False,
-                 sm_reserve: int = 8):
+                 sm_reserve: int = 8, bucket_allreduce: bool = False):
         self.actor, self.qf1, self.target_actor, self.qf1_target = actor, qf1, target_actor, qf1_target
         self.lr, self.gamma, self.tau, self.betas, self.eps = lr, gamma, tau, betas, eps
         self.pg, self.world_size = process_group, int(world_size)
@@ -57,7 +57,11 @@ class DDPGUpdater:
         self.step_critic = 0
         self.fork_streams = bool(fork_streams)
         self._side = None
-        if self.fork_streams and self.world_size > 1 and not self.shard:
+        # Per-layer all-reduces behind the embedder backward (see _bucketed) pay on 2 GPUs (1.92 -> 1.85 ms)
+        # but not on 8 (2.04 -> 2.10 ms: six collectives instead of two, and they compete with the
+        # backward for SMs), so one all-reduce per network after its backward is the default.
+        self.bucket_allreduce = bool(bucket_allreduce)
+        if self._bucketed():
             ops.set_sm_reserve(sm_reserve)      # room for the per-layer all-reduces beside the embedder backward
         self._neg = None
         # Adam step counters in device memory: [critic, actor].  Always used, so that an eager update
@@ -73,7 +77,7 @@ class DDPGUpdater:
         """Data parallel with the forked backward: every dense layer's gradient block is all-reduced on
         the side stream as soon as it is complete (behind the embedder backward); only the small
         embedder block is left for after it."""
-        return self.fork_streams and self.world_size > 1 and not self.shard
+        return self.bucket_allreduce and self.fork_streams and self.world_size > 1 and not self.shard
 
     def _layer_allreduce(self, net, g):
         if not self._bucketed():

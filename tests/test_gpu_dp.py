@@ -36,10 +36,10 @@ def _worker(rank, world, port, n_max, B, steps, out):
     mine = dp.shard_transitions(*full, rank, world)
     t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
     results = {}
-    for mode in ("allreduce", "sharded", "forked"):
+    for mode in ("allreduce", "sharded", "forked", "bucketed"):
         nets = _build(spec, dev)
         upd = ddpg.DDPGUpdater(*nets, lr=1e-3, gamma=0.99, tau=1e-2, world_size=world, rank=rank,
-                               shard_optimizer=mode == "sharded", global_batch=B, fork_streams=mode == "forked")
+                               shard_optimizer=mode == "sharded", global_batch=B, fork_streams=mode in ("forked", "bucketed"), bucket_allreduce=mode == "bucketed")
         cur, nxt = GraphBatch.from_states(mine[0], dense_mask=False).to(dev), GraphBatch.from_states(mine[1], dense_mask=False).to(dev)
         for _ in range(steps):
             qv, ql, al = upd.update(cur.view(), nxt.view(), t(mine[2]), t(mine[3]), t(mine[4]))
