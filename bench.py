@@ -355,7 +355,8 @@ def run_ours(args):
         # share of the step is reported: its algorithmic bytes over all launches / its device time
         def family(name):
             if name.startswith(("linear_", "gemm")):
-                return "gemm_tc_kernel (tcgen05 TF32)" if args.precision == "tf32" else "gemm_simt_kernel (fp32 FMA)"
+                return {"tf32": "gemm_tc_kernel (tcgen05 TF32)", "tf32x3": "gemm_tc_kernel (tcgen05 3xTF32)",
+                        "fp32": "gemm_simt_kernel (fp32 FMA)"}[args.precision]
             return name.split("[")[0] + "_kernel"
         fam_ms, fam_bytes, fam_launch = {}, {}, {}
         for k, ms in per_op.items():
@@ -381,7 +382,8 @@ def run_ours(args):
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None,
-            "dtype": "f32" if args.precision == "fp32" else "tf32 tensor-core GEMMs (fp32 accumulate), f32 elsewhere",
+            "dtype": {"fp32": "f32", "tf32": "tf32 tensor-core GEMMs (fp32 accumulate), f32 elsewhere",
+                      "tf32x3": "f32 (dense layers: 3xTF32 split on tcgen05, fp32 accumulate; fp32-faithful)"}[args.precision],
             "data": "synthetic",
             "config": {"workload": workload_name(w), "states_per_gpu": B, "n_max": n_max,
                        "precision": args.precision,
@@ -564,8 +566,10 @@ def main():
                     help="carry the dense [B, A] mask tensor instead of the per-state node counts")
     ap.add_argument("--no-graph", dest="graph", action="store_false",
                     help="c3: launch the update kernel by kernel instead of replaying its CUDA graph")
-    ap.add_argument("--precision", default=os.environ.get("GSC_BENCH_PRECISION", "tf32"), choices=["fp32", "tf32"],
-                    help="dense layers: exact fp32 FMA kernel, or tcgen05 tensor cores (TF32 operands, fp32 accumulate)")
+    ap.add_argument("--precision", default=os.environ.get("GSC_BENCH_PRECISION", "tf32x3"),
+                    choices=["fp32", "tf32", "tf32x3"],
+                    help="dense layers: tf32x3 (default) = tcgen05 tensor cores, fp32-faithful 3xTF32 split -- the mode "
+                         "the parity tests run; tf32 = single-pass TF32 operands; fp32 = exact FMA kernel")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":

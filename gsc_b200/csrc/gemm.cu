@@ -15,7 +15,7 @@ namespace gsc {
 // gemm_tc.cu
 bool gemm_tc_supported(const gsc_gemm_args* a, int64_t M, int64_t N, bool* a_mn, bool* b_mn);
 int gemm_tc_launch(const gsc_gemm_args* a, int64_t M, int64_t N, float* C, int64_t ldc, void* workspace,
-                   size_t workspace_bytes, bool a_mn, bool b_mn, cudaStream_t st, int* used_splits);
+                   size_t workspace_bytes, bool a_mn, bool b_mn, bool x3, cudaStream_t st, int* used_splits);
 
 constexpr int kBM = 64, kBN = 64, kBK = 16, kGemmThreads = 256, kPad = 4;
 
@@ -263,12 +263,13 @@ extern "C" int gsc_gemm(const gsc_gemm_args* a, int64_t M, int64_t N, float* C, 
   GSC_REQUIRE(!(g.flags & GSC_EPI_MUL) || g.mul, "gsc_gemm: GSC_EPI_MUL without mul");
   GSC_REQUIRE(!(g.flags & GSC_EPI_GATE) || g.gate, "gsc_gemm: GSC_EPI_GATE without gate");
   g.M = M; g.N = N; g.ldc = ldc; g.C = C;
-  if (a->flags & GSC_EPI_TF32) {
+  if (a->flags & (GSC_EPI_TF32 | GSC_EPI_TF32X3)) {
     bool a_mn = false, b_mn = false;
     // tiny problems stay on the exact path: the tensor-core pipeline has a fixed fill cost
     if ((double)M * (double)N * (double)tiles * kBK >= 4.0e6 && gemm_tc_supported(a, M, N, &a_mn, &b_mn)) {
       int splits = 1;
-      int rc = gemm_tc_launch(a, M, N, C, ldc, workspace, workspace_bytes, a_mn, b_mn, st, &splits);
+      int rc = gemm_tc_launch(a, M, N, C, ldc, workspace, workspace_bytes, a_mn, b_mn,
+                              (a->flags & GSC_EPI_TF32X3) != 0, st, &splits);
       if (rc) return rc;
       if (splits > 1) {
         g.splits = splits;

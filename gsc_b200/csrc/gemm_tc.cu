@@ -42,6 +42,17 @@ constexpr int kTcEpiBytes = kTcBM * kTcBN * 4;                 // 64 KB: epilogu
 constexpr int kTcSmemBytes = kTcMaxStages * kTcStageBytes + 1024 /*align*/ + 256 /*barriers*/;
 static_assert(kTcEpiStages * kTcStageBytes + kTcEpiBytes == kTcMaxStages * kTcStageBytes, "ring/epilogue split");
 constexpr int kTmemCols = 2 * kTcBN;                          // 256
+// 3xTF32 (fp32-faithful) variant: four converter warps split every staged operand tile x into
+// hi = tf32(x) (written back in place) and lo = tf32(x - hi) (written to a second ring), and the MMA
+// warp issues hi*hi + hi*lo + lo*hi.  Seven 32 KB slots: raw ring | lo ring | epilogue tile.
+constexpr int kTcX3Slots = 7;
+constexpr int kTcX3RawEpi = 3, kTcX3LoEpi = 2;                // next to the 64 KB epilogue tile
+constexpr int kTcX3RawSplit = 4, kTcX3LoSplit = 3;            // split-K launches (direct partial stores)
+constexpr int kTcConvWarps = 4;
+constexpr int kTcThreadsX3 = kTcThreads + 32 * kTcConvWarps;  // 448
+constexpr int kTcSmemBytesX3 = kTcX3Slots * kTcStageBytes + 1024 + 256;
+constexpr int kTcBarSlots = 8;                                // barrier slots per ring
+static_assert(kTcMaxStages <= kTcBarSlots && kTcX3RawSplit <= kTcBarSlots, "barrier slots");
 
 struct TcParams {
   int64_t M, N, ldc, ld_mul, ld_gate;
@@ -58,6 +69,10 @@ struct TcParams {
   int kb_end[3];          // exclusive prefix of 32-wide k-blocks per segment
   int kb_total, kb_per_split, splits, tiles_m, tiles_n;
   int stages;             // operand ring depth: kTcEpiStages with the TMA epilogue, kTcMaxStages without
+  int lo_stages;          // 3xTF32: depth of the lo ring (0 otherwise)
+  int ebuf_slot;          // first 32 KB slot of the epilogue tile
+  int bar_slot;           // slot index where the barriers start (= total slots)
+  int dbg;                // GSC_TC_DBG experiment bits: 1 no MMAs, 2 no TMA loads, 4 no epilogue body, 8 no conversion
   int epi_tma;            // 1: output tile leaves through shared memory + TMA store (coalesced, asynchronous)
   int epi_kind;           // operand streamed in by TMA for the epilogue: 0 none, 1 mul, 2 gate
 };
@@ -143,8 +158,8 @@ __device__ __forceinline__ WorkItem decode_work(const TcParams& p, int w) {
   return it;
 }
 
-template <bool A_MN, bool B_MN>
-__global__ void __launch_bounds__(kTcThreads, 1)
+template <bool A_MN, bool B_MN, bool X3>
+__global__ void __launch_bounds__(X3 ? kTcThreadsX3 : kTcThreads, 1)
 gemm_tc_kernel(const __grid_constant__ TcParams p, const __grid_constant__ CUtensorMap mapA0,
                const __grid_constant__ CUtensorMap mapA1, const __grid_constant__ CUtensorMap mapA2,
                const __grid_constant__ CUtensorMap mapB0, const __grid_constant__ CUtensorMap mapB1,
@@ -152,18 +167,22 @@ gemm_tc_kernel(const __grid_constant__ TcParams p, const __grid_constant__ CUten
                const __grid_constant__ CUtensorMap mapE) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;       // 1024 B: swizzle-128B atoms
-  const uint32_t ebuf = smem_base + kTcEpiStages * kTcStageBytes;          // epilogue tile, 4 x [128 rows x 128 B]
-  const uint32_t bar_base = smem_base + kTcMaxStages * kTcStageBytes;
-  constexpr int kTcStages = kTcMaxStages;                                  // barrier slots
+  const uint32_t ebuf = smem_base + p.ebuf_slot * kTcStageBytes;           // epilogue tile, 4 x [128 rows x 128 B]
+  const uint32_t lo_base = smem_base + p.stages * kTcStageBytes;           // 3xTF32: lo ring behind the raw ring
+  const uint32_t bar_base = smem_base + p.bar_slot * kTcStageBytes;
+  constexpr int kTcStages = kTcBarSlots;                                   // barrier slots per ring
   const int num_stages = p.stages;
-  // barriers: full[S], empty[S], tmem_full[2], tmem_empty[2], then the TMEM base address slot
+  // barriers: full[S], empty[S], lo_full[4], lo_empty[4], tmem_full[2], tmem_empty[2], epilogue
+  // operand full/empty, then the TMEM base address slot
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto empty_bar = [&](int s) { return bar_base + 8u * (kTcStages + s); };
-  auto tfull_bar = [&](int s) { return bar_base + 8u * (2 * kTcStages + s); };
-  auto tempty_bar = [&](int s) { return bar_base + 8u * (2 * kTcStages + 2 + s); };
-  const uint32_t efull_bar = bar_base + 8u * (2 * kTcStages + 4);
-  const uint32_t eempty_bar = bar_base + 8u * (2 * kTcStages + 5);
-  const uint32_t tmem_slot = bar_base + 8u * (2 * kTcStages + 6);
+  auto lofull_bar = [&](int s) { return bar_base + 8u * (2 * kTcStages + s); };
+  auto loempty_bar = [&](int s) { return bar_base + 8u * (2 * kTcStages + 4 + s); };
+  auto tfull_bar = [&](int s) { return bar_base + 8u * (2 * kTcStages + 8 + s); };
+  auto tempty_bar = [&](int s) { return bar_base + 8u * (2 * kTcStages + 10 + s); };
+  const uint32_t efull_bar = bar_base + 8u * (2 * kTcStages + 12);
+  const uint32_t eempty_bar = bar_base + 8u * (2 * kTcStages + 13);
+  const uint32_t tmem_slot = bar_base + 8u * (2 * kTcStages + 14);
   uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -171,6 +190,7 @@ gemm_tc_kernel(const __grid_constant__ TcParams p, const __grid_constant__ CUten
 
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < kTcStages; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+    for (int s = 0; s < 4; ++s) { mbar_init(lofull_bar(s), kTcConvWarps); mbar_init(loempty_bar(s), 1); }
     for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), kTcEpiWarps); }
     mbar_init(efull_bar, 1);
     mbar_init(eempty_bar, 2);                     // both column halves release the mask/gate tile
@@ -199,6 +219,7 @@ gemm_tc_kernel(const __grid_constant__ TcParams p, const __grid_constant__ CUten
           const CUtensorMap* mA = s == 0 ? &mapA0 : (s == 1 ? &mapA1 : &mapA2);
           const CUtensorMap* mB = s == 0 ? &mapB0 : (s == 1 ? &mapB1 : &mapB2);
           mbar_wait(empty_bar(stage), phase ^ 1u);
+          if (p.dbg & 2) { mbar_arrive(full_bar(stage)); if (++stage == num_stages) { stage = 0; phase ^= 1u; } continue; }
           mbar_expect_tx(full_bar(stage), kTcStageBytes);
           const uint32_t sa = smem_base + stage * kTcStageBytes;
           const uint32_t sb = sa + kTcBM * kTcBK * 4;
@@ -234,8 +255,8 @@ gemm_tc_kernel(const __grid_constant__ TcParams p, const __grid_constant__ CUten
       const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((A_MN ? 1u : 0u) << 15) |
                              ((B_MN ? 1u : 0u) << 16) | ((uint32_t)(kTcBN >> 3) << 17) |
                              ((uint32_t)(kTcBM >> 4) << 24);
-      int stage = 0;
-      uint32_t phase = 0;
+      int stage = 0, lstage = 0;
+      uint32_t phase = 0, lphase = 0;
       int iter = 0;
       for (int w = blockIdx.x; w < total_work; w += gridDim.x, ++iter) {
         const WorkItem it = decode_work(p, w);
@@ -244,21 +265,67 @@ gemm_tc_kernel(const __grid_constant__ TcParams p, const __grid_constant__ CUten
         tc_fence_after();
         const uint32_t tmem_d = tmem_base + (uint32_t)(as * kTcBN);
         for (int kb = it.kb_begin; kb < it.kb_end; ++kb) {
-          mbar_wait(full_bar(stage), phase);
+          if (X3) mbar_wait(lofull_bar(lstage), lphase);     // hi (in place) and lo images are ready
+          else mbar_wait(full_bar(stage), phase);
           tc_fence_after();
           const uint32_t sa = smem_base + stage * kTcStageBytes;
           const uint32_t sb = sa + kTcBM * kTcBK * 4;
+          const uint32_t la = lo_base + lstage * kTcStageBytes;
+          const uint32_t lb = la + kTcBM * kTcBK * 4;
 #pragma unroll
           for (int j = 0; j < kTcBK / 8; ++j) {
             // K-major: 8 k = 32 B further inside the 128 B swizzle row.  MN-major: next 8-row k group.
-            const uint64_t da = A_MN ? smem_desc(sa + j * 1024, 4096, 512, 1) : smem_desc(sa + j * 32, 16, 1024, 2);
-            const uint64_t db = B_MN ? smem_desc(sb + j * 1024, 4096, 512, 1) : smem_desc(sb + j * 32, 16, 1024, 2);
+            auto desc_a = [&](uint32_t base) { return A_MN ? smem_desc(base + j * 1024, 4096, 512, 1) : smem_desc(base + j * 32, 16, 1024, 2); };
+            auto desc_b = [&](uint32_t base) { return B_MN ? smem_desc(base + j * 1024, 4096, 512, 1) : smem_desc(base + j * 32, 16, 1024, 2); };
+            const uint64_t da = desc_a(sa), db = desc_b(sb);
+            if (p.dbg & 1) continue;
             tc_mma_tf32(tmem_d, da, db, idesc, (kb > it.kb_begin || j > 0) ? 1u : 0u);
+            if (X3) {
+              tc_mma_tf32(tmem_d, da, desc_b(lb), idesc, 1u);
+              tc_mma_tf32(tmem_d, desc_a(la), db, idesc, 1u);
+            }
           }
           tc_commit(empty_bar(stage));            // frees the smem stage once these MMAs retire
           if (++stage == num_stages) { stage = 0; phase ^= 1u; }
+          if (X3) {
+            tc_commit(loempty_bar(lstage));
+            if (++lstage == p.lo_stages) { lstage = 0; lphase ^= 1u; }
+          }
         }
         tc_commit(tfull_bar(as));                 // accumulator complete -> epilogue
+      }
+    }
+  } else if (X3 && warp >= 2 + kTcEpiWarps) {
+    // ===================== converter warps (10..13), 3xTF32 only =====================
+    // Every staged operand element x becomes hi = tf32(x), rewritten in place, and lo = tf32(x - hi)
+    // at the same offset of the lo ring (the split is elementwise, so it is layout-agnostic: K-major
+    // and MN-major swizzled tiles alike).  x - hi is exact in fp32.
+    const int ct = (warp - 2 - kTcEpiWarps) * 32 + lane;        // 0..127
+    int stage = 0, lstage = 0;
+    uint32_t phase = 0, lphase = 0;
+    for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
+      const WorkItem it = decode_work(p, w);
+      for (int kb = it.kb_begin; kb < it.kb_end; ++kb) {
+        mbar_wait(full_bar(stage), phase);                       // TMA bytes have landed
+        mbar_wait(loempty_bar(lstage), lphase ^ 1u);             // the MMAs that read this lo slot retired
+        const uint32_t src = smem_base + stage * kTcStageBytes + ct * 16;
+        const uint32_t dst = lo_base + lstage * kTcStageBytes + ct * 16;
+#pragma unroll 4
+        for (int i = 0; i < ((p.dbg & 8) ? 0 : kTcStageBytes / (16 * 32 * kTcConvWarps)); ++i) {
+          float4 v, hi, lo;
+          asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(src + i * 2048));
+          hi.x = to_tf32(v.x); lo.x = to_tf32(v.x - hi.x);
+          hi.y = to_tf32(v.y); lo.y = to_tf32(v.y - hi.y);
+          hi.z = to_tf32(v.z); lo.z = to_tf32(v.z - hi.z);
+          hi.w = to_tf32(v.w); lo.w = to_tf32(v.w - hi.w);
+          asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(src + i * 2048), "f"(hi.x), "f"(hi.y), "f"(hi.z), "f"(hi.w) : "memory");
+          asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(dst + i * 2048), "f"(lo.x), "f"(lo.y), "f"(lo.z), "f"(lo.w) : "memory");
+        }
+        fence_proxy_async_smem();                                 // st.shared -> visible to the tensor core
+        __syncwarp();
+        if (lane == 0) mbar_arrive(lofull_bar(lstage));
+        if (++stage == num_stages) { stage = 0; phase ^= 1u; }
+        if (++lstage == p.lo_stages) { lstage = 0; lphase ^= 1u; }
       }
     }
   } else {
@@ -271,6 +338,12 @@ gemm_tc_kernel(const __grid_constant__ TcParams p, const __grid_constant__ CUten
       const int as = iter & 1;
       mbar_wait(tfull_bar(as), ((uint32_t)iter >> 1) & 1u);
       tc_fence_after();
+      if (p.dbg & 4) {
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(tempty_bar(as));
+        continue;
+      }
       if (p.epi_tma) {
         // ---- TMA epilogue: accumulators (+ prefetched mask/gate tile) -> smem tile in place -> TMA store ----
         if (p.epi_kind) mbar_wait(efull_bar, (uint32_t)iter & 1u);
@@ -482,12 +555,12 @@ static int tc_round_mode() {
 }
 
 int gemm_tc_launch(const gsc_gemm_args* a, int64_t M, int64_t N, float* C, int64_t ldc, void* workspace,
-                   size_t workspace_bytes, bool a_mn, bool b_mn, cudaStream_t st, int* used_splits) {
+                   size_t workspace_bytes, bool a_mn, bool b_mn, bool x3, cudaStream_t st, int* used_splits) {
   TcParams p{};
   CUtensorMap maps[8];
   memset(maps, 0, sizeof(maps));
   int kb = 0;
-  const int rnd = tc_round_mode();
+  const int rnd = x3 ? 0 : tc_round_mode();     // 3xTF32 needs the unrounded fp32 values in shared memory
   for (int s = 0; s < a->num_seg; ++s) {
     int rc;
     if (!a_mn) rc = make_map(&maps[s], a->A[s], a->K[s], M, a->a_rs[s], kTcBK, kTcBM, rnd, false);
@@ -533,19 +606,37 @@ int gemm_tc_launch(const gsc_gemm_args* a, int64_t M, int64_t N, float* C, int64
       p.epi_tma = 1; p.epi_kind = kind;
     }
   }
-  p.stages = p.epi_tma ? kTcEpiStages : kTcMaxStages;
+  if (x3) {
+    p.stages = p.epi_tma ? kTcX3RawEpi : kTcX3RawSplit;
+    p.lo_stages = p.epi_tma ? kTcX3LoEpi : kTcX3LoSplit;
+    p.ebuf_slot = kTcX3RawEpi + kTcX3LoEpi;
+    p.bar_slot = kTcX3Slots;
+  } else {
+    p.stages = p.epi_tma ? kTcEpiStages : kTcMaxStages;
+    p.lo_stages = 0;
+    p.ebuf_slot = kTcEpiStages;
+    p.bar_slot = kTcMaxStages;
+  }
+  { const char* e = getenv("GSC_TC_DBG"); p.dbg = e ? atoi(e) : 0; }
   const int64_t work = tiles * p.splits;
   const int grid = (int)(work < kNumSMs ? work : kNumSMs);
+  const int smem = x3 ? kTcSmemBytesX3 : kTcSmemBytes;
+  const int threads = x3 ? kTcThreadsX3 : kTcThreads;
 
   auto launch = [&](auto kernel) -> int {
-    GSC_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemBytes));
-    kernel<<<grid, kTcThreads, kTcSmemBytes, st>>>(p, maps[0], maps[1], maps[2], maps[3], maps[4], maps[5], maps[6], maps[7]);
+    GSC_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    kernel<<<grid, threads, smem, st>>>(p, maps[0], maps[1], maps[2], maps[3], maps[4], maps[5], maps[6], maps[7]);
     GSC_LAUNCH_CHECK("gemm_tc_kernel");
     return GSC_OK;
   };
-  if (!a_mn && !b_mn) return launch(gemm_tc_kernel<false, false>);
-  if (!a_mn && b_mn) return launch(gemm_tc_kernel<false, true>);
-  return launch(gemm_tc_kernel<true, true>);
+  if (x3) {
+    if (!a_mn && !b_mn) return launch(gemm_tc_kernel<false, false, true>);
+    if (!a_mn && b_mn) return launch(gemm_tc_kernel<false, true, true>);
+    return launch(gemm_tc_kernel<true, true, true>);
+  }
+  if (!a_mn && !b_mn) return launch(gemm_tc_kernel<false, false, false>);
+  if (!a_mn && b_mn) return launch(gemm_tc_kernel<false, true, false>);
+  return launch(gemm_tc_kernel<true, true, false>);
 }
 
 }  // namespace gsc

@@ -161,6 +161,7 @@ __global__ void __launch_bounds__(kGnnThreads, 2) gnn_fwd_kernel(const GnnArgs p
     const int g0 = chunk * p.G, g1 = min(p.B, g0 + p.G);
     const int nbase = p.graph_ptr[g0];
     const int nc = p.graph_ptr[g1] - nbase;
+    if (nc > p.cap) __trap();     // a graph larger than the max_nodes the launch was sized for: fail loudly
 
     for (int a = 0; a < p.num_apps; ++a) {
       const int cv = p.app_conv[a];
@@ -393,6 +394,7 @@ __global__ void __launch_bounds__(kGnnThreads, 2) gnn_fwd_tc_kernel(const GnnArg
     const int g0 = chunk * p.G, g1 = min(p.B, g0 + p.G);
     const int nbase = p.graph_ptr[g0];
     const int nc = p.graph_ptr[g1] - nbase;
+    if (nc > p.cap) __trap();     // a graph larger than the max_nodes the launch was sized for: fail loudly
     const int warp_first = tid & ~31;                                // slot loops must be warp-uniform (tcgen05.ld)
     // the chunk's CSR rows are walked by every application: stage them in shared memory once
     const int ebase = p.rowptr[nbase];
@@ -578,6 +580,7 @@ __global__ void __launch_bounds__(kGnnThreads, 1) gnn_bwd_kernel(const GnnArgs p
     const int g0 = chunk * p.G, g1 = min(p.B, g0 + p.G);
     const int nbase = p.graph_ptr[g0];
     const int nc = p.graph_ptr[g1] - nbase;
+    if (nc > p.cap) __trap();     // a graph larger than the max_nodes the launch was sized for: fail loudly
 
     // d_out of the last application = pool backward: d_emb[g] / n_g (times ReLU' if it had one).
     for (int t = threadIdx.x; t < (g1 - g0) * HP; t += kGnnThreads) {
@@ -937,6 +940,7 @@ __global__ void __launch_bounds__(kGnnThreads, 1) gnn_bwd_tc_kernel(const GnnArg
     const int g0 = chunk * p.G, g1 = min(p.B, g0 + p.G);
     const int nbase = p.graph_ptr[g0];
     const int nc = p.graph_ptr[g1] - nbase;
+    if (nc > p.cap) __trap();     // a graph larger than the max_nodes the launch was sized for: fail loudly
     const int warp_first = tid & ~31;
     const int used_tiles = (nc + 127) >> 7;
     GSC_TICK(0);
@@ -1532,6 +1536,7 @@ static int launch_bwd_both(GnnArgs a, int max_nodes, float* d_params, cudaStream
     a.gather_kernel_launched = 1;
   }
   if (global_rows) {
+    GSC_CUDA_TRY(cudaFuncSetAttribute(gnn_bwd_kernel<HP, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_f));
     gnn_bwd_kernel<HP, true><<<grid, kGnnThreads, smem_f, st>>>(a);
   } else {
     GSC_CUDA_TRY(cudaFuncSetAttribute(gnn_bwd_kernel<HP, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_f));

@@ -265,11 +265,15 @@ class GraphedUpdate:
             self.idx.copy_(self.idx_h[0])
             self.ptrs.copy_(self.ptrs_h[0])
         cl = lambda t: None if t is None else t.clone()
+        # The embedder kernels size their shared memory from max_nodes, which is frozen into the graph:
+        # a structured batch is captured at the environment limit n_max, so that every later minibatch
+        # fits; other batches are checked against the captured value in ``load``.
+        cap_nodes = lambda gb: gb.n_max if gb.structured else gb.max_nodes
         mk = lambda gb, share=None: GraphBatch(
             gb.x.clone(), gb.edge_index.clone() if share is None else share.edge_index,
             gb.batch.clone() if share is None else share.batch,
             (cl(gb._mask) if not gb.structured else None) if share is None else share._mask,
-            gb.num_graphs, gb.max_nodes, None,
+            gb.num_graphs, cap_nodes(gb), None,
             cl(gb.n_nodes) if share is None else share.n_nodes, gb.n_max, gb.groups)
         self.cur = mk(cur)
         self.nxt = mk(nxt, self.cur if nxt.edge_index is cur.edge_index else None)
@@ -293,10 +297,19 @@ class GraphedUpdate:
         torch.cuda.current_stream().wait_stream(side)
         restore()
         torch.cuda.synchronize()
+        # capture on the stream the warm-up ran on: the workspaces are per stream, so the warm-up has
+        # sized exactly the buffers the captured launches use (nothing is allocated during capture)
         self.graph = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(self.graph):
+        with torch.cuda.graph(self.graph, stream=side):
             self.out = self._run()
         restore()
+
+    def close(self) -> None:
+        """Destroy the captured graph.  A graph that captured NCCL collectives keeps the communicator
+        alive: call this (on every rank) before ``torch.distributed.destroy_process_group()``."""
+        torch.cuda.synchronize()
+        self.graph = None
+        self.out = None
 
     def _run(self):
         if self.rb is not None:
@@ -324,6 +337,10 @@ class GraphedUpdate:
     def load(self, cur: GraphBatch, nxt: GraphBatch, actions, rewards, dones, non_blocking: bool = True):
         """Copy a minibatch (host or device tensors of the captured shapes) into the static inputs."""
         nb = non_blocking
+        for new, own in ((cur, self.cur), (nxt, self.nxt)):
+            if new.max_nodes is not None and own.max_nodes is not None and new.max_nodes > own.max_nodes:
+                raise ValueError(f"minibatch holds a graph of {new.max_nodes} nodes; the graph was captured for at "
+                                 f"most {own.max_nodes} nodes per graph")
         self.cur.x.copy_(cur.x, non_blocking=nb)
         self.cur.edge_index.copy_(cur.edge_index, non_blocking=nb)
         self.cur.batch.copy_(cur.batch, non_blocking=nb)
@@ -371,8 +388,11 @@ class GraphedPredict:
         gb = GraphBatch.wrap(obs)
         cl = lambda t: None if t is None else t.clone()
         self.actor = actor
+        # max_nodes is frozen into the graph (it sizes the embedder's shared memory): a structured batch
+        # is captured at the environment limit, other batches are checked in ``load``
         self.gb = GraphBatch(gb.x.clone(), gb.edge_index.clone(), cl(gb.batch),
-                             None if gb.structured else cl(gb._mask), gb.num_graphs, gb.max_nodes, None,
+                             None if gb.structured else cl(gb._mask), gb.num_graphs,
+                             gb.n_max if gb.structured else gb.max_nodes, None,
                              cl(gb.n_nodes), gb.n_max, gb.groups)
         if self.gb.max_nodes is None:
             gb.csr()
@@ -385,12 +405,15 @@ class GraphedPredict:
         torch.cuda.current_stream().wait_stream(side)
         torch.cuda.synchronize()
         self.graph = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(self.graph):
+        with torch.cuda.graph(self.graph, stream=side):          # same stream as the warm-up (per-stream workspaces)
             self.out = predict(actor, self.gb.view())
 
     def load(self, obs, non_blocking: bool = True) -> None:
         gb = GraphBatch.wrap(obs)
         nb = non_blocking
+        if gb.max_nodes is not None and gb.max_nodes > self.gb.max_nodes:
+            raise ValueError(f"batch holds a graph of {gb.max_nodes} nodes; the graph was captured for at most "
+                             f"{self.gb.max_nodes} nodes per graph")
         self.gb.x.copy_(gb.x, non_blocking=nb)
         self.gb.edge_index.copy_(gb.edge_index, non_blocking=nb)
         if self.gb.batch is not None:

@@ -386,8 +386,10 @@ def net_backward(net: _FlatNet, flat: torch.Tensor, gb: GraphBatch, ctx, dz: tor
     A = net.action_dim
     d_action = None
     d = dz
+    keep = []          # output gradients that the side stream reads: alive until the streams are joined
     for i in range(len(lins) - 1, -1, -1):
         W, _, Wp, pad = lins[i]
+        keep.append(d)
         if grad_flat is not None:
             def layer_grads(i=i, d=d, pad=pad):
                 if i == 0 and st:
@@ -419,6 +421,7 @@ def net_backward(net: _FlatNet, flat: torch.Tensor, gb: GraphBatch, ctx, dz: tor
         done = torch.cuda.Event()
         done.record(side)
         main.wait_event(done)               # gradients complete, and nothing read on `side` is released early
+    del keep
     return d_action
 
 

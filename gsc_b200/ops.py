@@ -15,11 +15,17 @@ from ._lib import EPI_BIAS, EPI_CLAMP1, EPI_GATE, EPI_MUL, EPI_RELU, GemmArgs, c
 _workspaces = {}
 launch_count = 0          # kernels enqueued through this module (bench.py reports it)
 
-# Arithmetic of the dense layers: "fp32" = exact FMA kernel (parity mode, default),
-# "tf32" = tcgen05 tensor cores (TF32 operands, fp32 accumulate in TMEM) where the operands are
-# TMA-mappable.  Tolerances of the two modes are stated separately in tests/ and DESIGN.md.
-precision = "fp32"
+# Arithmetic of the dense layers (tolerances of the modes are stated separately in tests/ and DESIGN.md):
+#   "tf32x3" (default) tcgen05 tensor cores, fp32-faithful: operands split hi + lo in shared memory,
+#                      hi*hi + hi*lo + lo*hi with fp32 accumulation in TMEM -- the parity mode AND the
+#                      mode bench.py times;
+#   "tf32"             single-pass TF32 operands (10 mantissa bits), the fast mode;
+#   "fp32"             exact FMA kernel (also what the tensor-core modes fall back to for operands
+#                      that TMA cannot map and for tiny problems).
+precision = "tf32x3"
+PRECISIONS = ("fp32", "tf32", "tf32x3")
 EPI_TF32 = 32
+EPI_TF32X3 = 256
 # Use the node counts instead of the dense mask whenever a batch carries them (GraphBatch.structured).
 use_structured_mask = True
 
@@ -28,7 +34,7 @@ class use_precision:
     """Context manager: ``with ops.use_precision("tf32"): ...``"""
 
     def __init__(self, mode: str):
-        if mode not in ("fp32", "tf32"):
+        if mode not in PRECISIONS:
             raise ValueError(mode)
         self.mode = mode
 
@@ -164,7 +170,7 @@ def pack_csr_noalloc(edge_index: torch.Tensor, batch: Optional[torch.Tensor], nu
         check(lib.gsc_pack_csr_noalloc(_ptr(edge_index), E, _ptr(batch), num_nodes, num_graphs, _ptr(rowptr),
                                        _ptr(col), _ptr(graph_ptr), _ptr(stats), _stream()),
               "gsc_pack_csr_noalloc")
-    _count(9 if E > 0 else 7)
+    _count(10 if E > 0 else 8)
     return rowptr, col, graph_ptr, stats
 
 
@@ -303,6 +309,10 @@ def gemm_raw(segs: Sequence[tuple], M: int, N: int, out: torch.Tensor, flags: in
         ktot += K
     if precision == "tf32":
         flags |= EPI_TF32
+    elif precision == "tf32x3":
+        flags |= EPI_TF32X3
+    elif precision != "fp32":
+        raise _lib.GscError(f"ops.precision = {precision!r}: expected one of {PRECISIONS}")
     args.num_seg, args.flags = len(segs), flags
     args.bias = _ptr(bias)
     if mul is not None:

@@ -41,6 +41,10 @@ extern "C" {
 #define GSC_EPI_TF32 32      /* allow the tensor-core path: tcgen05 kind::tf32, fp32 accumulate.
                                 Without it the GEMM is exact fp32 (FMA).  Falls back to fp32 when
                                 the operands are not TMA-mappable (16 B bases, strides % 4 floats). */
+#define GSC_EPI_TF32X3 256   /* tensor-core path that stays fp32-faithful: every operand is split in
+                                shared memory into x = hi + lo (both exact TF32 values) and the
+                                product is hi*hi + hi*lo + lo*hi with fp32 accumulation (3xTF32,
+                                relative error ~2^-21 per product).  Takes precedence over TF32. */
 
 int gsc_version(void);
 /* Leave `num_sms` SMs (0..74, default 0) free in the persistent embedder-backward launches, for
@@ -74,7 +78,8 @@ int gsc_pack_csr(const int64_t* edge_index, int64_t num_edges, const int64_t* ba
  * that bind this C-ABI with a fixed device-memory budget and no caching allocator.
  * Limit: num_nodes <= GSC_PACK_NOALLOC_MAX_NODES, otherwise GSC_EINVAL (use gsc_pack_csr).
  * The first call on a device looks up the array's device address -- make it before any stream
- * capture.  All calls on a device share the array: the packer rewrites every element it reads, so
+ * capture.  The array is found through the CURRENT device (cudaGetDevice), so the device that
+ * `stream` belongs to must be current when this is called.  All calls on a device share the array: the packer rewrites every element it reads, so
  * stale contents are harmless, but calls that overlap on the GPU race and must be serialised. */
 #define GSC_PACK_NOALLOC_MAX_NODES (1 << 20)
 int gsc_pack_csr_noalloc(const int64_t* edge_index, int64_t num_edges, const int64_t* batch,

@@ -178,10 +178,17 @@ def test_gnn_embed_bwd_directed_graph_uses_scatter_kernel():
 
 
 # ------------------------------------------------------------------ GEMM family
+@pytest.fixture(params=["fp32", "tf32x3"])
+def dense_precision(request):
+    """The rel-2e-5 GEMM tests run on the exact FMA kernel and on the 3xTF32 tensor-core kernel."""
+    with ops.use_precision(request.param):
+        yield request.param
+
+
 @pytest.mark.parametrize("M,N,Ks", [(100, 64, (22, 1728, 1728)), (100, 256, (22, 1728)), (37, 5, (3,)),
                                     (4096, 130, (256,)), (100, 1, (64,)), (8, 64, (22, 30000, 30000)),
                                     (1, 256, (22, 1728))])
-def test_linear_fwd_segments(M, N, Ks):
+def test_linear_fwd_segments(M, N, Ks, dense_precision):
     gen = torch.Generator().manual_seed(M + N)
     xs = [torch.randn(M, K, generator=gen, dtype=torch.float64) for K in Ks]
     W = torch.randn(N, sum(Ks), generator=gen, dtype=torch.float64) / np.sqrt(sum(Ks))
@@ -196,7 +203,7 @@ def test_linear_fwd_segments(M, N, Ks):
     assert rel_err(got2.cpu().numpy(), ref2.numpy()) < 2e-5
 
 
-def test_linear_fwd_strided_padded_weight():
+def test_linear_fwd_strided_padded_weight(dense_precision):
     gen = torch.Generator().manual_seed(0)
     M, N, K = 50, 40, 22 + 96
     store = torch.zeros(N, 124, device=DEV)
@@ -209,7 +216,7 @@ def test_linear_fwd_strided_padded_weight():
 
 
 @pytest.mark.parametrize("M,N,K", [(100, 64, 1728), (100, 1728, 256), (4096, 256, 22), (64, 30000, 256), (3, 1, 64)])
-def test_linear_dgrad_and_wgrad(M, N, K):
+def test_linear_dgrad_and_wgrad(M, N, K, dense_precision):
     gen = torch.Generator().manual_seed(M + K)
     dY = torch.randn(M, N, generator=gen, dtype=torch.float64)
     W = torch.randn(N, K + 10, generator=gen, dtype=torch.float64)
@@ -229,7 +236,7 @@ def test_linear_dgrad_and_wgrad(M, N, K):
     assert rel_err(ops.colsum(dY.float().to(DEV)).cpu().numpy(), dY.sum(0).numpy()) < 2e-5
 
 
-def test_gemm_is_deterministic_under_split_k():
+def test_gemm_is_deterministic_under_split_k(dense_precision):
     gen = torch.Generator().manual_seed(5)
     x = torch.randn(100, 60000, generator=gen).to(DEV)
     W = torch.randn(64, 60000, generator=gen).to(DEV)

@@ -1,0 +1,20 @@
+#!/bin/bash
+# round 2, call 1: full GPU test suite on the 3xTF32 build, GEMM probe, bench in both tensor-core modes
+set -u
+O=gpurun_out; mkdir -p $O
+timeout 900 python -m pytest tests -m gpu -x -q > $O/r2_tests1.log 2>&1; echo "pytest rc=$?"
+tail -15 $O/r2_tests1.log
+timeout 300 python tools/gemm_probe.py > $O/r2_gemm_probe1.log 2>&1; echo "probe rc=$?"
+cat $O/r2_gemm_probe1.log
+timeout 300 python bench.py --precision tf32 > $O/r2_bench_c3_tf32_a.json 2> $O/r2_bench_c3_tf32_a.err; echo "bench tf32 rc=$?"
+timeout 300 python bench.py --precision tf32x3 > $O/r2_bench_c3_x3_a.json 2> $O/r2_bench_c3_x3_a.err; echo "bench x3 rc=$?"
+python - <<'PY'
+import json
+for f in ("r2_bench_c3_tf32_a", "r2_bench_c3_x3_a"):
+    try:
+        d = json.loads(open(f"gpurun_out/{f}.json").read().strip().splitlines()[-1])
+        print(f, d["ms_per_step"], d["value"], d["e2e"]["value"], d["roofline"]["per_kernel_ms"])
+    except Exception as e:
+        print(f, "failed", e)
+PY
+tail -5 $O/r2_bench_c3_x3_a.err
