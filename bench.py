@@ -1,15 +1,19 @@
 #!/usr/bin/env python
-"""Benchmark of the GSC hot path on B200 (contract: see the task statement / DESIGN.md section 6).
+"""Benchmark of the GSC hot path on B200 (contract: see the task statement / DESIGN.md section 5).
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c2|c3] [--batch B]
-  python bench.py --impl reference ...     # the CPU oracle on the box's host cores
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c2|c3|c4|c5] [--batch B]
+  python bench.py --impl reference ...     # the CPU oracle on the box's host cores, same workload
 
-A "step" is one pass of the hot path over one batch of synthetic network states:
+A "step" is one pass of the hot path over one batch of synthetic network states (SURVEY.md 8d):
   c2  batch packer + GNN embedder + actor MLP inference  (B = 4096 states, N_max = 24, n ~ U{16..24})
   c3  full DDPG update: packer, 5 forward + 3 backward passes, 2 fused Adam/soft-update launches
-      (N_max = n = 100, |E| = 150, replay minibatch of B states per GPU)
-For N > 1 every rank works on its own B states (weak scaling); c3 all-reduces the flat gradient
-buffers over NCCL, c2 has no collective.  One JSON line is printed by rank 0.
+      (N_max = n = 100, |E| = 150, replay minibatch of B = 1024 states per GPU)      [default]
+  c4  the same update on 1000-node topologies (A = 3 000 000, 1.92 G parameters), B = 32 states per
+      GPU; for N > 1 the optimizer is sharded (reduce-scatter, Adam on 1/N, all-gather)
+  c5  inference on 65 536 states of the largest bundled topology size (N_max = n = 110, |E| = 148)
+For N > 1 every rank works on its own B states (weak scaling); the training workloads exchange the
+flat gradient buffers over NCCL, the inference workloads have no collective (replicas).  One JSON
+line is printed by rank 0.
 """
 from __future__ import annotations
 
@@ -40,33 +44,53 @@ def measured_peaks():
 
 
 # ------------------------------------------------------------------------------------------------
-def make_workload(args, rank: int):
+# name -> (kind, N_max, n_low, n_high, links per state (None: round(1.5 n)), default states per GPU)
+# kind "c2" = inference step, "c3" = DDPG update step (the two step shapes of the hot path).
+WORKLOADS = {"c2": ("c2", 24, 16, 24, None, 4096), "c3": ("c3", 100, 100, 100, 150, 1024),
+             "c4": ("c3", 1000, 1000, 1000, 1500, 32), "c5": ("c2", 110, 110, 110, 148, 65536)}
+
+
+def make_workload(args, rank: int, max_states: int = 0):
+    """``max_states``: generate only that many states (the CPU arm's bounded sample of a large workload)."""
     from gsc_b200 import synth
     seed = 1234 + 1000 * rank
-    if args.workload == "c2":
-        B = args.batch or 4096
-        st = synth.make_states(B, 24, 16, 24, seed=seed)
-        return dict(kind="c2", B=B, n_max=24, cur=st)
-    B = args.batch or 1024
-    cur, nxt, actions, rewards, dones = synth.make_transitions(B, 100, 100, 100, seed=seed, fixed_links=150,
-                                                               num_topologies=32)
-    return dict(kind="c3", B=B, n_max=100, cur=cur, nxt=nxt, actions=actions, rewards=rewards, dones=dones)
+    kind, n_max, lo, hi, links, B = WORKLOADS[args.workload]
+    B = args.batch or B
+    G = min(B, max_states) if max_states else B
+    base = dict(kind=kind, name=args.workload, B=B, n_max=n_max, n_low=lo, n_high=hi, links=links)
+    if kind == "c2":
+        st = synth.make_states(G, n_max, lo, hi, seed=seed, fixed_links=links,
+                               num_topologies=None if args.workload == "c2" else 24)
+        return dict(base, cur=st)
+    cur, nxt, actions, rewards, dones = synth.make_transitions(G, n_max, lo, hi, seed=seed, fixed_links=links,
+                                                               num_topologies=32 if n_max <= 100 else 4)
+    return dict(base, cur=cur, nxt=nxt, actions=actions, rewards=rewards, dones=dones)
 
 
 def workload_name(w):
-    if w["kind"] == "c2":
-        return f"c2: batch packer + GNN embedder + actor inference, B={w['B']}/GPU, N_max=24, n~U{{16..24}}, |E|=round(1.5n)"
-    return f"c3: full DDPG update (fwd+bwd+Adam+target), B={w['B']}/GPU, N_max=n=100, |E|=150"
+    size = (f"N_max={w['n_max']}, n~U{{{w['n_low']}..{w['n_high']}}}" if w["n_low"] != w["n_high"]
+            else f"N_max=n={w['n_max']}")
+    links = "|E|=round(1.5n)" if w["links"] is None else f"|E|={w['links']}"
+    what = "batch packer + GNN embedder + actor inference" if w["kind"] == "c2" else "full DDPG update (fwd+bwd+Adam+target)"
+    return f"{w['name']}: {what}, B={w['B']}/GPU, {size}, {links}"
 
 
-def algorithmic_bytes(w, Pa: int, Pc: int) -> float:
-    """SURVEY.md section 8d formulas with the actual n, e, A, B of this batch."""
+def make_config(w):
+    """The workload description; identical in the GPU arm and in the --impl reference arm."""
+    return {"workload": workload_name(w), "states_per_gpu": w["B"], "n_max": w["n_max"],
+            "action_dim": w["n_max"] * w["n_max"] * 3, "gnn": "3 features -> 22 hidden, 2 layers x 2 iterations, mean aggregation",
+            "weights": "reference init (PyG glorot / torch Linear), seeded", "seed": 1234}
+
+
+def algorithmic_bytes(w, Pa: int, Pc: int, opt_div: int = 1) -> float:
+    """SURVEY.md section 8d formulas with the actual n, e, A, B of this batch (``opt_div``: the
+    optimizer's share of the 48 B/param is divided by the world size when it is sharded)."""
     st = w["cur"]
     Nt, E, B, A = st.x.shape[0], st.edge_index.shape[1], st.num_graphs, st.action_dim
     graph = 4.0 * Nt * 3 + 16.0 * E + 8.0 * Nt          # 4nF + 16e (two int64 per directed edge) + 8n (batch)
     if w["kind"] == "c2":
         return graph + 4.0 * A * B * 2 + 4.0 * Pa
-    return 2 * (graph + 4.0 * A * B) + (4.0 * A + 8) * B + 48.0 * (Pa + Pc)
+    return 2 * (graph + 4.0 * A * B) + (4.0 * A + 8) * B + (16.0 + 32.0 / opt_div) * (Pa + Pc)
 
 
 # ------------------------------------------------------------------------------------------------
@@ -134,6 +158,7 @@ def run_ours(args):
     dev = torch.device("cuda", local)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
+    shard_opt = (args.shard_optimizer if args.shard_optimizer is not None else args.workload == "c4") and world > 1
     w = make_workload(args, rank)
     B, n_max = w["B"], w["n_max"]
     ops.precision = args.precision
@@ -150,7 +175,7 @@ def run_ours(args):
         ta.load_state_dict(actor.state_dict())
         tq.load_state_dict(qf1.state_dict())
         upd = ddpg.DDPGUpdater(actor, qf1, ta, tq, lr=1e-3, gamma=0.99, tau=1e-4,
-                               world_size=world, rank=rank, shard_optimizer=args.shard_optimizer,
+                               world_size=world, rank=rank, shard_optimizer=shard_opt,
                                fork_streams=args.fork, sm_reserve=args.sm_reserve,
                                bucket_allreduce=args.bucket_allreduce)
 
@@ -288,8 +313,8 @@ def run_ours(args):
             out_host.copy_(ddpg.predict(actor, gb), non_blocking=True)
         h2d = sum(t_.numel() * t_.element_size() for t_ in e2e_in)
     else:
-        cap = max(2 * B, 2048)
-        rb = DeviceGraphReplayBuffer(cap, spec.env.action_space, device=dev, n_max=n_max, e_max=2 * 150 + 4)
+        cap = max(2 * B, 2048 if n_max <= 100 else 64)      # the action rows are 4A bytes each (12 MB at N_max = 1000)
+        rb = DeviceGraphReplayBuffer(cap, spec.env.action_space, device=dev, n_max=n_max, e_max=2 * (w["links"] or 2 * n_max) + 4)
         for _ in range(cap // B - 1):                                   # leave room for the streamed adds
             rb.bulk_load(w["cur"], w["nxt"], w["actions"], w["rewards"], w["dones"])
         g0 = st0.graph(0)
