@@ -292,6 +292,7 @@ def run_ours(args):
     from gsc_b200.buffer import BufferSample, DeviceGraphReplayBuffer
     from gsc_b200.graph import GraphData
     st0 = w["cur"]
+    g_e2e_ref = []
     if w["kind"] == "c2":
         h_n = torch.from_numpy(st0.n.astype(np.int32)).pin_memory()
         e2e_in = [host["cur"].x, host["cur"].edge_index, host["cur"].batch, h_n]
@@ -333,6 +334,7 @@ def run_ours(args):
                 n0 = GraphBatch(n0.x, c0.edge_index, c0.batch, None, n0.num_graphs, c0.max_nodes, None,
                                 c0.n_nodes, c0.n_max, c0.groups)
                 g_e2e = ddpg.GraphedUpdate(upd, c0, n0, smp0.actions, smp0.rewards, smp0.dones, replay=rb)
+                g_e2e_ref.append(g_e2e)
 
         def e2e_step():
             if rb.pos + 1 >= rb.buffer_size:
@@ -369,40 +371,51 @@ def run_ours(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     dev_ms, e2e_ms = float(t[0]), float(t[1])
 
+    parity = dp_parity(upd, dev, rank, world, args, shard_opt) if (world > 1 and upd is not None) else None
+
     if rank == 0:
         hbm, which = measured_peaks()
         total_states = B * world * args.steps
         value = total_states / (dev_ms / 1e3)
         e2e_value = total_states / (e2e_ms / 1e3)
         d2h = out_host.numel() * 4
-        # dominant kernel + roofline: entry points are grouped by the kernel that does their work
-        # (all dense-layer calls run gemm_tc_kernel / gemm_simt_kernel), the group with the largest
-        # share of the step is reported: its algorithmic bytes over all launches / its device time
-        def family(name):
-            if name.startswith(("linear_", "gemm")):
-                return {"tf32": "gemm_tc_kernel (tcgen05 TF32)", "tf32x3": "gemm_tc_kernel (tcgen05 3xTF32)",
-                        "fp32": "gemm_simt_kernel (fp32 FMA)"}[args.precision]
-            return name.split("[")[0] + "_kernel"
-        fam_ms, fam_bytes, fam_launch = {}, {}, {}
+        # Dominant kernel + roofline.  Every timed entry point (name[shape]) launches one kernel (plus, for
+        # split-K GEMMs, a small finalize); the entry point with the largest total time in the step is
+        # reported under its kernel's name: algorithmic bytes of its launches / its device time.  The
+        # per-kernel times come from a kernel-by-kernel pass of the same step (serialised: no overlap
+        # between streams), so their sum exceeds the graph-timed step; shares, not absolutes, compare.
+        def kernel_of(name):
+            base = name.split("[")[0]
+            if base.startswith(("linear_", "gemm")):
+                role = {"linear_fwd": "<K-major,K-major>", "linear_dgrad": "<K-major,MN-major>",
+                        "linear_wgrad": "<MN-major,MN-major>"}.get(base, "")
+                kern = {"tf32": "gemm_tc_kernel", "tf32x3": "gemm_tc_kernel", "fp32": "gemm_simt_kernel"}[args.precision]
+                mode = {"tf32": "tcgen05 TF32", "tf32x3": "tcgen05 3xTF32", "fp32": "fp32 FMA"}[args.precision]
+                return f"{kern}{role} {name[name.index('['):]} ({mode})"
+            return {"gnn_bwd": "gnn_bwd_tc_kernel", "gnn_fwd": "gnn_fwd_tc_kernel", "adam_soft_update": "adam_soft_dev_kernel",
+                    "pack_csr": "pack_csr kernels"}.get(base, base + "_kernel") + (name[name.index("["):] if "[" in name else "")
+        top_op = max(per_op, key=per_op.get)
+        top_ms = per_op[top_op]
+        alg_b = op_bytes(top_op, w, Pa, Pc) * per_op_n[top_op]
+        step_bytes = algorithmic_bytes(w, Pa, Pc, world if shard_opt else 1)
+        fam = {}
         for k, ms in per_op.items():
-            f = family(k)
-            fam_ms[f] = fam_ms.get(f, 0.0) + ms
-            fam_bytes[f] = fam_bytes.get(f, 0.0) + op_bytes(k, w, Pa, Pc) * per_op_n[k]
-            fam_launch[f] = fam_launch.get(f, 0.0) + per_op_n[k]
-        top = max(fam_ms, key=fam_ms.get)
-        top_ms = fam_ms[top]
-        alg_b = fam_bytes[top]
-        step_bytes = algorithmic_bytes(w, Pa, Pc)
-        roof = {"bound": "hbm", "kernel": top, "achieved": alg_b / (top_ms / 1e3) / 1e9, "peak": hbm,
+            f = k.split("[")[0]
+            fam[f] = fam.get(f, 0.0) + ms
+        roof = {"bound": "hbm", "kernel": kernel_of(top_op), "achieved": alg_b / (top_ms / 1e3) / 1e9, "peak": hbm,
                 "unit": "GB/s", "frac": alg_b / (top_ms / 1e3) / 1e9 / hbm,
-                "traffic": profiled_traffic(w, args, top),
-                "peak_source": which, "kernel_ms_per_step": top_ms, "kernel_launches_per_step": fam_launch[top],
-                "kernel_share_of_step": top_ms / sum(fam_ms.values()),
-                "algorithmic_bytes_per_step": alg_b,
+                "traffic": profiled_traffic(w, args, top_op),
+                "peak_source": which, "kernel_ms_per_step": top_ms, "kernel_launches_per_step": per_op_n[top_op],
+                "kernel_share_of_step": top_ms / sum(per_op.values()),
+                "algorithmic_bytes_per_launch": alg_b / per_op_n[top_op],
+                "timing": "CUDA events around each entry point, kernel-by-kernel pass of the same step (serialised)",
                 "step_algorithmic_bytes": step_bytes,
                 "step_frac_of_hbm_roofline": step_bytes / (dev_ms / args.steps / 1e3) / 1e9 / hbm,
-                "per_kernel_ms": {k: round(v, 4) for k, v in sorted(fam_ms.items(), key=lambda kv: -kv[1])}}
-        cpu = cpu_baseline(args, w, sample_states=min(B, 256 if w["kind"] == "c3" else 4096))
+                "per_entry_point_family_ms": {k: round(v, 4) for k, v in sorted(fam.items(), key=lambda kv: -kv[1])}}
+        # the CPU oracle is timed on rank 0 at N = 1 only (other ranks would spin in a barrier meanwhile)
+        cpu = cpu_baseline(args, w, sample_states=min(B, {"c2": 4096, "c3": 256, "c4": 2, "c5": 1024}[w["name"]])) \
+            if world == 1 else None
+        par = (f"dp{world}" + ("+sharded-optimizer" if shard_opt else "")) if w["kind"] == "c3" else f"replicas{world}"
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
@@ -410,15 +423,12 @@ def run_ours(args):
             "dtype": {"fp32": "f32", "tf32": "tf32 tensor-core GEMMs (fp32 accumulate), f32 elsewhere",
                       "tf32x3": "f32 (dense layers: 3xTF32 split on tcgen05, fp32 accumulate; fp32-faithful)"}[args.precision],
             "data": "synthetic",
-            "config": {"workload": workload_name(w), "states_per_gpu": B, "n_max": n_max,
-                       "precision": args.precision,
-                       "streams": "3 forward chains forked" if (args.fork and w["kind"] == "c3") else "single",
-                       "mask": "dense [B, A] tensor" if args.dense_mask else "structured: mask[:n,:,:,:n] from node counts",
-                       "cuda_graph": bool(graphed is not None or gpredict is not None),
-                       "weights": "reference init (PyG glorot / torch Linear), torch.manual_seed(1234)",
-                       "l2": "flushed between timed steps (256 MiB write)",
-                       "parallelism": (f"dp{world}" + ("+sharded-optimizer" if args.shard_optimizer and world > 1 else ""))
-                       if w["kind"] == "c3" else f"replicas{world}"},
+            "config": dict(make_config(w), parallelism=par),
+            "impl_config": {"precision": args.precision,
+                            "streams": "3 forward chains forked" if (args.fork and w["kind"] == "c3") else "single",
+                            "mask": "dense [B, A] tensor" if args.dense_mask else "structured: mask[:n,:,:,:n] from node counts",
+                            "cuda_graph": bool(graphed is not None or gpredict is not None),
+                            "l2": "flushed between timed steps (256 MiB write)"},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                     "ms_per_step": e2e_ms / args.steps,
                     "path": ("pinned host states -> H2D -> mask from n on device -> packer+embedder+actor -> D2H actions"
@@ -427,40 +437,89 @@ def run_ours(args):
                              "reference's host RNG, indices H2D, gather from device storage + DDPG update as one "
                              "CUDA-graph launch -> D2H losses")},
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "cpu_baseline": cpu,
-            "per_op_ms": {k: round(v, 4) for k, v in sorted(per_op.items(), key=lambda kv: -kv[1])[:12]},
+            "per_op_ms": {k: round(v, 4) for k, v in sorted(per_op.items(), key=lambda kv: -kv[1])[:14]},
             "wall_ms_per_step_incl_flush": t_wall / args.steps * 1e3,
         }
+        if parity is not None:
+            line["dp_parity"] = parity
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()
         torch.cuda.synchronize()
-        if graphed is not None:
-            # A captured graph keeps the communicator's resources alive and destroy_process_group() then
-            # waits forever (observed with torch 2.11 / NCCL 2.28): everything is printed and every
-            # rank has passed the barrier, so leave without the teardown.
-            sys.stdout.flush()
-            sys.stderr.flush()
-            os._exit(0)
+        for g in (graphed, g_e2e_ref[0] if g_e2e_ref else None):
+            if g is not None:
+                g.close()            # a captured graph keeps the communicator alive: destroy it first
         dist.destroy_process_group()
 
 
-def profiled_traffic(w, args, kernel: str):
-    """DRAM bytes (read + written) per launch of the dominant kernel, from the committed ncu --set full
-    capture of this workload (profiles/r1_traffic.json, written from the .ncu-rep by
-    tools/ncu_traffic.py); None when no capture of this workload/precision is committed."""
-    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r1_traffic.json")
+def dp_parity(upd, dev, rank, world, args, shard_opt):
+    """N > 1: (a) the replicas of the benchmarked networks are bit-identical after the run; (b) on a small
+    problem (N_max = 24, 8 states per rank) three data-parallel updates in the benchmarked mode equal three
+    single-GPU updates of the full minibatch (weights rel 2e-4, losses rel 1e-4: what
+    tests/test_gpu_dp.py checks on a 2-GPU box)."""
+    import torch.distributed as dist
+    from gsc_b200 import ddpg, dp, synth
+    from gsc_b200.graph import GraphBatch
+    from gsc_b200.models import Actor, AgentSpec, QNetwork
+    same = True
+    for net in (upd.actor, upd.qf1, upd.target_actor, upd.qf1_target):
+        other = net.flat.clone()
+        dist.broadcast(other, src=0)
+        same = same and bool(torch.equal(other, net.flat))
+    flag = torch.tensor([1 if same else 0], device=dev)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    n_max, Bg = 24, 8 * world
+    spec = AgentSpec(n_max)
+
+    def build():
+        torch.manual_seed(11)
+        nets = [cls(spec) for cls in (Actor, QNetwork, Actor, QNetwork)]
+        nets[2].load_state_dict(nets[0].state_dict())
+        nets[3].load_state_dict(nets[1].state_dict())
+        return [n.to(dev) for n in nets]
+    full = synth.make_transitions(Bg, n_max, 12, n_max, seed=3, num_topologies=5)
+    mine = dp.shard_transitions(*full, rank, world)
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+
+    def run(nets, data, **kw):
+        u = ddpg.DDPGUpdater(*nets, lr=1e-3, gamma=0.99, tau=1e-2, fork_streams=args.fork, **kw)
+        cur = GraphBatch.from_states(data[0], dense_mask=False).to(dev)
+        nxt = GraphBatch.from_states(data[1], dense_mask=False).to(dev)
+        for _ in range(3):
+            _, ql, al = u.update(cur.view(), nxt.view(), t(data[2]), t(data[3]), t(data[4]))
+        return torch.stack([ql.reshape(()), al.reshape(())])
+    nets_dp = build()
+    losses = run(nets_dp, mine, world_size=world, rank=rank, shard_optimizer=shard_opt, global_batch=Bg,
+                 bucket_allreduce=args.bucket_allreduce)
+    dist.all_reduce(losses)
+    out = {"replicas_bit_identical": bool(int(flag[0]))}
+    if rank == 0:
+        nets_1 = build()
+        ref = run(nets_1, full)
+        out["weights_rel_err_vs_single_gpu"] = max(float((a.flat - b.flat).abs().max() / b.flat.abs().max())
+                                                   for a, b in zip(nets_dp, nets_1))
+        out["losses_rel_err_vs_single_gpu"] = float((losses - ref).abs().max() / ref.abs().max())
+        out["ok"] = bool(out["replicas_bit_identical"] and out["weights_rel_err_vs_single_gpu"] < 2e-4
+                         and out["losses_rel_err_vs_single_gpu"] < 1e-4)
+        out["what"] = f"3 updates, N_max=24, {Bg} states sharded over {world} ranks vs 1 GPU on the full minibatch"
+    torch.cuda.synchronize()
+    dist.barrier()
+    return out
+
+
+def profiled_traffic(w, args, op_name: str):
+    """DRAM bytes (read + written) per launch of the dominant entry point's kernel, from the committed ncu
+    --set full capture of this workload (profiles/r2_traffic.json: {workload_bB_precision: {entry point:
+    {"dram_bytes_per_launch": ...}}}, written from the .ncu-rep by tools/ncu_traffic.py).  A pointer to the
+    capture, not a measurement of this run; None when no capture of this workload/precision is committed."""
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r2_traffic.json")
     try:
         with open(path) as f:
             table = json.load(f)
     except (OSError, ValueError):
         return None
-    key = f"{w['kind']}_b{w['B']}_{args.precision}"
-    name = kernel.split(" ")[0]
-    for cand in (name, name.replace("_kernel", "_tc_kernel"), name.replace("adam_soft_update", "adam_soft_dev")):
-        entry = table.get(key, {}).get(cand)
-        if entry is not None:
-            return entry.get("dram_bytes_per_launch")
-    return None
+    entry = table.get(f"{w['name']}_b{w['B']}_{args.precision}", {}).get(op_name)
+    return None if entry is None else entry.get("dram_bytes_per_launch")
 
 
 def op_bytes(name: str, w, Pa, Pc) -> float:
@@ -541,30 +600,39 @@ def cpu_baseline(args, w, sample_states: int, reps: int = 3):
 
 
 def run_reference(args):
+    """The reference's CPU path (the oracle port: PyG is not installable here) on the same workload, with
+    exactly --steps timed steps after --warmup untimed ones.  c2/c3 run the full batch of one GPU per step;
+    c4/c5 a bounded sample of it (stated in cpu_baseline.sample) so that the run ends within minutes."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    w = make_workload(args, 0)
-    S = min(w["B"], 256 if w["kind"] == "c3" else 4096)
+    cap = {"c2": 0, "c3": 0, "c4": 2, "c5": 1024}[args.workload]
+    w = make_workload(args, 0, max_states=cap)
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    fn, S = oracle_step_fn(w, S)
-    for _ in range(max(1, min(args.warmup, 2))):
+    fn, S = oracle_step_fn(w, cap or w["B"])
+    warm = max(0, args.warmup)
+    for _ in range(warm):
         fn()
-    steps = max(1, min(args.steps, 10))
+    steps = max(1, args.steps)
     t0 = time.perf_counter()
     for _ in range(steps):
         fn()
     dt = time.perf_counter() - t0
     value = S * steps / dt
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    par = f"dp{world}" if w["kind"] == "c3" else f"replicas{world}"
+    if w["name"] == "c4" and world > 1:
+        par += "+sharded-optimizer"
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT,
-            "n_gpus": int(os.environ.get("WORLD_SIZE", "1")), "steps": steps, "warmup": max(1, min(args.warmup, 2)),
+            "n_gpus": world, "steps": steps, "warmup": warm,
             "ms_per_step": dt / steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
-            "config": {"workload": workload_name(w), "states_per_step": S,
-                       "note": "reference CPU path = oracle port (PyG absent); bounded sample per step"},
+            "config": dict(make_config(w), parallelism=par),
+            "impl_config": {"note": "reference CPU path = oracle port (PyG 2.3.0 is not installable here); one process, "
+                                    "all host threads; no GPU"},
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
-                             "sample": f"{S} states per step x {steps} steps"},
+                             "sample": f"{S} of the {w['B']} states of one GPU's batch per step x {steps} steps"},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
 
@@ -575,9 +643,9 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default=os.environ.get("GSC_BENCH_WORKLOAD", "c3"), choices=["c2", "c3"],
+    ap.add_argument("--workload", default=os.environ.get("GSC_BENCH_WORKLOAD", "c3"), choices=sorted(WORKLOADS),
                     help="c3 (default): full DDPG update, the fwd+bwd+Adam step BASELINE.json's metric names; "
-                         "c2: embedder + actor inference")
+                         "c4: the same update on 1000-node topologies; c2 / c5: embedder + actor inference")
     ap.add_argument("--batch", type=int, default=0)
     ap.add_argument("--bucket-allreduce", action="store_true",
                     help="N > 1: all-reduce every dense layer's gradient block on the side stream behind the backward")
@@ -585,8 +653,9 @@ def main():
                     help="N > 1: SMs the embedder backward leaves free for the concurrent NCCL kernels")
     ap.add_argument("--no-fork", dest="fork", action="store_false",
                     help="run the three independent forward chains of the update on one stream")
-    ap.add_argument("--shard-optimizer", action="store_true",
-                    help="N > 1: reduce-scatter gradients, Adam + soft update on a 1/N parameter shard, all-gather")
+    ap.add_argument("--shard-optimizer", action=argparse.BooleanOptionalAction, default=None,
+                    help="N > 1: reduce-scatter gradients, Adam + soft update on a 1/N parameter shard, all-gather "
+                         "(default: on for c4, off otherwise)")
     ap.add_argument("--dense-mask", action="store_true",
                     help="carry the dense [B, A] mask tensor instead of the per-state node counts")
     ap.add_argument("--no-graph", dest="graph", action="store_false",

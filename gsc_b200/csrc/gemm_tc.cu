@@ -325,14 +325,19 @@ gemm_tc_kernel(const __grid_constant__ TcParams p, const __grid_constant__ CUten
     }
   } else if (X3 && warp >= kTcEpiWarps) {
     // ===================== converter warps, 3xTF32 only =====================
-    // Every staged operand element x becomes hi = tf32(x) (round to nearest, ties away: add half an ulp
-    // of the 10-bit mantissa to the magnitude bits and clear the 13 low bits), rewritten in place, and
-    // lo = tf32(x - hi) at the same offset of the lo ring; x - hi is exact in fp32.  The split is
-    // elementwise, hence layout-agnostic: K-major and MN-major swizzled tiles alike.
+    // The tensor core reads only the 19 high bits of an fp32 operand (sign, exponent, 10 mantissa bits;
+    // checked on the device by tools/tf32_trunc_check.py), so the staged tile itself already is the hi
+    // image, hi = trunc(x).  The converters write lo = x - trunc(x) (exact in fp32, at most 13
+    // significant bits, of which the tensor core again keeps the top 11) at the same offset of the lo
+    // ring.  Dropped: lo*lo and the 2 low bits of lo, together ~2^-21 relative per product.  The split
+    // is elementwise, hence layout-agnostic: K-major and MN-major swizzled tiles alike.
+    // (GSC_TC_DBG bit 16, experiments only: round-to-nearest split, hi rewritten in place.)
     const int ct = (warp - kTcEpiWarps) * 32 + lane;            // 0..127
     int stage = 0, lstage = 0;
     uint32_t phase = 0, lphase = 0;
     constexpr int kIters = kTcStageBytes / (16 * 32 * kTcConvWarps);   // 16 float4 per thread and stage
+    const bool inplace = (p.dbg & 16) != 0;
+    const uint32_t rnd = inplace ? 0x1000u : 0u;
     for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
       const WorkItem it = decode_work(p, w);
 #pragma unroll 1
@@ -343,22 +348,23 @@ gemm_tc_kernel(const __grid_constant__ TcParams p, const __grid_constant__ CUten
         const uint32_t dst = lo_base + lstage * kTcStageBytes + ct * 16;
         if (!(p.dbg & 8)) {
 #pragma unroll
-          for (int i0 = 0; i0 < kIters; i0 += 4) {
-            uint32_t v[4][4];
+          for (int i0 = 0; i0 < kIters; i0 += 8) {               // eight 128-bit loads in flight per thread
+            uint32_t v[8][4];
 #pragma unroll
-            for (int u = 0; u < 4; ++u)
+            for (int u = 0; u < 8; ++u)
               asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
                            : "=r"(v[u][0]), "=r"(v[u][1]), "=r"(v[u][2]), "=r"(v[u][3]) : "r"(src + (i0 + u) * 2048));
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
+            for (int u = 0; u < 8; ++u) {
               uint32_t hi[4], lo[4];
 #pragma unroll
               for (int e = 0; e < 4; ++e) {
-                hi[e] = (v[u][e] + 0x1000u) & 0xffffe000u;
+                hi[e] = ((v[u][e] + rnd) & 0xffffe000u);
                 const float l = __uint_as_float(v[u][e]) - __uint_as_float(hi[e]);
-                lo[e] = (__float_as_uint(l) + 0x1000u) & 0xffffe000u;
+                lo[e] = inplace ? ((__float_as_uint(l) + 0x1000u) & 0xffffe000u) : __float_as_uint(l);
               }
-              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(src + (i0 + u) * 2048), "r"(hi[0]), "r"(hi[1]), "r"(hi[2]), "r"(hi[3]) : "memory");
+              if (inplace)
+                asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(src + (i0 + u) * 2048), "r"(hi[0]), "r"(hi[1]), "r"(hi[2]), "r"(hi[3]) : "memory");
               asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst + (i0 + u) * 2048), "r"(lo[0]), "r"(lo[1]), "r"(lo[2]), "r"(lo[3]) : "memory");
             }
           }
@@ -433,6 +439,11 @@ gemm_tc_kernel(const __grid_constant__ TcParams p, const __grid_constant__ CUten
           const uint32_t keep = f_smask ? smask_bits(p, nb, col0) : 0xffffffffu;
           float v[32];
           tc_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(as * kTcBN + c * 32), v);
+          if (c == c_end - 1) {                                       // last TMEM read of this tile:
+            tc_fence_before();                                        // the accumulator buffer is free again
+            __syncwarp();
+            if (lane == 0) mbar_arrive(tempty_bar(as));
+          }
           const uint32_t rbase = ebuf + c * 16384 + lrow * 128;
 #pragma unroll
           for (int q = 0; q < 8; ++q) {
@@ -457,10 +468,23 @@ gemm_tc_kernel(const __grid_constant__ TcParams p, const __grid_constant__ CUten
             }
             asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(o[0]), "f"(o[1]), "f"(o[2]), "f"(o[3]) : "memory");
           }
+          if (p.epi_kind == 0) {
+            // No prefetched operand tile: every 32-column chunk has its own 16 KB buffer and leaves with
+            // its own TMA store, which drains while the next chunk is computed.  One named barrier per
+            // chunk: before it the issuing thread makes sure the previous store of this column half has
+            // been read out of shared memory (its buffer is the next one to be overwritten).
+            fence_proxy_async_smem();                                  // st.shared -> visible to the TMA store
+            const bool issuer = (warp & 3) == 0 && lane == 0;
+            if (issuer) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+            asm volatile("bar.sync %0, 128;" ::"r"(1 + (warp >> 2)) : "memory");
+            if (issuer && col0 < ncols) {
+              asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(
+                               reinterpret_cast<uint64_t>(&mapC)), "r"(ebuf + c * 16384), "r"(col0), "r"(it.m0) : "memory");
+              asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+            }
+          }
         }
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(tempty_bar(as));                 // accumulator buffer is free again
+        if (p.epi_kind == 0) continue;
         fence_proxy_async_smem();                                    // st.shared -> visible to the TMA store
         // the two column halves (warps 0..3 / 4..7) own their half of the tile buffer, their own named
         // barrier and their own TMA store: one half computes while the other drains

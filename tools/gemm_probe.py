@@ -57,4 +57,12 @@ for prec in ("tf32", "tf32x3"):
             continue
         os.environ["GSC_TC_DBG"] = str(dbg)
         print(f"ablate {prec:7s} actor_l2 fwd  dbg={dbg:2d} ({label:28s}) {timeit(cases['actor_l2 fwd [1024x30000x256] smask']):8.1f} us", flush=True)
+ops.precision = "tf32"
+for dbg, label in ((6, "MMAs only"), (6 + 32, "MMAs only, no wait, no commit"), (6 + 64, "MMAs only, no wait")):
+    os.environ["GSC_TC_DBG"] = str(dbg)
+    print(f"handshake tf32 actor_l2 fwd dbg={dbg:3d} ({label:30s}) {timeit(cases['actor_l2 fwd [1024x30000x256] smask']):8.1f} us", flush=True)
+os.environ["GSC_TC_DBG"] = "16"
+ops.precision = "tf32x3"
+for name, fn in cases.items():
+    print(f"x3 in-place rounded split  {name:45s} {timeit(fn):8.1f} us", flush=True)
 os.environ["GSC_TC_DBG"] = "0"
