@@ -51,7 +51,7 @@ _PROTOS = {
     "gsc_gnn_embed_fwd": (c_int, [c_void_p, c_int64, c_int, c_void_p, c_void_p, c_void_p, c_int64,
                                   c_int, c_void_p, c_int, c_int, c_int, c_void_p, c_int64, c_void_p, c_void_p]),
     "gsc_node_features": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_void_p]),
-    "gsc_gnn_bwd_workspace_bytes": (c_size_t, [c_int64, c_int, c_int, c_int, c_int]),
+    "gsc_gnn_bwd_workspace_bytes": (c_size_t, [c_int64, c_int64, c_int, c_int, c_int, c_int, c_int]),
     "gsc_gnn_embed_bwd": (c_int, [c_void_p, c_int64, c_int, c_void_p, c_void_p, c_void_p, c_int64,
                                   c_int, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_int64, c_void_p,
                                   c_void_p, c_void_p, c_size_t, c_void_p]),

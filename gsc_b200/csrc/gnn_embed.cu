@@ -34,6 +34,7 @@ struct GnnArgs {
   const float* d_emb;     // bwd only
   float* partials;        // bwd only: [gridDim.x][param_floats]
   float* rows_ws;         // bwd, large graphs only: [gridDim.x][5][cap][HP] node-row scratch in global memory
+  float* dx;              // bwd, tcgen05 kernel: [num_apps][Nt][2*HP] = d_xl | d_xr of every node, read by gnn_wgrad_kernel
   float* dbg;             // optional phase timers (debug hook), nullptr in production
   const int32_t* stats;   // bwd: packer stats (stats[3] == 0 <=> symmetric graph), nullable
   const int32_t* flags;   // bwd: flags[0] != 0 <=> some chunk's edges exceed the gather kernel's shared memory
@@ -782,19 +783,16 @@ __global__ void __launch_bounds__(kGnnThreads, 1) gnn_bwd_kernel(const GnnArgs p
 //   (W) [dWl|dbl ; dWr|dbr] += [dxl|dxr]^T x [h_in|1]       (reduction over nodes)
 // contracts over the node index, i.e. both operands would be MN-major; for 32-bit operands the
 // tensor core only takes that through the 32-byte-atom swizzled image, a second copy of both
-// operands that does not fit next to the K-major ones.  It therefore runs on the FMA pipe with an
-// 8 x 5 register tile per lane (two 128-bit and ten 32-bit LDS per 40 FMAs), accumulated per CTA in
-// shared memory over all its chunks and applications and written out once per launch.
+// operands that does not fit next to the K-major ones.  It is not part of this kernel: the
+// [dxl|dxr] rows of every application are written to the workspace (they are in registers anyway
+// when the (H) operand is built) and gnn_wgrad_kernel reduces them over the nodes afterwards --
+// a streaming pass with a 4 x 8 register tile per thread instead of accumulators that this
+// kernel would have to carry (and spill) across all of its phases.
 template <int HP>
 struct TcB {
   static constexpr int kN1 = 2 * HP;                               // (R) columns: xl | xr
   static constexpr int kNH = (HP + 15) / 16 * 16;                  // (H) columns (N % 16 == 0 for M = 128)
-  static constexpr int kWCols = HP + 1;                            // (W) row: HP weight columns + bias column
-  static constexpr int kWFloats = 2 * HP * kWCols;                 // [2HP channels][HP+1]
-  static constexpr int kCG = HP / 4;                               // (W) lane tiling: channel groups of 8 ...
-  static constexpr int kKG = 32 / kCG;                             // ... times column groups
-  static constexpr int kKPer = (kWCols + kKG - 1) / kKG;
-  static constexpr int kHChunks = HP / 4 + 1;                      // h row: HP floats + [1,0,0,0]
+  static constexpr int kHChunks = HP / 4;                          // h row: HP floats
   static constexpr int kHGroup = kHChunks * 128;
   static constexpr int kHTile = 16 * kHGroup;
   static constexpr int kDChunks = 2 * HP / 4;                      // dx row: dxl | dxr
@@ -807,7 +805,7 @@ struct TcB {
   static constexpr int kVecFloats = 4 * HP;                        // bl, br, att, pad
   static constexpr int kSlotFloats = (kGnnThreads / 32) * 2 * HP;  // per-warp private d_att | d_bias sums
   static constexpr int kConvBytes = 2 * kB1 + 2 * kB2 + (kVecFloats + kSlotFloats) * 4;
-  static constexpr int kMaxConvs = 4;                              // (W) accumulators are per lane, per conv
+  static constexpr int kMaxConvs = 4;
   __device__ __forceinline__ static int hoff(int r, int c) { return (r >> 3) * kHGroup + c * 128 + (r & 7) * 16; }
   __device__ __forceinline__ static int doff(int r, int c) { return (r >> 3) * kDGroup + c * 128 + (r & 7) * 16; }
 };
@@ -901,13 +899,6 @@ __global__ void __launch_bounds__(kGnnThreads, 1) gnn_bwd_tc_kernel(const GnnArg
     }
     for (int t = tid; t < T::kSlotFloats; t += kGnnThreads) vec[4 * HP + t] = 0.f;   // d_att | d_bias slots
   }
-  // (W) accumulators: an 8 x kKPer register tile per lane and conv, kept across every chunk and
-  // application of this CTA (local memory between uses) and reduced over the warps once, at the end.
-  float wacc[T::kMaxConvs][8 * T::kKPer];
-#pragma unroll
-  for (int cvv = 0; cvv < T::kMaxConvs; ++cvv)
-#pragma unroll
-    for (int u = 0; u < 8 * T::kKPer; ++u) wacc[cvv][u] = 0.f;
   if (tid == 0) {
     mbar_init(bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -995,7 +986,7 @@ __global__ void __launch_bounds__(kGnnThreads, 1) gnn_bwd_tc_kernel(const GnnArg
       float* vec = reinterpret_cast<float*>(b2_hi + 2 * T::kB2);
       const bool last_app = a == p.num_apps - 1;
 
-      // ---- 1. layer input rows -> split h operand (with the constant-1 chunk) ----
+      // ---- 1. layer input rows -> split h operand ----
       for (int i = tid; i < nc; i += kGnnThreads) {
         const int64_t node = (int64_t)nbase + i;
         uint8_t* hh = h_hi + (i >> 7) * T::kHTile;
@@ -1017,8 +1008,6 @@ __global__ void __launch_bounds__(kGnnThreads, 1) gnn_bwd_tc_kernel(const GnnArg
           *reinterpret_cast<float4*>(hh + T::hoff(r, c4)) = hi;
           *reinterpret_cast<float4*>(hl + T::hoff(r, c4)) = lo;
         }
-        *reinterpret_cast<float4*>(hh + T::hoff(r, HP / 4)) = make_float4(1.f, 0.f, 0.f, 0.f);
-        *reinterpret_cast<float4*>(hl + T::hoff(r, HP / 4)) = make_float4(0.f, 0.f, 0.f, 0.f);
       }
       GSC_TICK(1);
       // ---- 2. (R) on the tensor cores ----
@@ -1201,54 +1190,20 @@ __global__ void __launch_bounds__(kGnnThreads, 1) gnn_bwd_tc_kernel(const GnnArg
       }
       __syncthreads();
       GSC_TICK(4);
-      // ---- 5a. (W): weight / bias gradients of lin_l, lin_r (FMA pipe, register-tiled) ----
-      {
-        const int cg = lane % T::kCG, kg = lane / T::kCG;
-        const int c0 = 8 * cg, k0 = T::kKPer * kg;
-        const bool active = kg < T::kKG && k0 < T::kWCols;
-        float acc[8][T::kKPer];
-#pragma unroll
-        for (int u = 0; u < 8; ++u)
-#pragma unroll
-          for (int q = 0; q < T::kKPer; ++q) acc[u][q] = wacc[cv][u * T::kKPer + q];
-        if (active) {
-          int koff[T::kKPer];                       // byte offset of column k inside an operand row group
-#pragma unroll
-          for (int q = 0; q < T::kKPer; ++q) koff[q] = ((k0 + q) >> 2) * 128 + ((k0 + q) & 3) * 4;
-          const float* dbase = (c0 < HP) ? xl_s + c0 : dxr_raw + (c0 - HP);
-#pragma unroll 2
-          for (int i = warp; i < nc; i += kGnnThreads / 32) {
-            const float4 d0 = reinterpret_cast<const float4*>(dbase + (size_t)i * HP)[0];
-            const float4 d1 = reinterpret_cast<const float4*>(dbase + (size_t)i * HP)[1];
-            const float dv[8] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w};
-            const int rbase = (i >> 7) * T::kHTile + ((i & 127) >> 3) * T::kHGroup + (i & 7) * 16;
-            float hv[T::kKPer];
-#pragma unroll
-            for (int q = 0; q < T::kKPer; ++q) {
-              const int k = k0 + q;
-              float h = (k == HP) ? 1.f : 0.f;
-              if (k < HP) h = *reinterpret_cast<const float*>(h_hi + rbase + koff[q]) +
-                              *reinterpret_cast<const float*>(h_lo + rbase + koff[q]);
-              hv[q] = h;
-            }
-#pragma unroll
-            for (int u = 0; u < 8; ++u)
-#pragma unroll
-              for (int q = 0; q < T::kKPer; ++q) acc[u][q] = fmaf(dv[u], hv[q], acc[u][q]);
-          }
-        }
-#pragma unroll
-        for (int u = 0; u < 8; ++u)
-#pragma unroll
-          for (int q = 0; q < T::kKPer; ++q) wacc[cv][u * T::kKPer + q] = acc[u][q];
-      }
-      GSC_TICK(5);
-      // ---- 5b. [dxl | dxr] rows -> split dx operand (buffers overlap the scratch: read, sync, write) ----
+      // ---- 5. [dxl | dxr] rows -> workspace (for gnn_wgrad_kernel) and -> split dx operand of (H)
+      //      (the operand buffers overlap the scratch rows: read, sync, write) ----
       {
         float dl0[HP], dr0[HP], dl1[HP], dr1[HP];      // up to 2 node slots per thread (cap <= 512)
         const int i_a = tid, i_b = tid + kGnnThreads;
-        if (i_a < nc) { load_row<HP>(xl_s + (size_t)i_a * HP, dl0); load_row<HP>(dxr_raw + (size_t)i_a * HP, dr0); }
-        if (i_b < nc) { load_row<HP>(xl_s + (size_t)i_b * HP, dl1); load_row<HP>(dxr_raw + (size_t)i_b * HP, dr1); }
+        float* dxa = p.dx + ((size_t)a * p.Nt + nbase) * (2 * HP);
+        if (i_a < nc) {
+          load_row<HP>(xl_s + (size_t)i_a * HP, dl0); load_row<HP>(dxr_raw + (size_t)i_a * HP, dr0);
+          store_row<HP>(dxa + (size_t)i_a * 2 * HP, dl0); store_row<HP>(dxa + (size_t)i_a * 2 * HP + HP, dr0);
+        }
+        if (i_b < nc) {
+          load_row<HP>(xl_s + (size_t)i_b * HP, dl1); load_row<HP>(dxr_raw + (size_t)i_b * HP, dr1);
+          store_row<HP>(dxa + (size_t)i_b * 2 * HP, dl1); store_row<HP>(dxa + (size_t)i_b * 2 * HP + HP, dr1);
+        }
         __syncthreads();
         auto put = [&](int i, const float (&dl)[HP], const float (&dr)[HP]) {
           uint8_t* dh = d_hi + (i >> 7) * T::kDTile;
@@ -1308,24 +1263,10 @@ __global__ void __launch_bounds__(kGnnThreads, 1) gnn_bwd_tc_kernel(const GnnArg
   tc_fence_after();
   const int64_t P = conv_param_offset(p.num_convs, p.in_dim, p.H);
   float* out = p.partials + (size_t)blockIdx.x * P;
-  float* slab = reinterpret_cast<float*>(h_hi);       // [warps][2HP][kWCols]: operand buffers are idle now
-  for (int cv = 0; cv < p.num_convs; ++cv) {
-    const int in = (cv == 0) ? p.in_dim : p.H, H = p.H;
+  for (int cv = 0; cv < p.num_convs; ++cv) {          // att and conv-bias entries; the rest is gnn_wgrad_kernel's
+    const int H = p.H;
     float* o = out + conv_param_offset(cv, p.in_dim, p.H);
     const float* vec = reinterpret_cast<const float*>(convs + cv * T::kConvBytes + 2 * T::kB1 + 2 * T::kB2);
-    __syncthreads();
-    {
-      const int cg = lane % T::kCG, kg = lane / T::kCG;
-      const int c0 = 8 * cg, k0 = T::kKPer * kg;
-      if (kg < T::kKG && k0 < T::kWCols) {
-#pragma unroll
-        for (int u = 0; u < 8; ++u)
-#pragma unroll
-          for (int q = 0; q < T::kKPer; ++q)
-            if (k0 + q < T::kWCols) slab[(size_t)warp * T::kWFloats + (c0 + u) * T::kWCols + k0 + q] = wacc[cv][u * T::kKPer + q];
-      }
-    }
-    __syncthreads();
     for (int t = tid; t < H; t += kGnnThreads) {
       float sa = 0.f, sb = 0.f;
       for (int w = 0; w < kGnnThreads / 32; ++w) {
@@ -1335,26 +1276,151 @@ __global__ void __launch_bounds__(kGnnThreads, 1) gnn_bwd_tc_kernel(const GnnArg
       o[t] = sa;
       o[H + t] = sb;
     }
-    auto gsum = [&](int idx) {
-      float sum = 0.f;
-      for (int w = 0; w < kGnnThreads / 32; ++w) sum += slab[(size_t)w * T::kWFloats + idx];
-      return sum;
-    };
-    for (int t = tid; t < 2 * H * in; t += kGnnThreads) {       // lin_l.weight then lin_r.weight
-      const int is_r = t >= H * in, tt = t - is_r * H * in;
-      const int c = tt / in, k = tt - c * in;
-      o[2 * H + (is_r ? (int64_t)H * in + H : 0) + tt] = gsum((is_r * HP + c) * T::kWCols + k);
-    }
-    for (int t = tid; t < 2 * H; t += kGnnThreads) {            // lin_l.bias then lin_r.bias
-      const int is_r = t >= H, c = t - is_r * H;
-      o[2 * H + (int64_t)H * in + (is_r ? (int64_t)H * in + H : 0) + c] = gsum((is_r * HP + c) * T::kWCols + HP);
-    }
   }
   tc_fence_before();
   __syncthreads();
   if (warp == 0) {
     tc_fence_after();
     tmem_dealloc(tmem_base, (uint32_t)tmem_cols);
+  }
+}
+
+// (W) of the tcgen05 backward: for every conv, [dWl|dbl ; dWr|dbr] = sum over its applications and over
+// all nodes of [dxl|dxr]_i (x) [h_in_i | 1].  Streaming reduction: CTA b owns the node slice
+// [b*Nt/grid, (b+1)*Nt/grid) and walks it in tiles of kWgTile nodes staged in shared memory (next tile
+// prefetched into registers); thread = (node lane, 4 channels x 8 input columns), i.e. per node three
+// 128-bit shared-memory loads feed 32 FMAs.  The node lanes are added in a fixed order and the CTA's
+// sums go to the W / bl / br entries of partial row b (gnn_bwd_reduce_kernel adds the rows).
+// Algorithmic bytes: 4 * (2HP + d_in) per node and application, read once.
+template <int HP>
+struct WgL {
+  static constexpr int kCh = 2 * HP;                           // channels: dxl | dxr
+  static constexpr int kCols = HP + 8;                         // h row in smem: HP inputs, 1.0, zero padding
+  static constexpr int kTiles = (kCh / 4) * (kCols / 8);       // thread tiles (4 channels x 8 columns) per node lane
+  static constexpr int kLanes = kGnnThreads / kTiles;          // node lanes (5 for HP = 24)
+  static constexpr int kTile = 8 * kLanes;                     // nodes per staged tile
+  static constexpr int kTileF4 = kTile * (kCh + HP) / 4;       // float4 per staged tile
+  static constexpr int kPre = (kTileF4 + kGnnThreads - 1) / kGnnThreads;
+  static constexpr int kSmemFloats = 2 * kTile * (kCh + kCols) + kLanes * kCh * (kCols + 1);
+  static_assert(kLanes >= 1, "more thread tiles than threads");
+};
+
+template <int HP>
+__global__ void __launch_bounds__(kGnnThreads) gnn_wgrad_kernel(const GnnArgs p) {
+  using L = WgL<HP>;
+  constexpr int kCh = L::kCh, kCols = L::kCols, kLanes = L::kLanes, kTile = L::kTile;
+  extern __shared__ float4 smem4[];
+  float* dx_s = reinterpret_cast<float*>(smem4);               // [2][kTile][kCh]
+  float* h_s = dx_s + 2 * kTile * kCh;                         // [2][kTile][kCols]
+  float* red_s = h_s + 2 * kTile * kCols;                      // [kLanes][kCh][kCols + 1]
+  if (p.stats == nullptr || p.stats[3] != 0 || p.flags[0] != 0) return;     // the scatter kernel ran instead
+  const int tid = threadIdx.x;
+  const int tile_t = tid % L::kTiles, nl = tid / L::kTiles;
+  const int c0 = 4 * (tile_t % (kCh / 4)), k0 = 8 * (tile_t / (kCh / 4));
+  const bool worker = nl < kLanes;
+  const int64_t lo = p.Nt * blockIdx.x / gridDim.x, hi = p.Nt * (blockIdx.x + 1) / gridDim.x;
+  const int64_t P = conv_param_offset(p.num_convs, p.in_dim, p.H);
+  float* out = p.partials + (size_t)blockIdx.x * P;
+  for (int t = tid; t < 2 * kTile * 8; t += kGnnThreads)      // constant columns of the h tiles: 1, 0, ..., 0
+    h_s[(t / 8) * kCols + HP + (t & 7)] = (t & 7) == 0 ? 1.f : 0.f;
+
+  for (int cv = 0; cv < p.num_convs; ++cv) {
+    const int d_in = cv == 0 ? p.in_dim : p.H;
+    float acc[4][8];
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+#pragma unroll
+      for (int q = 0; q < 8; ++q) acc[u][q] = 0.f;
+    for (int a = 0; a < p.num_apps; ++a) {
+      if (p.app_conv[a] != cv) continue;
+      const float* dxa = p.dx + (size_t)a * p.Nt * kCh;
+      const float* ha = a == 0 ? nullptr : p.saved + (size_t)(a - 1) * p.Nt * HP;
+      // staged tile, float4 index e: e < kTile*kCh/4 -> dx rows, else h rows
+      float4 pre[L::kPre];
+      auto fetch = [&](int64_t n0) {
+#pragma unroll
+        for (int r = 0; r < L::kPre; ++r) {
+          const int e = tid + r * kGnnThreads;
+          float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (e < kTile * kCh / 4) {
+            if (n0 + e / (kCh / 4) < hi) v = reinterpret_cast<const float4*>(dxa + (size_t)n0 * kCh)[e];
+          } else if (e < L::kTileF4) {
+            const int eh = e - kTile * kCh / 4, i = eh / (HP / 4), q = eh % (HP / 4);
+            if (n0 + i < hi) {
+              if (ha != nullptr) {
+                v = reinterpret_cast<const float4*>(ha + (size_t)(n0 + i) * HP)[q];
+              } else {
+                const float* xr = p.x + (size_t)(n0 + i) * p.in_dim;
+                v.x = 4 * q + 0 < p.in_dim ? xr[4 * q + 0] : 0.f;
+                v.y = 4 * q + 1 < p.in_dim ? xr[4 * q + 1] : 0.f;
+                v.z = 4 * q + 2 < p.in_dim ? xr[4 * q + 2] : 0.f;
+                v.w = 4 * q + 3 < p.in_dim ? xr[4 * q + 3] : 0.f;
+              }
+            }
+          }
+          pre[r] = v;
+        }
+      };
+      auto stash = [&](int buf) {
+#pragma unroll
+        for (int r = 0; r < L::kPre; ++r) {
+          const int e = tid + r * kGnnThreads;
+          if (e < kTile * kCh / 4) {
+            reinterpret_cast<float4*>(dx_s + buf * kTile * kCh)[e] = pre[r];
+          } else if (e < L::kTileF4) {
+            const int eh = e - kTile * kCh / 4, i = eh / (HP / 4), q = eh % (HP / 4);
+            *reinterpret_cast<float4*>(h_s + (buf * kTile + i) * kCols + 4 * q) = pre[r];
+          }
+        }
+      };
+      int buf = 0;
+      fetch(lo);
+      __syncthreads();                                         // previous readers of buffer 0 are done
+      stash(0);
+      __syncthreads();
+      for (int64_t n0 = lo; n0 < hi; n0 += kTile, buf ^= 1) {
+        const bool more = n0 + kTile < hi;
+        if (more) fetch(n0 + kTile);
+        if (worker) {
+#pragma unroll 2
+          for (int i = nl; i < kTile; i += kLanes) {           // rows past the slice are zero
+            const float4 d = *reinterpret_cast<const float4*>(dx_s + (buf * kTile + i) * kCh + c0);
+            const float4 h0 = *reinterpret_cast<const float4*>(h_s + (buf * kTile + i) * kCols + k0);
+            const float4 h1 = *reinterpret_cast<const float4*>(h_s + (buf * kTile + i) * kCols + k0 + 4);
+            const float dv[4] = {d.x, d.y, d.z, d.w};
+            const float hv[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+#pragma unroll
+              for (int q = 0; q < 8; ++q) acc[u][q] = fmaf(dv[u], hv[q], acc[u][q]);
+          }
+        }
+        if (more) stash(buf ^ 1);                              // nobody reads that buffer in this iteration
+        __syncthreads();
+      }
+    }
+    // node lanes -> CTA sums (fixed order) -> partial row
+    if (worker)
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+#pragma unroll
+        for (int q = 0; q < 8; ++q) red_s[(nl * kCh + c0 + u) * (kCols + 1) + k0 + q] = acc[u][q];
+    __syncthreads();
+    const int H = p.H;
+    float* o = out + conv_param_offset(cv, p.in_dim, p.H);
+    for (int t = tid; t < kCh * (d_in + 1); t += kGnnThreads) {
+      const int ch = t / (d_in + 1), kk = t % (d_in + 1);
+      const int is_r = ch >= HP, c = ch - is_r * HP;
+      if (c >= H) continue;
+      const int k = kk == d_in ? HP : kk;                      // last entry: the bias column
+      float sum = 0.f;
+#pragma unroll
+      for (int l = 0; l < kLanes; ++l) sum += red_s[(l * kCh + ch) * (kCols + 1) + k];
+      const int64_t base = 2 * H + (is_r ? (int64_t)H * d_in + H : 0);
+      if (kk == d_in) o[base + (int64_t)H * d_in + c] = sum;   // lin_{l,r}.bias
+      else o[base + (int64_t)c * d_in + kk] = sum;             // lin_{l,r}.weight[c][k]
+    }
+    __syncthreads();
   }
 }
 
@@ -1533,6 +1599,10 @@ static int launch_bwd_both(GnnArgs a, int max_nodes, float* d_params, cudaStream
     GSC_CUDA_TRY(cudaFuncSetAttribute(gnn_bwd_tc_kernel<HP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_t));
     gnn_bwd_tc_kernel<HP><<<grid, kGnnThreads, smem_t, st>>>(t, cols);   // returns at once unless symmetric
     GSC_LAUNCH_CHECK("gnn_bwd_tc_kernel");
+    const int smem_w = WgL<HP>::kSmemFloats * 4;
+    GSC_CUDA_TRY(cudaFuncSetAttribute(gnn_wgrad_kernel<HP>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_w));
+    gnn_wgrad_kernel<HP><<<grid, kGnnThreads, smem_w, st>>>(t);           // its weight gradients (same condition)
+    GSC_LAUNCH_CHECK("gnn_wgrad_kernel");
     a.gather_kernel_launched = 1;
   }
   if (global_rows) {
@@ -1609,10 +1679,17 @@ static bool bwd_rows_in_global(int max_nodes, int H, int num_layers) {
   return (2 * (size_t)num_layers * conv_floats + 5 * cap * hp) * 4 > 227 * 1024;
 }
 
-extern "C" size_t gsc_gnn_bwd_workspace_bytes(int64_t B, int max_nodes, int in_dim, int H, int num_layers) {
+static int num_apps_of(int num_layers, int num_iter) { return 1 + (num_layers > 1 ? num_iter * (num_layers - 1) : 0); }
+// [d_xl | d_xr] rows of every application (tcgen05 backward -> gnn_wgrad_kernel)
+static size_t bwd_dx_bytes(int64_t Nt, int H, int num_layers, int num_iter) {
+  return ((size_t)num_apps_of(num_layers, num_iter) * (size_t)Nt * 2 * pick_hp(H) * 4 + 255) / 256 * 256;
+}
+
+extern "C" size_t gsc_gnn_bwd_workspace_bytes(int64_t Nt, int64_t B, int max_nodes, int in_dim, int H, int num_layers,
+                                              int num_iter) {
   (void)B;
-  if (max_nodes < 1 || H < 1 || H > GSC_MAX_HIDDEN || num_layers < 1) return 0;
-  size_t bytes = bwd_partials_bytes(in_dim, H, num_layers) + kBwdFlagBytes;
+  if (Nt < 0 || max_nodes < 1 || H < 1 || H > GSC_MAX_HIDDEN || num_layers < 1 || num_iter < 0) return 0;
+  size_t bytes = bwd_partials_bytes(in_dim, H, num_layers) + kBwdFlagBytes + bwd_dx_bytes(Nt, H, num_layers, num_iter);
   if (bwd_rows_in_global(max_nodes, H, num_layers)) {
     const size_t cap = ((size_t)max_nodes + 31) / 32 * 32;
     bytes += (size_t)kNumSMs * 5 * cap * pick_hp(H) * 4;
@@ -1631,12 +1708,13 @@ extern "C" int gsc_gnn_embed_bwd(const float* x, int64_t Nt, int in_dim, const i
   if (rc) return rc;
   GSC_REQUIRE(saved && d_emb && d_params && workspace && d_emb_ld >= H, "gnn bwd: null pointer or d_emb_ld < hidden");
   a.emb_ld = d_emb_ld;
-  if (workspace_bytes < gsc_gnn_bwd_workspace_bytes(B, max_nodes, in_dim, H, num_layers))
+  if (workspace_bytes < gsc_gnn_bwd_workspace_bytes(Nt, B, max_nodes, in_dim, H, num_layers, num_iter))
     return fail(GSC_EWORKSPACE, "gnn bwd: workspace %zu < %zu", workspace_bytes,
-                gsc_gnn_bwd_workspace_bytes(B, max_nodes, in_dim, H, num_layers));
+                gsc_gnn_bwd_workspace_bytes(Nt, B, max_nodes, in_dim, H, num_layers, num_iter));
   a.saved = const_cast<float*>(saved); a.d_emb = d_emb; a.partials = (float*)workspace;
   a.flags = reinterpret_cast<const int32_t*>(static_cast<uint8_t*>(workspace) + bwd_partials_bytes(in_dim, H, num_layers));
-  a.rows_ws = reinterpret_cast<float*>(static_cast<uint8_t*>(workspace) + bwd_partials_bytes(in_dim, H, num_layers) + kBwdFlagBytes);
+  a.dx = reinterpret_cast<float*>(static_cast<uint8_t*>(workspace) + bwd_partials_bytes(in_dim, H, num_layers) + kBwdFlagBytes);
+  a.rows_ws = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(a.dx) + bwd_dx_bytes(Nt, H, num_layers, num_iter));
   a.dbg = g_gnn_debug;
   a.stats = pack_stats;
   cudaStream_t st = (cudaStream_t)stream;

@@ -281,15 +281,15 @@ def gnn_embed_bwd(x, rowptr, col, graph_ptr, num_graphs: int, max_nodes: int, pa
     Nt, in_dim = int(x.shape[0]), int(x.shape[1])
     if d_params is None:
         d_params = torch.empty_like(params)
-    ws, wsn = workspace(lib.gsc_gnn_bwd_workspace_bytes(num_graphs, max_nodes, in_dim, hidden, num_layers),
-                        x.device, "gnn_bwd")
+    ws, wsn = workspace(lib.gsc_gnn_bwd_workspace_bytes(Nt, num_graphs, max_nodes, in_dim, hidden, num_layers,
+                                                        num_iter), x.device, "gnn_bwd")
     with _Timed("gnn_bwd"):
         check(lib.gsc_gnn_embed_bwd(_ptr(x), Nt, in_dim, _ptr(rowptr), _ptr(col), _ptr(graph_ptr),
                                     num_graphs, max_nodes, _ptr(params), hidden, num_layers, num_iter,
                                     _ptr(saved), _ptr(d_emb), _ld(d_emb), _ptr(d_params), _ptr(pack_stats),
                                     _ptr(ws), wsn, _stream()),
               "gsc_gnn_embed_bwd")
-    _count(2)
+    _count(5)
     return d_params
 
 

@@ -143,8 +143,12 @@ int gsc_gnn_embed_fwd(const float* x, int64_t num_nodes, int in_dim, const int32
  * scatters with shared-memory atomics.
  * Graphs whose node rows do not fit in shared memory (about > 450 nodes at hidden = 22, e.g. the
  * 1000-node topologies of the data-parallel configuration) keep them in the workspace, which is why
- * its size depends on max_nodes. */
-size_t gsc_gnn_bwd_workspace_bytes(int64_t num_graphs, int max_nodes, int in_dim, int hidden, int num_layers);
+ * its size depends on max_nodes.
+ * The workspace also holds the [d_xl | d_xr] rows of every node and GATv2 application
+ * (num_nodes * (1 + num_iter*(num_layers-1)) * 2*hidden_padded floats): the gather kernel writes
+ * them and a streaming reduction turns them into the lin_l / lin_r weight and bias gradients. */
+size_t gsc_gnn_bwd_workspace_bytes(int64_t num_nodes, int64_t num_graphs, int max_nodes, int in_dim, int hidden,
+                                   int num_layers, int num_iter);
 int gsc_gnn_embed_bwd(const float* x, int64_t num_nodes, int in_dim, const int32_t* rowptr,
                       const int32_t* col, const int32_t* graph_ptr, int64_t num_graphs,
                       int max_nodes, const float* params, int hidden, int num_layers, int num_iter,
