@@ -272,13 +272,25 @@ def run_ours(args):
         ops.timer = {}
         launches0 = ops.launch_count
         g_keep, graphed, p_keep, gpredict = graphed, None, gpredict, None
-        for _ in range(op_steps):
+        for i_op in range(op_steps):
             flush.zero_()
+            if args.timeline and i_op == op_steps - 1:
+                ops.timeline = []
+                tl0 = torch.cuda.Event(enable_timing=True)
+                tl0.record()
             step(resident)
         graphed, gpredict = g_keep, p_keep
         barrier()
         launches = (ops.launch_count - launches0) // op_steps
         timer, ops.timer = ops.timer, None
+    if args.timeline and ops.timeline and rank == 0:
+        # where every entry point of the last kernel-by-kernel step ran: stream, start, end (ms from step start)
+        torch.cuda.synchronize()
+        streams = {}
+        for name, a, b, sh in sorted(ops.timeline, key=lambda r: tl0.elapsed_time(r[1])):
+            sid = streams.setdefault(sh, len(streams))
+            print(f"[timeline] s{sid} {tl0.elapsed_time(a):8.3f} -> {tl0.elapsed_time(b):8.3f}  {name}", file=sys.stderr)
+        ops.timeline = None
     per_op = {k: sum(a.elapsed_time(b) for a, b in v) / op_steps for k, v in timer.items()}
     per_op_n = {k: len(v) / op_steps for k, v in timer.items()}
 
@@ -658,6 +670,8 @@ def main():
                          "(default: on for c4, off otherwise)")
     ap.add_argument("--dense-mask", action="store_true",
                     help="carry the dense [B, A] mask tensor instead of the per-state node counts")
+    ap.add_argument("--timeline", action="store_true",
+                    help="print, per entry point of one kernel-by-kernel step, its stream and start/end time (stderr)")
     ap.add_argument("--no-graph", dest="graph", action="store_false",
                     help="c3: launch the update kernel by kernel instead of replaying its CUDA graph")
     ap.add_argument("--precision", default=os.environ.get("GSC_BENCH_PRECISION", "tf32x3"),

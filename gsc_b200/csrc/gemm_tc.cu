@@ -647,7 +647,9 @@ int gemm_tc_launch(const gsc_gemm_args* a, int64_t M, int64_t N, float* C, int64
   p.tiles_n = (int)ceil_div(N, kTcBN);
   const int64_t tiles = (int64_t)p.tiles_m * p.tiles_n;
   // split K when the output tiles alone cannot fill the machine; keep >= 4 k-blocks per split
-  int64_t want = tiles >= kNumSMs ? 1 : ceil_div(kNumSMs, tiles);
+  // (tiles * splits work items on kNumSMs persistent CTAs: never more items than CTAs, or a few CTAs
+  // would run two of them and the launch would take two rounds)
+  int64_t want = tiles >= kNumSMs ? 1 : kNumSMs / tiles;
   int64_t max_by_k = kb / 4 > 0 ? kb / 4 : 1;
   if (want > max_by_k) want = max_by_k;
   if (workspace == nullptr) want = 1;

@@ -86,6 +86,7 @@ def _count(n: int):
 # kernel).  ``timer`` maps name -> list of (start_event, end_event); events are recorded on the
 # launching stream around the C-ABI call, no synchronisation happens here.
 timer = None
+timeline = None       # optional list of (name, start_event, end_event, stream handle) in launch order
 
 
 class _Timed:
@@ -104,6 +105,8 @@ class _Timed:
         if timer is not None:
             self.ev[1].record(torch.cuda.current_stream())
             timer.setdefault(self.name, []).append(self.ev)
+            if timeline is not None:
+                timeline.append((self.name, self.ev[0], self.ev[1], torch.cuda.current_stream().cuda_stream))
         return False
 
 
