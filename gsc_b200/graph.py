@@ -53,6 +53,22 @@ class GraphData:
         yield "edge_index", self.edge_index
         yield "mask", self.mask
 
+    # item access and from_dict: how the reference attaches the mask (simulator_wrapper.py:306) and
+    # rebuilds the stored rows when it samples (buffer.py:68,77)
+    def __len__(self):  # three (key, tensor) rows: numpy stores a state as one row of an object array
+        return 3
+
+    def __setitem__(self, key, value):
+        setattr(self, key, value)
+
+    def __getitem__(self, key):
+        return getattr(self, key)
+
+    @classmethod
+    def from_dict(cls, mapping) -> "GraphData":
+        d = dict(mapping)
+        return cls(d.pop("x"), d.pop("edge_index"), d.pop("mask", None), **d)
+
 
 class GraphBatch:
     """A collated minibatch in ``Batch.from_data_list`` layout (reference
