@@ -1285,7 +1285,429 @@ __global__ void __launch_bounds__(kGnnThreads, 1) gnn_bwd_tc_kernel(const GnnArg
   }
 }
 
-// (W) of the tcgen05 backward: for every conv, [dWl|dbl ; dWr|dbr] = sum over its applications and over
+// ================================ gather backward, warp-level node transforms ===============
+// The same gather algorithm as gnn_bwd_tc_kernel (target pass over in-edges, source pass over the
+// out-edges of a symmetric graph through the reverse-edge index, no floating-point atomics), built
+// for occupancy instead of tensor cores: the edge passes are chains of dependent shared-memory
+// gathers and short FMA sequences, i.e. latency, and what hides latency is more resident warps.
+//   * CTA = 128 threads = 128 node slots (one thread owns one node for a whole chunk of graphs);
+//   * shared memory per CTA: three row arrays (xl, xr, g; the gradients d_xl / d_xr / d_h stay in the
+//     owner's registers), the per-edge (alpha, ds) pair, the chunk's CSR with its reverse index and
+//     ONE c-major copy of every conv's weights -- ~60 KB, so three CTAs (12 warps, 170 registers
+//     per thread) share an SM where the tcgen05 variant, with its operand images, fits one;
+//   * the node transforms ([32 nodes of a warp] x [HP] x [2HP] and back) run as warp-level 3xTF32
+//     mma.sync m16n8k8 through a small warp-private tile: ~110 instructions per warp instead of the
+//     ~1400 of the FMA form, and none of the operand staging, TMEM round trips and CTA barriers that
+//     tcgen05 needs for such small products;
+//   * weight gradients: [dxl|dxr] rows go to the workspace for gnn_wgrad_kernel, as before.
+// Used for symmetric batches whose largest graph has at most 128 nodes; larger graphs take the
+// tcgen05 kernel (<= 384 nodes) or the scatter kernel.
+constexpr int kGbThreads = 128;
+constexpr int kGbEdgesPerNode = 6;       // per-edge arrays per node slot (self-loops included)
+
+template <int HP>
+struct GbL {
+  static constexpr int kConvFloats = 2 * HP * HP + 4 * HP;     // Wl[c][k], Wr[c][k], bl, br, att, (pad)
+  static constexpr int kSlotFloats = (kGbThreads / 32) * 2 * HP;   // per-warp d_att | d_bias sums, per conv
+  static constexpr int kTS = HP + 4;                           // row stride of the warp tiles (conflict-free fragments)
+  static constexpr int kTileFloats = 32 * kTS;                 // one [32 node slots][HP] tile per warp
+  __host__ __device__ static constexpr size_t bytes(int num_convs) {
+    return (size_t)num_convs * (kConvFloats + kSlotFloats) * 4 + 3 * (size_t)kGbThreads * HP * 4 +
+           (size_t)(kGbThreads / 32) * kTileFloats * 4 +
+           (size_t)kGbThreads * 8 /*pq*/ + ((size_t)kGbThreads + 4) * 4 /*rp*/ +
+           (size_t)kGbEdgesPerNode * kGbThreads * (4 + 4 + 2 + 2) + (size_t)kGbThreads * 2 /*perm*/ + 64 * 4;
+  }
+};
+
+// Warp-level tensor-core MMA (m16n8k8, TF32 operands, fp32 accumulate).  The node transforms of the
+// gather kernel are [32 nodes] x [HP] x [2HP] per warp: far too small to stage for tcgen05, but as
+// 3xTF32 mma.sync they cost ~110 instructions per warp where the FMA form costs ~1400.
+__device__ __forceinline__ void mma_tf32(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
+               : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+// x = hi + lo with hi = the 19 high bits (what the tensor core reads), lo = x - hi (exact), truncated likewise
+__device__ __forceinline__ void tf32_split(float x, uint32_t& hi, uint32_t& lo) {
+  hi = __float_as_uint(x) & 0xffffe000u;
+  lo = __float_as_uint(x - __uint_as_float(hi)) & 0xffffe000u;
+}
+// acc[mt][nt] += A[32 x 8*KS] (warp tile in shared memory, row stride TS) x B, with B(k, n) = bmat[n*bn + k*bk]
+// (any strided view of a weight matrix in shared memory), as 3xTF32: hi*hi + hi*lo + lo*hi.
+template <int KS, int NT, int TS>
+__device__ __forceinline__ void warp_gemm_3xtf32(float (&acc)[2][NT][4], const float* __restrict__ tile,
+                                                 const float* __restrict__ bmat, int bn, int bk, int lane) {
+  const int gid = lane >> 2, tig = lane & 3;
+#pragma unroll
+  for (int ks = 0; ks < KS; ++ks) {
+    uint32_t ah[2][4], al[2][4];
+#pragma unroll
+    for (int mt = 0; mt < 2; ++mt) {
+      const float* r0 = tile + (16 * mt + gid) * TS + 8 * ks + tig;
+      tf32_split(r0[0], ah[mt][0], al[mt][0]);
+      tf32_split(r0[8 * TS], ah[mt][1], al[mt][1]);
+      tf32_split(r0[4], ah[mt][2], al[mt][2]);
+      tf32_split(r0[8 * TS + 4], ah[mt][3], al[mt][3]);
+    }
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt) {
+      const float* bp = bmat + (8 * nt + gid) * bn + (8 * ks + tig) * bk;
+      uint32_t bh0, bl0, bh1, bl1;
+      tf32_split(bp[0], bh0, bl0);
+      tf32_split(bp[4 * bk], bh1, bl1);
+#pragma unroll
+      for (int mt = 0; mt < 2; ++mt) {
+        mma_tf32(acc[mt][nt], ah[mt], bl0, bl1);
+        mma_tf32(acc[mt][nt], al[mt], bh0, bh1);
+        mma_tf32(acc[mt][nt], ah[mt], bh0, bh1);
+      }
+    }
+  }
+}
+
+template <int HP>
+__global__ void __launch_bounds__(kGbThreads, 3) gnn_bwd_gather_kernel(const GnnArgs p) {
+  using L = GbL<HP>;
+  constexpr int cap = kGbThreads, emax = kGbEdgesPerNode * kGbThreads;
+  extern __shared__ float4 smem4[];
+  float* wsm = reinterpret_cast<float*>(smem4);                     // [num_convs][kConvFloats]
+  float* slot_s = wsm + p.num_convs * L::kConvFloats;               // [num_convs][warps][2HP]
+  float* xl_s = slot_s + p.num_convs * L::kSlotFloats;              // [cap][HP]
+  float* xr_s = xl_s + cap * HP;
+  float* g_s = xr_s + cap * HP;
+  float* tile_s = g_s + cap * HP;                                   // [warps][32][kTS] warp-private MMA operand tiles
+  float2* pq_s = reinterpret_cast<float2*>(tile_s + (kGbThreads / 32) * L::kTileFloats);   // [cap] 0.6 att.xl_j, 0.6 att.xr_i
+  int* rp_s = reinterpret_cast<int*>(pq_s + cap);                   // [cap + 4]
+  float* es_s = reinterpret_cast<float*>(rp_s + cap + 4);           // [emax] score, then alpha
+  float* eda_s = es_s + emax;                                       // [emax] g_i.xl_j, then d_score
+  uint16_t* col_s = reinterpret_cast<uint16_t*>(eda_s + emax);      // [emax]
+  uint16_t* rev_s = col_s + emax;                                   // [emax]
+  uint16_t* perm_s = rev_s + emax;                                  // [cap]
+  int* hist_s = reinterpret_cast<int*>(perm_s + cap);               // [64]
+  if (p.stats == nullptr || p.stats[3] != 0 || p.flags[0] != 0) return;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  float* tile = tile_s + warp * L::kTileFloats;
+  const int gid = lane >> 2, tig = lane & 3;
+
+  // ---- weights, c-major and zero padded: Wl[c][k] at wsm[c*HP + k], Wr behind it, then bl, br, att ----
+  for (int cv = 0; cv < p.num_convs; ++cv) {
+    const int in = cv == 0 ? p.in_dim : p.H, H = p.H;
+    const float* src = p.params + conv_param_offset(cv, p.in_dim, p.H);
+    const float* att = src;
+    const float* Wl = src + 2 * H;
+    const float* bl = Wl + (int64_t)H * in;
+    const float* Wr = bl + H;
+    const float* br = Wr + (int64_t)H * in;
+    float* w = wsm + cv * L::kConvFloats;
+    for (int t = tid; t < 2 * HP * HP; t += kGbThreads) {
+      const int r = t >= HP * HP, tt = t - r * HP * HP, c = tt / HP, k = tt - c * HP;
+      w[t] = (c < H && k < in) ? (r ? Wr : Wl)[c * in + k] : 0.f;
+    }
+    for (int t = tid; t < HP; t += kGbThreads) {
+      const bool ok = t < H;
+      w[2 * HP * HP + t] = ok ? bl[t] : 0.f;
+      w[2 * HP * HP + HP + t] = ok ? br[t] : 0.f;
+      w[2 * HP * HP + 2 * HP + t] = ok ? att[t] : 0.f;
+      w[2 * HP * HP + 3 * HP + t] = 0.f;
+    }
+    for (int t = tid; t < L::kSlotFloats; t += kGbThreads) slot_s[cv * L::kSlotFloats + t] = 0.f;
+  }
+  __syncthreads();
+
+  const int num_chunks = (p.B + p.G - 1) / p.G;
+  for (int chunk = blockIdx.x; chunk < num_chunks; chunk += gridDim.x) {
+    const int g0 = chunk * p.G, g1 = min(p.B, g0 + p.G);
+    const int nbase = p.graph_ptr[g0];
+    const int nc = p.graph_ptr[g1] - nbase;
+    if (nc > cap) __trap();     // a graph larger than the max_nodes the launch was sized for: fail loudly
+    // chunk CSR -> shared memory, degree-sorted node order, reverse-edge index (see gnn_bwd_tc_kernel)
+    const int ebase = p.rowptr[nbase];
+    const int ne = p.rowptr[nbase + nc] - ebase;            // <= emax (checked by gnn_chunk_edges_kernel)
+    for (int i = tid; i <= nc; i += kGbThreads) rp_s[i] = p.rowptr[nbase + i] - ebase;
+    for (int e = tid; e < ne; e += kGbThreads) col_s[e] = (uint16_t)(p.col[ebase + e] - nbase);
+    if (tid < 64) hist_s[tid] = 0;
+    __syncthreads();
+    if (tid < nc) atomicAdd(hist_s + 63 - min(rp_s[tid + 1] - rp_s[tid], 63), 1);
+    __syncthreads();
+    if (warp == 0) {                                   // exclusive scan of the 64 buckets
+      int a0 = hist_s[2 * lane], a1 = hist_s[2 * lane + 1];
+      int incl = a0 + a1;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += t;
+      }
+      hist_s[2 * lane] = incl - a0 - a1;
+      hist_s[2 * lane + 1] = incl - a1;
+    }
+    __syncthreads();
+    if (tid < nc) perm_s[atomicAdd(hist_s + 63 - min(rp_s[tid + 1] - rp_s[tid], 63), 1)] = (uint16_t)tid;
+    if (tid < nc) {
+      const int e0 = rp_s[tid], e1 = rp_s[tid + 1];
+      for (int e = e0; e < e1; ++e) {
+        const int j = col_s[e];
+        int k = 0;
+        for (int q = e0; q < e; ++q) k += (col_s[q] == j);
+        int r = e;
+        for (int q = rp_s[j]; q < rp_s[j + 1]; ++q)
+          if (col_s[q] == tid && k-- == 0) { r = q; break; }
+        rev_s[e] = (uint16_t)r;
+      }
+    }
+    __syncthreads();
+
+    // this thread's node for the whole chunk (rows of similar length share a warp)
+    const bool active = tid < nc;
+    const int i = active ? perm_s[tid] : 0;
+    const int64_t node = (int64_t)nbase + i;
+    const int e0 = active ? rp_s[i] : 0, e1 = active ? rp_s[i + 1] : 0;
+    const float inv_deg = active ? 1.f / (float)(e1 - e0) : 0.f;
+    float g[HP];                                         // d_out of the current application for node i
+#pragma unroll
+    for (int c = 0; c < HP; ++c) g[c] = 0.f;
+    if (active) {                                        // pool backward: d_emb[graph] / n_graph
+      int gg = g0;
+      while (gg + 1 < g1 && p.graph_ptr[gg + 1] - nbase <= i) ++gg;
+      const float inv_n = 1.f / (float)(p.graph_ptr[gg + 1] - p.graph_ptr[gg]);
+#pragma unroll
+      for (int c = 0; c < HP; ++c) g[c] = (c < p.H) ? p.d_emb[(size_t)gg * p.emb_ld + c] * inv_n : 0.f;
+    }
+
+    for (int a = p.num_apps - 1; a >= 0; --a) {
+      const int cv = p.app_conv[a];
+      const float* w = wsm + cv * L::kConvFloats;
+      const float* vec = w + 2 * HP * HP;                // bl | br | att
+      float* slot = slot_s + cv * L::kSlotFloats + warp * 2 * HP;
+      // ---- 1. recompute [xl | xr] = h_in [Wl ; Wr]^T on the warp's 32 node slots (3xTF32 mma.sync):
+      //         own input row -> warp tile -> A fragments; B fragments straight from the c-major weights;
+      //         the accumulator fragments (+ bias) go to the xl / xr rows of their nodes ----
+      {
+        {
+          float hin[HP];
+#pragma unroll
+          for (int k = 0; k < HP; ++k) hin[k] = 0.f;
+          if (active) {
+            if (a == 0) {
+#pragma unroll
+              for (int k = 0; k < HP; ++k) hin[k] = (k < p.in_dim) ? p.x[node * p.in_dim + k] : 0.f;
+            } else {
+              load_row<HP>(p.saved + ((size_t)(a - 1) * p.Nt + node) * HP, hin);
+            }
+          }
+          store_row<HP>(tile + lane * L::kTS, hin);
+        }
+        __syncwarp();
+        float acc[2][2 * HP / 8][4];
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+          for (int nt = 0; nt < 2 * HP / 8; ++nt)
+#pragma unroll
+            for (int q = 0; q < 4; ++q) acc[mt][nt][q] = 0.f;
+        if (a == 0 && p.in_dim <= 8) warp_gemm_3xtf32<1, 2 * HP / 8, L::kTS>(acc, tile, w, HP, 1, lane);
+        else warp_gemm_3xtf32<HP / 8, 2 * HP / 8, L::kTS>(acc, tile, w, HP, 1, lane);
+        // rows (16 mt + gid) and (+ 8), channels 8 nt + 2 tig (+ 1): nt < HP/8 is xl, the rest xr
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+          for (int hrow = 0; hrow < 2; ++hrow) {
+            const int slot_i = warp * 32 + 16 * mt + 8 * hrow + gid;
+            const bool live = slot_i < nc;
+            const int ni = live ? perm_s[slot_i] : 0;
+            float pl = 0.f, pr = 0.f;
+#pragma unroll
+            for (int nt = 0; nt < 2 * HP / 8; ++nt) {
+              const int ch = (8 * nt + 2 * tig) % HP;
+              const bool is_r = nt >= HP / 8;
+              const float b0 = vec[(is_r ? HP : 0) + ch], b1 = vec[(is_r ? HP : 0) + ch + 1];
+              const float v0 = acc[mt][nt][2 * hrow] + b0, v1 = acc[mt][nt][2 * hrow + 1] + b1;
+              const float d = fmaf(vec[2 * HP + ch], v0, vec[2 * HP + ch + 1] * v1);
+              if (is_r) pr += d; else pl += d;
+              if (live) *reinterpret_cast<float2*>((is_r ? xr_s : xl_s) + ni * HP + ch) = make_float2(v0, v1);
+            }
+            pl += __shfl_xor_sync(0xffffffffu, pl, 1); pr += __shfl_xor_sync(0xffffffffu, pr, 1);
+            pl += __shfl_xor_sync(0xffffffffu, pl, 2); pr += __shfl_xor_sync(0xffffffffu, pr, 2);
+            if (live && tig == 0) pq_s[ni] = make_float2(0.6f * pl, 0.6f * pr);     // score scalars p_j, q_i
+          }
+        // g = relu'(out) d_out / deg of the own node; conv-bias gradient
+        float dbias[HP];
+#pragma unroll
+        for (int c = 0; c < HP; ++c) dbias[c] = 0.f;
+        if (active) {
+          if (p.app_relu[a]) {
+            float out[HP];
+            load_row<HP>(p.saved + ((size_t)a * p.Nt + node) * HP, out);
+#pragma unroll
+            for (int c = 0; c < HP; ++c) g[c] = out[c] > 0.f ? g[c] : 0.f;
+          }
+#pragma unroll
+          for (int c = 0; c < HP; ++c) { dbias[c] = g[c]; g[c] *= inv_deg; }
+          store_row<HP>(g_s + i * HP, g);
+        }
+#pragma unroll
+        for (int c = 0; c < HP; ++c) {
+          const float sb = warp_sum(dbias[c]);
+          if (lane == (c & 31)) slot[HP + c] += sb;       // warp-private slot
+        }
+      }
+      __syncthreads();
+
+      // ---- 2. target side (see gnn_bwd_tc_kernel 4T): alpha_e, ds_e of every in-edge, d_xr ----
+      float datt[HP], dxr[HP];
+#pragma unroll
+      for (int c = 0; c < HP; ++c) { datt[c] = 0.f; dxr[c] = 0.f; }
+      if (active) {
+        float xr[HP], sg[HP];
+        load_row<HP>(xr_s + i * HP, xr);
+        const float q_i = pq_s[i].y;
+        float m = -INFINITY;
+        {
+          float b[HP];
+          load_row<HP>(vec + 2 * HP, b);
+#pragma unroll
+          for (int c = 0; c < HP; ++c) b[c] *= 0.4f;
+          // scores and g.xl_j of every in-edge: iterations are independent (the softmax statistics
+          // are taken from shared memory afterwards), so the loads of the next edge overlap this one
+#pragma unroll 2
+          for (int e = e0; e < e1; ++e) {
+            const int j = col_s[e];
+            float v[HP];
+            load_row<HP>(xl_s + j * HP, v);
+            const float sc_e = pq_s[j].x + q_i + abs_score<HP>(v, xr, b);
+            es_s[e] = sc_e;
+            eda_s[e] = dot4<HP>(g, v);
+            m = fmaxf(m, sc_e);
+          }
+        }
+        float l = 0.f, dot = 0.f;
+        for (int e = e0; e < e1; ++e) {
+          const float pe = __expf(es_s[e] - m);
+          es_s[e] = pe;
+          l += pe;
+          dot = fmaf(pe, eda_s[e], dot);
+        }
+        const float inv_l = 1.f / (l + 1e-16f);
+        dot *= inv_l;
+        float ds_sum = 0.f;
+#pragma unroll
+        for (int c = 0; c < HP; ++c) sg[c] = 0.f;
+#pragma unroll 2
+        for (int e = e0; e < e1; ++e) {
+          const int j = col_s[e];
+          float v[HP];
+          load_row<HP>(xl_s + j * HP, v);
+          const float alpha = es_s[e] * inv_l;
+          const float ds = alpha * (eda_s[e] - dot);
+          es_s[e] = alpha;
+          eda_s[e] = ds;
+          ds_sum += ds;
+#pragma unroll
+          for (int c = 0; c < HP; ++c) sg[c] += signed_by(ds, v[c] + xr[c]);
+        }
+        const float base = 0.6f * ds_sum;
+#pragma unroll
+        for (int c = 0; c < HP; ++c) {
+          const float wv = fmaf(0.4f, sg[c], base);
+          datt[c] = xr[c] * wv;
+          dxr[c] = vec[2 * HP + c] * wv;
+        }
+      }
+      __syncthreads();
+
+      // ---- 3. source side (4S): d_xl over the out-edges = this node's own CSR row of a symmetric graph ----
+      float dxl[HP];
+#pragma unroll
+      for (int c = 0; c < HP; ++c) dxl[c] = 0.f;
+      if (active) {
+        float v[HP], sg[HP];
+        load_row<HP>(xl_s + i * HP, v);
+#pragma unroll
+        for (int c = 0; c < HP; ++c) sg[c] = 0.f;
+        float ds_sum = 0.f;
+#pragma unroll 2
+        for (int e = e0; e < e1; ++e) {
+          const int ti = col_s[e], r = rev_s[e];
+          const float alpha = es_s[r], ds = eda_s[r];
+          float xr[HP], gi[HP];
+          load_row<HP>(xr_s + ti * HP, xr);
+          load_row<HP>(g_s + ti * HP, gi);
+          ds_sum += ds;
+#pragma unroll
+          for (int c = 0; c < HP; ++c) {
+            dxl[c] = fmaf(alpha, gi[c], dxl[c]);
+            sg[c] += signed_by(ds, v[c] + xr[c]);
+          }
+        }
+        const float base = 0.6f * ds_sum;
+#pragma unroll
+        for (int c = 0; c < HP; ++c) {
+          const float wv = fmaf(0.4f, sg[c], base);
+          datt[c] = fmaf(v[c], wv, datt[c]);
+          dxl[c] = fmaf(vec[2 * HP + c], wv, dxl[c]);
+        }
+        // [dxl | dxr] row -> workspace (gnn_wgrad_kernel)
+        float* dxa = p.dx + ((size_t)a * p.Nt + node) * (2 * HP);
+        store_row<HP>(dxa, dxl);
+        store_row<HP>(dxa + HP, dxr);
+      }
+#pragma unroll
+      for (int c = 0; c < HP; ++c) {
+        const float sa = warp_sum(datt[c]);
+        if (lane == (c & 31)) slot[c] += sa;
+      }
+      // ---- 4. d_h_in = d_xl Wl + d_xr Wr -> d_out of application a-1: two [32 x HP] x [HP x HP] products
+      //         through the warp tile (d_xl rows, then d_xr rows); the result rows return through the tile ----
+      if (a > 0) {
+        float acc[2][HP / 8][4];
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+          for (int nt = 0; nt < HP / 8; ++nt)
+#pragma unroll
+            for (int q = 0; q < 4; ++q) acc[mt][nt][q] = 0.f;
+        __syncwarp();
+        store_row<HP>(tile + lane * L::kTS, dxl);
+        __syncwarp();
+        warp_gemm_3xtf32<HP / 8, HP / 8, L::kTS>(acc, tile, w, 1, HP, lane);               // B(k = c, n) = Wl[c][n]
+        __syncwarp();
+        store_row<HP>(tile + lane * L::kTS, dxr);
+        __syncwarp();
+        warp_gemm_3xtf32<HP / 8, HP / 8, L::kTS>(acc, tile, w + HP * HP, 1, HP, lane);     // ... + d_xr Wr
+        __syncwarp();
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+          for (int nt = 0; nt < HP / 8; ++nt) {
+            *reinterpret_cast<float2*>(tile + (16 * mt + gid) * L::kTS + 8 * nt + 2 * tig) = make_float2(acc[mt][nt][0], acc[mt][nt][1]);
+            *reinterpret_cast<float2*>(tile + (16 * mt + 8 + gid) * L::kTS + 8 * nt + 2 * tig) = make_float2(acc[mt][nt][2], acc[mt][nt][3]);
+          }
+        __syncwarp();
+        load_row<HP>(tile + lane * L::kTS, g);
+      }
+      __syncthreads();        // the rows are rewritten by the next application / chunk
+    }
+  }
+
+  // ---- CTA partial sums of d_att and the conv bias -> partial row (the rest is gnn_wgrad_kernel's) ----
+  __syncthreads();
+  const int64_t P = conv_param_offset(p.num_convs, p.in_dim, p.H);
+  float* out = p.partials + (size_t)blockIdx.x * P;
+  for (int cv = 0; cv < p.num_convs; ++cv) {
+    float* o = out + conv_param_offset(cv, p.in_dim, p.H);
+    const float* sl = slot_s + cv * L::kSlotFloats;
+    for (int t = tid; t < p.H; t += kGbThreads) {
+      float sa = 0.f, sb = 0.f;
+      for (int wv = 0; wv < kGbThreads / 32; ++wv) {
+        sa += sl[wv * 2 * HP + t];
+        sb += sl[wv * 2 * HP + HP + t];
+      }
+      o[t] = sa;
+      o[p.H + t] = sb;
+    }
+  }
+}
+
+// (W) of the gather backward kernels: for every conv, [dWl|dbl ; dWr|dbr] = sum over its applications and over
 // all nodes of [dxl|dxr]_i (x) [h_in_i | 1].  Streaming reduction: CTA b owns the node slice
 // [b*Nt/grid, (b+1)*Nt/grid) and walks it in tiles of kWgTile nodes staged in shared memory (next tile
 // prefetched into registers); thread = (node lane, 4 channels x 8 input columns), i.e. per node three
@@ -1539,6 +1961,16 @@ static int launch_fwd_tc(GnnArgs a, int max_nodes, cudaStream_t st, bool* done) 
   return GSC_OK;
 }
 
+// GSC_GNN_BWD=1 keeps the tcgen05 gather backward for graphs that the FMA gather kernel could take (experiments)
+static int gnn_bwd_variant() {
+  static int mode = -1;
+  if (mode < 0) {
+    const char* e = getenv("GSC_GNN_BWD");
+    mode = e ? atoi(e) : 0;
+  }
+  return mode;
+}
+
 static bool gnn_use_tc() {
   static int mode = -1;
   if (mode < 0) {
@@ -1586,7 +2018,29 @@ static int launch_bwd_both(GnnArgs a, int max_nodes, float* d_params, cudaStream
   const bool tc = gnn_use_tc() && a.stats != nullptr && plan_bwd_tc<HP>(a, max_nodes, &cap_t, &cols, &smem_t);
   int grid = grid_f;
   GSC_CUDA_TRY(cudaMemsetAsync(const_cast<int32_t*>(a.flags), 0, sizeof(int32_t), st));
-  if (tc) {
+  const size_t smem_g = GbL<HP>::bytes(a.num_convs);
+  const bool gather_fma = gnn_bwd_variant() != 1 && a.stats != nullptr && max_nodes <= kGbThreads &&
+                          3 * (smem_g + 1024) <= 227 * 1024;
+  if (gather_fma) {
+    GnnArgs t = a;
+    t.cap = kGbThreads;
+    t.G = graphs_per_cta(kGbThreads, max_nodes, t.B, 3);
+    const int chunks_t = (t.B + t.G - 1) / t.G;
+    gnn_chunk_edges_kernel<<<(chunks_t + 255) / 256, 256, 0, st>>>(t.rowptr, t.graph_ptr, t.B, t.G,
+                                                                   kGbEdgesPerNode * kGbThreads, const_cast<int32_t*>(a.flags));
+    GSC_LAUNCH_CHECK("gnn_chunk_edges_kernel");
+    int grid_g = 3 * (kNumSMs - sm_reserve());
+    if (chunks_t < grid_g) grid_g = chunks_t;
+    grid = grid_g > grid_f ? grid_g : grid_f;       // one partial row per CTA of either kernel
+    GSC_CUDA_TRY(cudaFuncSetAttribute(gnn_bwd_gather_kernel<HP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_g));
+    gnn_bwd_gather_kernel<HP><<<grid, kGbThreads, smem_g, st>>>(t);       // returns at once unless symmetric
+    GSC_LAUNCH_CHECK("gnn_bwd_gather_kernel");
+    const int smem_w = WgL<HP>::kSmemFloats * 4;
+    GSC_CUDA_TRY(cudaFuncSetAttribute(gnn_wgrad_kernel<HP>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_w));
+    gnn_wgrad_kernel<HP><<<grid, kGnnThreads, smem_w, st>>>(t);           // its weight gradients (same condition)
+    GSC_LAUNCH_CHECK("gnn_wgrad_kernel");
+    a.gather_kernel_launched = 1;
+  } else if (tc) {
     GnnArgs t = a;
     t.cap = cap_t;
     t.G = graphs_per_cta(cap_t, max_nodes, t.B, 1);
@@ -1667,8 +2121,8 @@ extern "C" int gsc_gnn_embed_fwd(const float* x, int64_t Nt, int in_dim, const i
 }
 
 // Partial gradients of every CTA, plus (graphs too large for shared memory) the node-row scratch.
-static size_t bwd_partials_bytes(int in_dim, int H, int num_layers) {
-  return ((size_t)kNumSMs * (size_t)conv_param_offset(num_layers, in_dim, H) * 4 + 255) / 256 * 256;
+static size_t bwd_partials_bytes(int in_dim, int H, int num_layers) {   // one row per CTA, up to 3 CTAs per SM
+  return ((size_t)3 * kNumSMs * (size_t)conv_param_offset(num_layers, in_dim, H) * 4 + 255) / 256 * 256;
 }
 constexpr size_t kBwdFlagBytes = 256;    // kernel-selection flags, between the partials and the node-row scratch
 static bool bwd_rows_in_global(int max_nodes, int H, int num_layers) {
