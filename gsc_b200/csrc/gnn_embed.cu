@@ -1708,56 +1708,59 @@ __global__ void __launch_bounds__(kGbThreads, 3) gnn_bwd_gather_kernel(const Gnn
 }
 
 // (W) of the gather backward kernels: for every conv, [dWl|dbl ; dWr|dbr] = sum over its applications and over
-// all nodes of [dxl|dxr]_i (x) [h_in_i | 1].  Streaming reduction: CTA b owns the node slice
-// [b*Nt/grid, (b+1)*Nt/grid) and walks it in tiles of kWgTile nodes staged in shared memory (next tile
-// prefetched into registers); thread = (node lane, 4 channels x 8 input columns), i.e. per node three
-// 128-bit shared-memory loads feed 32 FMAs.  The node lanes are added in a fixed order and the CTA's
-// sums go to the W / bl / br entries of partial row b (gnn_bwd_reduce_kernel adds the rows).
-// Algorithmic bytes: 4 * (2HP + d_in) per node and application, read once.
+// all nodes of [dxl|dxr]_i (x) [h_in_i | 1], i.e. the product dX^T [2HP x nodes] x [H_in | 1] [nodes x (HP+1)]
+// with the reduction over the nodes.  Streaming kernel: CTA b owns the node slice [b*Nt/grid, (b+1)*Nt/grid)
+// and walks it in tiles of 64 nodes staged in shared memory (next tile prefetched into registers); each of
+// the eight warps takes one 8-node k-step of a tile and issues 3xTF32 mma.sync m16n8k8 for all 2HP/16 x
+// (HP+8)/8 output tiles (the A operand is dX read transposed out of the staged rows).  The warps' accumulators are
+// added in a fixed order and the CTA's sums go to the W / bl / br entries of partial row b
+// (gnn_bwd_reduce_kernel adds the rows).  Algorithmic bytes: 4 * (2HP + d_in) per node and application.
 template <int HP>
 struct WgL {
-  static constexpr int kCh = 2 * HP;                           // channels: dxl | dxr
-  static constexpr int kCols = HP + 8;                         // h row in smem: HP inputs, 1.0, zero padding
-  static constexpr int kTiles = (kCh / 4) * (kCols / 8);       // thread tiles (4 channels x 8 columns) per node lane
-  static constexpr int kLanes = kGnnThreads / kTiles;          // node lanes (5 for HP = 24)
-  static constexpr int kTile = 8 * kLanes;                     // nodes per staged tile
-  static constexpr int kTileF4 = kTile * (kCh + HP) / 4;       // float4 per staged tile
+  static constexpr int kCh = 2 * HP;                           // channels: dxl | dxr (padded to a multiple of 16 below)
+  static constexpr int kMT = (kCh + 15) / 16;                  // m16 tiles over the channels
+  static constexpr int kNT = (HP + 8) / 8;                     // n8 tiles over [h | 1 | 0...]
+  static constexpr int pad_stride(int n) { return (n + 8) % 16 == 8 ? n + 8 : n + 16; }   // result % 32 is 8 or 24
+  static constexpr int kDS = pad_stride(16 * kMT);             // dx row stride in smem: conflict-free transposed A reads
+  static constexpr int kHS = pad_stride(8 * kNT);              // h row stride in smem: likewise for the B reads
+  static constexpr int kTile = 64;                             // nodes per staged tile = 8 warps x one k-step
+  static constexpr int kTileF4 = kTile * (kCh + HP) / 4;       // float4 per staged tile (global side)
   static constexpr int kPre = (kTileF4 + kGnnThreads - 1) / kGnnThreads;
-  static constexpr int kSmemFloats = 2 * kTile * (kCh + kCols) + kLanes * kCh * (kCols + 1);
-  static_assert(kLanes >= 1, "more thread tiles than threads");
+  static constexpr int kRedStride = 8 * kNT + 1;
+  static constexpr int kSmemFloats = 2 * kTile * (kDS + kHS) + (kGnnThreads / 32) * 16 * kMT * kRedStride;
 };
 
 template <int HP>
 __global__ void __launch_bounds__(kGnnThreads) gnn_wgrad_kernel(const GnnArgs p) {
   using L = WgL<HP>;
-  constexpr int kCh = L::kCh, kCols = L::kCols, kLanes = L::kLanes, kTile = L::kTile;
+  constexpr int kCh = L::kCh, kMT = L::kMT, kNT = L::kNT, kDS = L::kDS, kHS = L::kHS, kTile = L::kTile;
   extern __shared__ float4 smem4[];
-  float* dx_s = reinterpret_cast<float*>(smem4);               // [2][kTile][kCh]
-  float* h_s = dx_s + 2 * kTile * kCh;                         // [2][kTile][kCols]
-  float* red_s = h_s + 2 * kTile * kCols;                      // [kLanes][kCh][kCols + 1]
+  float* dx_s = reinterpret_cast<float*>(smem4);               // [2][kTile][kDS]
+  float* h_s = dx_s + 2 * kTile * kDS;                         // [2][kTile][kHS]
+  float* red_s = h_s + 2 * kTile * kHS;                        // [warps][16 kMT][kRedStride]
   if (p.stats == nullptr || p.stats[3] != 0 || p.flags[0] != 0) return;     // the scatter kernel ran instead
-  const int tid = threadIdx.x;
-  const int tile_t = tid % L::kTiles, nl = tid / L::kTiles;
-  const int c0 = 4 * (tile_t % (kCh / 4)), k0 = 8 * (tile_t / (kCh / 4));
-  const bool worker = nl < kLanes;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, gid = lane >> 2, tig = lane & 3;
   const int64_t lo = p.Nt * blockIdx.x / gridDim.x, hi = p.Nt * (blockIdx.x + 1) / gridDim.x;
   const int64_t P = conv_param_offset(p.num_convs, p.in_dim, p.H);
   float* out = p.partials + (size_t)blockIdx.x * P;
-  for (int t = tid; t < 2 * kTile * 8; t += kGnnThreads)      // constant columns of the h tiles: 1, 0, ..., 0
-    h_s[(t / 8) * kCols + HP + (t & 7)] = (t & 7) == 0 ? 1.f : 0.f;
+  // constant parts of the staged rows: dx pad channels = 0; h columns HP.. = 1, 0, 0, ...
+  for (int t = tid; t < 2 * kTile * (kDS - kCh); t += kGnnThreads) dx_s[(t / (kDS - kCh)) * kDS + kCh + t % (kDS - kCh)] = 0.f;
+  for (int t = tid; t < 2 * kTile * (kHS - HP); t += kGnnThreads) h_s[(t / (kHS - HP)) * kHS + HP + t % (kHS - HP)] = (t % (kHS - HP)) == 0 ? 1.f : 0.f;
 
   for (int cv = 0; cv < p.num_convs; ++cv) {
     const int d_in = cv == 0 ? p.in_dim : p.H;
-    float acc[4][8];
+    float acc[kMT][kNT][4];
 #pragma unroll
-    for (int u = 0; u < 4; ++u)
+    for (int mt = 0; mt < kMT; ++mt)
 #pragma unroll
-      for (int q = 0; q < 8; ++q) acc[u][q] = 0.f;
+      for (int nt = 0; nt < kNT; ++nt)
+#pragma unroll
+        for (int q = 0; q < 4; ++q) acc[mt][nt][q] = 0.f;
     for (int a = 0; a < p.num_apps; ++a) {
       if (p.app_conv[a] != cv) continue;
       const float* dxa = p.dx + (size_t)a * p.Nt * kCh;
       const float* ha = a == 0 ? nullptr : p.saved + (size_t)(a - 1) * p.Nt * HP;
-      // staged tile, float4 index e: e < kTile*kCh/4 -> dx rows, else h rows
+      // staged tile, float4 index e on the global side: e < kTile*kCh/4 -> dx rows, else h rows
       float4 pre[L::kPre];
       auto fetch = [&](int64_t n0) {
 #pragma unroll
@@ -1788,10 +1791,11 @@ __global__ void __launch_bounds__(kGnnThreads) gnn_wgrad_kernel(const GnnArgs p)
         for (int r = 0; r < L::kPre; ++r) {
           const int e = tid + r * kGnnThreads;
           if (e < kTile * kCh / 4) {
-            reinterpret_cast<float4*>(dx_s + buf * kTile * kCh)[e] = pre[r];
+            const int i = e / (kCh / 4), q = e % (kCh / 4);
+            *reinterpret_cast<float4*>(dx_s + (buf * kTile + i) * kDS + 4 * q) = pre[r];
           } else if (e < L::kTileF4) {
             const int eh = e - kTile * kCh / 4, i = eh / (HP / 4), q = eh % (HP / 4);
-            *reinterpret_cast<float4*>(h_s + (buf * kTile + i) * kCols + 4 * q) = pre[r];
+            *reinterpret_cast<float4*>(h_s + (buf * kTile + i) * kHS + 4 * q) = pre[r];
           }
         }
       };
@@ -1803,30 +1807,47 @@ __global__ void __launch_bounds__(kGnnThreads) gnn_wgrad_kernel(const GnnArgs p)
       for (int64_t n0 = lo; n0 < hi; n0 += kTile, buf ^= 1) {
         const bool more = n0 + kTile < hi;
         if (more) fetch(n0 + kTile);
-        if (worker) {
-#pragma unroll 2
-          for (int i = nl; i < kTile; i += kLanes) {           // rows past the slice are zero
-            const float4 d = *reinterpret_cast<const float4*>(dx_s + (buf * kTile + i) * kCh + c0);
-            const float4 h0 = *reinterpret_cast<const float4*>(h_s + (buf * kTile + i) * kCols + k0);
-            const float4 h1 = *reinterpret_cast<const float4*>(h_s + (buf * kTile + i) * kCols + k0 + 4);
-            const float dv[4] = {d.x, d.y, d.z, d.w};
-            const float hv[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
+        {                                                      // this warp's k-step: nodes 8*warp .. 8*warp+7 of the tile
+          const float* dt = dx_s + (buf * kTile + 8 * warp) * kDS;     // rows past the slice are zero
+          const float* ht = h_s + (buf * kTile + 8 * warp) * kHS;
+          uint32_t bh[kNT][2], bl[kNT][2];
 #pragma unroll
-            for (int u = 0; u < 4; ++u)
+          for (int nt = 0; nt < kNT; ++nt) {                   // B(k = node, n = input column)
+            tf32_split(ht[tig * kHS + 8 * nt + gid], bh[nt][0], bl[nt][0]);
+            tf32_split(ht[(tig + 4) * kHS + 8 * nt + gid], bh[nt][1], bl[nt][1]);
+          }
 #pragma unroll
-              for (int q = 0; q < 8; ++q) acc[u][q] = fmaf(dv[u], hv[q], acc[u][q]);
+          for (int mt = 0; mt < kMT; ++mt) {                   // A(row = channel, col = node): dX read transposed
+            uint32_t ah[4], al[4];
+            tf32_split(dt[tig * kDS + 16 * mt + gid], ah[0], al[0]);
+            tf32_split(dt[tig * kDS + 16 * mt + gid + 8], ah[1], al[1]);
+            tf32_split(dt[(tig + 4) * kDS + 16 * mt + gid], ah[2], al[2]);
+            tf32_split(dt[(tig + 4) * kDS + 16 * mt + gid + 8], ah[3], al[3]);
+#pragma unroll
+            for (int nt = 0; nt < kNT; ++nt) {
+              mma_tf32(acc[mt][nt], ah, bl[nt][0], bl[nt][1]);
+              mma_tf32(acc[mt][nt], al, bh[nt][0], bh[nt][1]);
+              mma_tf32(acc[mt][nt], ah, bh[nt][0], bh[nt][1]);
+            }
           }
         }
         if (more) stash(buf ^ 1);                              // nobody reads that buffer in this iteration
         __syncthreads();
       }
     }
-    // node lanes -> CTA sums (fixed order) -> partial row
-    if (worker)
+    // warps -> CTA sums (fixed order) -> partial row
+    {
+      float* rw = red_s + warp * 16 * kMT * L::kRedStride;
 #pragma unroll
-      for (int u = 0; u < 4; ++u)
+      for (int mt = 0; mt < kMT; ++mt)
 #pragma unroll
-        for (int q = 0; q < 8; ++q) red_s[(nl * kCh + c0 + u) * (kCols + 1) + k0 + q] = acc[u][q];
+        for (int nt = 0; nt < kNT; ++nt) {
+          rw[(16 * mt + gid) * L::kRedStride + 8 * nt + 2 * tig] = acc[mt][nt][0];
+          rw[(16 * mt + gid) * L::kRedStride + 8 * nt + 2 * tig + 1] = acc[mt][nt][1];
+          rw[(16 * mt + gid + 8) * L::kRedStride + 8 * nt + 2 * tig] = acc[mt][nt][2];
+          rw[(16 * mt + gid + 8) * L::kRedStride + 8 * nt + 2 * tig + 1] = acc[mt][nt][3];
+        }
+    }
     __syncthreads();
     const int H = p.H;
     float* o = out + conv_param_offset(cv, p.in_dim, p.H);
@@ -1837,7 +1858,7 @@ __global__ void __launch_bounds__(kGnnThreads) gnn_wgrad_kernel(const GnnArgs p)
       const int k = kk == d_in ? HP : kk;                      // last entry: the bias column
       float sum = 0.f;
 #pragma unroll
-      for (int l = 0; l < kLanes; ++l) sum += red_s[(l * kCh + ch) * (kCols + 1) + k];
+      for (int w = 0; w < kGnnThreads / 32; ++w) sum += red_s[(w * 16 * kMT + ch) * L::kRedStride + k];
       const int64_t base = 2 * H + (is_r ? (int64_t)H * d_in + H : 0);
       if (kk == d_in) o[base + (int64_t)H * d_in + c] = sum;   // lin_{l,r}.bias
       else o[base + (int64_t)c * d_in + kk] = sum;             // lin_{l,r}.weight[c][k]
