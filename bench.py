@@ -520,18 +520,26 @@ def dp_parity(upd, dev, rank, world, args, shard_opt):
 
 
 def profiled_traffic(w, args, op_name: str):
-    """DRAM bytes (read + written) per launch of the dominant entry point's kernel, from the committed ncu
-    --set full capture of this workload (profiles/r2_traffic.json: {workload_bB_precision: {entry point:
-    {"dram_bytes_per_launch": ...}}}, written from the .ncu-rep by tools/ncu_traffic.py).  A pointer to the
-    capture, not a measurement of this run; None when no capture of this workload/precision is committed."""
+    """DRAM bytes (read + written) per launch of the kernel behind the dominant entry point, from the committed
+    ncu --set full capture of this workload (profiles/r2_traffic.json: {workload_bB_precision: {kernel name:
+    {"dram_bytes_per_launch": ...}}}, written from the raw page by tools/ncu_traffic.py; for the GEMM kernel
+    the figure is the mean over the shapes of the step).  A pointer to the capture, not a measurement of this
+    run; None when no capture of this workload/precision is committed."""
     path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r2_traffic.json")
     try:
         with open(path) as f:
             table = json.load(f)
     except (OSError, ValueError):
         return None
-    entry = table.get(f"{w['name']}_b{w['B']}_{args.precision}", {}).get(op_name)
-    return None if entry is None else entry.get("dram_bytes_per_launch")
+    base = op_name.split("[")[0]
+    kernels = {"gnn_bwd": ["gnn_bwd_gather_kernel", "gnn_bwd_tc_kernel", "gnn_bwd_kernel"],
+               "gnn_fwd": ["gnn_fwd_tc_kernel", "gnn_fwd_kernel"], "adam_soft_update": ["adam_soft_dev_kernel"],
+               "linear_fwd": ["gemm_tc_kernel"], "linear_dgrad": ["gemm_tc_kernel"], "linear_wgrad": ["gemm_tc_kernel"]}
+    entry = table.get(f"{w['name']}_b{w['B']}_{args.precision}", {})
+    for k in kernels.get(base, [base + "_kernel"]):
+        if k in entry:
+            return entry[k].get("dram_bytes_per_launch")
+    return None
 
 
 def op_bytes(name: str, w, Pa, Pc) -> float:

@@ -1302,6 +1302,10 @@ __global__ void __launch_bounds__(kGnnThreads, 1) gnn_bwd_tc_kernel(const GnnArg
 //   * weight gradients: [dxl|dxr] rows go to the workspace for gnn_wgrad_kernel, as before.
 // Used for symmetric batches whose largest graph has at most 128 nodes; larger graphs take the
 // tcgen05 kernel (<= 384 nodes) or the scatter kernel.
+#ifndef GSC_EDGE_UNROLL
+#define GSC_EDGE_UNROLL 2
+#endif
+constexpr int kGbEdgeUnroll = GSC_EDGE_UNROLL;   // edge loops of the gather kernel
 constexpr int kGbThreads = 128;
 constexpr int kGbEdgesPerNode = 6;       // per-edge arrays per node slot (self-loops included)
 
@@ -1568,7 +1572,7 @@ __global__ void __launch_bounds__(kGbThreads, 3) gnn_bwd_gather_kernel(const Gnn
           for (int c = 0; c < HP; ++c) b[c] *= 0.4f;
           // scores and g.xl_j of every in-edge: iterations are independent (the softmax statistics
           // are taken from shared memory afterwards), so the loads of the next edge overlap this one
-#pragma unroll 2
+#pragma unroll(kGbEdgeUnroll)
           for (int e = e0; e < e1; ++e) {
             const int j = col_s[e];
             float v[HP];
@@ -1591,7 +1595,7 @@ __global__ void __launch_bounds__(kGbThreads, 3) gnn_bwd_gather_kernel(const Gnn
         float ds_sum = 0.f;
 #pragma unroll
         for (int c = 0; c < HP; ++c) sg[c] = 0.f;
-#pragma unroll 2
+#pragma unroll(kGbEdgeUnroll)
         for (int e = e0; e < e1; ++e) {
           const int j = col_s[e];
           float v[HP];
@@ -1624,7 +1628,7 @@ __global__ void __launch_bounds__(kGbThreads, 3) gnn_bwd_gather_kernel(const Gnn
 #pragma unroll
         for (int c = 0; c < HP; ++c) sg[c] = 0.f;
         float ds_sum = 0.f;
-#pragma unroll 2
+#pragma unroll(kGbEdgeUnroll)
         for (int e = e0; e < e1; ++e) {
           const int ti = col_s[e], r = rev_s[e];
           const float alpha = es_s[r], ds = eda_s[r];

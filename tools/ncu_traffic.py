@@ -1,7 +1,7 @@
 """Summarise an `ncu --set full` report: per kernel (name up to the template arguments) launches, time,
 DRAM bytes, L2->SM bytes, tensor-pipe activity.  Usage: python tools/ncu_traffic.py report.ncu-rep|raw_page.csv [key]
 With a key (e.g. c3_b1024_tf32) the per-kernel DRAM bytes per launch are merged into
-profiles/r1_traffic.json, which bench.py reads for `roofline.traffic`."""
+profiles/r2_traffic.json, which bench.py reads for `roofline.traffic`."""
 import collections, csv, io, json, os, re, subprocess, sys
 
 rep = sys.argv[1]
@@ -45,7 +45,7 @@ for k, a in agg.items():
     print(f"| `{k}` | {a['n']} | {a['us']:.1f} | {a['rd']/1e6:.1f} | {a['wr']/1e6:.1f} | {gbs:.0f} | {a['l2sm']/1e6:.1f} | "
           f"{a['tensor']/a['n']:.1f} | {a['ipc']/a['n']:.1f} |")
 if len(sys.argv) > 2:
-    path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "profiles", "r1_traffic.json")
+    path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "profiles", "r2_traffic.json")
     try:
         table = json.load(open(path))
     except (OSError, ValueError):
