@@ -404,7 +404,8 @@ def run_ours(args):
                 kern = {"tf32": "gemm_tc_kernel", "tf32x3": "gemm_tc_kernel", "fp32": "gemm_simt_kernel"}[args.precision]
                 mode = {"tf32": "tcgen05 TF32", "tf32x3": "tcgen05 3xTF32", "fp32": "fp32 FMA"}[args.precision]
                 return f"{kern}{role} {name[name.index('['):]} ({mode})"
-            return {"gnn_bwd": "gnn_bwd_tc_kernel", "gnn_fwd": "gnn_fwd_tc_kernel", "adam_soft_update": "adam_soft_dev_kernel",
+            return {"gnn_bwd": "gnn_bwd_gather_kernel + gnn_wgrad_kernel" if w["n_max"] <= 128 else "gnn_bwd_tc_kernel / gnn_bwd_kernel",
+                    "gnn_fwd": "gnn_fwd_tc_kernel", "adam_soft_update": "adam_soft_dev_kernel",
                     "pack_csr": "pack_csr kernels"}.get(base, base + "_kernel") + (name[name.index("["):] if "[" in name else "")
         top_op = max(per_op, key=per_op.get)
         top_ms = per_op[top_op]
