@@ -668,8 +668,9 @@ def main():
                     help="c3 (default): full DDPG update, the fwd+bwd+Adam step BASELINE.json's metric names; "
                          "c4: the same update on 1000-node topologies; c2 / c5: embedder + actor inference")
     ap.add_argument("--batch", type=int, default=0)
-    ap.add_argument("--bucket-allreduce", action="store_true",
-                    help="N > 1: all-reduce every dense layer's gradient block on the side stream behind the backward")
+    ap.add_argument("--bucket-allreduce", nargs="?", const=True, default=False, choices=[True, "mlp", "layer"],
+                    help="N > 1: all-reduce the dense-layer gradient blocks on the side stream behind the embedder "
+                         "backward: per layer (default when given) or as one block ('mlp')")
     ap.add_argument("--sm-reserve", type=int, default=8,
                     help="N > 1: SMs the embedder backward leaves free for the concurrent NCCL kernels")
     ap.add_argument("--no-fork", dest="fork", action="store_false",

@@ -13,12 +13,19 @@ struct AdamScalars {
   float lr_over_bc1, sqrt_bc2, beta1, beta2, eps, tau;
 };
 
+// target <- tau*p + (1-tau)*target with a fixed operation order (one product, one fused multiply-add): the
+// fused Adam pass and the stand-alone soft update must agree bit for bit, because data-parallel ranks with a
+// sharded optimizer compute the same target element through either of them.
+__device__ __forceinline__ float soft_mix(float tau, float p, float t) {
+  return __fmaf_rn(tau, p, __fmul_rn(1.f - tau, t));
+}
+
 __device__ __forceinline__ void adam_one(float& p, float g, float& m, float& v, float* tgt, const AdamScalars& s) {
   m = s.beta1 * m + (1.f - s.beta1) * g;
   v = s.beta2 * v + (1.f - s.beta2) * g * g;
   const float denom = sqrtf(v) / s.sqrt_bc2 + s.eps;
   p = p - s.lr_over_bc1 * (m / denom);
-  if (tgt) *tgt = s.tau * p + (1.f - s.tau) * (*tgt);
+  if (tgt) *tgt = soft_mix(s.tau, p, *tgt);
 }
 
 __global__ void __launch_bounds__(256) adam_soft_kernel(float* __restrict__ p, const float* __restrict__ g,
@@ -146,6 +153,39 @@ extern "C" int gsc_mul_gate(const float* x, int64_t ldx, const float* mul, int64
   if (blocks > 8LL * kNumSMs) blocks = 8LL * kNumSMs;
   mul_gate_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(x, ldx, mul, ld_mul, gate, ld_gate, M, N, out, ldo);
   GSC_LAUNCH_CHECK("mul_gate_kernel");
+  return GSC_OK;
+}
+
+// target <- tau*p + (1-tau)*target over a flat range (the soft update alone: data-parallel ranks with a
+// sharded optimizer apply it to the parameter slices they received from the other ranks)
+__global__ void __launch_bounds__(256) soft_update_kernel(const float* __restrict__ p, float* __restrict__ tgt,
+                                                          int64_t n, float tau) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (((reinterpret_cast<uintptr_t>(p) | reinterpret_cast<uintptr_t>(tgt)) & 15) == 0) {
+    const int64_t n4 = n >> 2;
+    const float4* p4 = reinterpret_cast<const float4*>(p);
+    float4* t4 = reinterpret_cast<float4*>(tgt);
+    for (int64_t i = tid; i < n4; i += stride) {
+      const float4 pp = p4[i];
+      float4 tt = t4[i];
+      tt.x = soft_mix(tau, pp.x, tt.x); tt.y = soft_mix(tau, pp.y, tt.y);
+      tt.z = soft_mix(tau, pp.z, tt.z); tt.w = soft_mix(tau, pp.w, tt.w);
+      t4[i] = tt;
+    }
+    for (int64_t i = (n4 << 2) + tid; i < n; i += stride) tgt[i] = soft_mix(tau, p[i], tgt[i]);
+  } else {
+    for (int64_t i = tid; i < n; i += stride) tgt[i] = soft_mix(tau, p[i], tgt[i]);
+  }
+}
+
+extern "C" int gsc_soft_update(const float* p, float* target, int64_t n, float tau, void* stream) {
+  GSC_REQUIRE(n >= 0 && (n == 0 || (p && target)), "gsc_soft_update: bad arguments");
+  if (n == 0) return GSC_OK;
+  int64_t blocks = ceil_div(n, 256 * 4);
+  if (blocks > 8 * kNumSMs) blocks = 8 * kNumSMs;
+  soft_update_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(p, target, n, tau);
+  GSC_LAUNCH_CHECK("soft_update_kernel");
   return GSC_OK;
 }
 

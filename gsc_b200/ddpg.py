@@ -60,7 +60,8 @@ class DDPGUpdater:
         # Per-layer all-reduces behind the embedder backward (see _bucketed) pay on 2 GPUs (1.92 -> 1.85 ms)
         # but not on 8 (2.04 -> 2.10 ms: six collectives instead of two, and they compete with the
         # backward for SMs), so one all-reduce per network after its backward is the default.
-        self.bucket_allreduce = bool(bucket_allreduce)
+        # "mlp": one all-reduce for the whole dense-layer block (instead of one per layer)
+        self.bucket_allreduce = bucket_allreduce if bucket_allreduce == "mlp" else bool(bucket_allreduce)
         if self._bucketed():
             ops.set_sm_reserve(sm_reserve)      # room for the per-layer all-reduces beside the embedder backward
         self._neg = None
@@ -83,6 +84,8 @@ class DDPGUpdater:
         if not self._bucketed():
             return None
         _, layers = net.grad_regions()
+        if self.bucket_allreduce == "mlp":          # layers are visited last to first: after layer 0 all are complete
+            return lambda i: allreduce_flat(g[layers[0][0]:layers[-1][1]], self.pg) if i == 0 else None
         return lambda i: allreduce_flat(g[layers[i][0]:layers[i][1]], self.pg)
 
     def _optimizer_step(self, net, target, g, gs, m, v, step_dev) -> None:
@@ -101,7 +104,10 @@ class DDPGUpdater:
         ops.adam_soft_update_dev(net.flat[lo:hi], gs, m, v, target.flat[lo:hi], self.lr, self.betas[0],
                                  self.betas[1], self.eps, step_dev, self.tau)
         all_gather_flat(net.flat, self.pg)
-        all_gather_flat(target.flat, self.pg)
+        # the other ranks' slices of the target network: soft update applied locally to the online weights
+        # just received (12 B/param of HBM traffic) instead of a second all-gather over the wire
+        ops.soft_update(net.flat[:lo], target.flat[:lo], self.tau)
+        ops.soft_update(net.flat[hi:], target.flat[hi:], self.tau)
 
     def update_critic(self, nxt: GraphBatch, cur: GraphBatch, dones, rewards, actions):
         """reference _update_critic (simple_ddpg.py:204-219)."""

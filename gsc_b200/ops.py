@@ -482,6 +482,17 @@ def adam_soft_update_dev(p, g, m, v, target, lr, beta1, beta2, eps, step_dev: to
     _count(2)
 
 
+def soft_update(p: torch.Tensor, target: torch.Tensor, tau: float):
+    """target <- tau * p + (1 - tau) * target over flat contiguous buffers."""
+    if not (p.is_contiguous() and target.is_contiguous()) or p.numel() != target.numel():
+        raise _lib.GscError("soft_update needs flat contiguous buffers of equal length")
+    if p.numel() == 0:
+        return
+    with _Timed(f"soft_update[{int(p.numel())}]"):
+        check(_lib.load().gsc_soft_update(_ptr(p), _ptr(target), int(p.numel()), tau, _stream()), "gsc_soft_update")
+    _count(1)
+
+
 def actor_head(y: torch.Tensor, group: int, noise: Optional[torch.Tensor] = None,
                low: float = 0.0, high: float = 1.0) -> torch.Tensor:
     """post_process_actions (and, with ``noise``, the exploration step) -> fp64 [R, A]."""

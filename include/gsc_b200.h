@@ -227,6 +227,11 @@ int gsc_adam_soft_update_dev(float* p, const float* g, float* m, float* v, float
                              float lr, float beta1, float beta2, float eps, int64_t* step_dev, float tau,
                              void* stream);
 
+/* The soft target update alone, target <- tau*p + (1-tau)*target (reference
+ * src/rlsp/agents/simple_ddpg.py:229-234), over a flat range: what a data-parallel rank with a sharded
+ * optimizer applies to the parameter slices it received from the other ranks. */
+int gsc_soft_update(const float* p, float* target, int64_t n, float tau, void* stream);
+
 /* ---- actor head ---------------------------------------------------------------------------
  * post_process_actions + normalize_scheduling_probabilities (reference
  * src/rlsp/agents/simple_ddpg.py:374-395, 338-372), applied to R action vectors of A values each,
