@@ -71,8 +71,10 @@ struct TcParams {
   int kb_total, kb_per_split, splits, tiles_m, tiles_n;
   int stages;             // operand ring depth: kTcEpiStages with the TMA epilogue, kTcMaxStages without
   int lo_stages;          // 3xTF32: depth of the lo ring (0 otherwise)
-  int ebuf_slot;          // first 32 KB slot of the epilogue tile
-  int bar_slot;           // slot index where the barriers start (= total slots)
+  int lo_off, lo_slot;    // 3xTF32: byte offset of the lo ring and bytes per slot
+  int ebuf_off;           // byte offset of the epilogue tile
+  int bar_off;            // byte offset of the barriers
+  int a_tmem;             // 3xTF32, K-major A: the A operand (hi and lo images) lives in tensor memory
   int dbg;                // GSC_TC_DBG experiment bits: 1 no MMAs, 2 no TMA loads, 4 no epilogue body, 8 no conversion
   int epi_tma;            // 1: output tile leaves through shared memory + TMA store (coalesced, asynchronous)
   int epi_kind;           // operand streamed in by TMA for the epilogue: 0 none, 1 mul, 2 gate
@@ -178,9 +180,12 @@ gemm_tc_kernel(const __grid_constant__ TcParams p, const __grid_constant__ CUten
                const __grid_constant__ CUtensorMap mapE) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;       // 1024 B: swizzle-128B atoms
-  const uint32_t ebuf = smem_base + p.ebuf_slot * kTcStageBytes;           // epilogue tile, 4 x [128 rows x 128 B]
-  const uint32_t lo_base = smem_base + p.stages * kTcStageBytes;           // 3xTF32: lo ring behind the raw ring
-  const uint32_t bar_base = smem_base + p.bar_slot * kTcStageBytes;
+  const uint32_t ebuf = smem_base + p.ebuf_off;                            // epilogue tile, 4 x [128 rows x 128 B]
+  const uint32_t lo_base = smem_base + p.lo_off;                           // 3xTF32: lo ring behind the raw ring
+  const uint32_t bar_base = smem_base + p.bar_off;
+  constexpr bool kATm = X3 && !A_MN;                                       // A-from-TMEM variant exists for K-major A
+  const bool a_tmem = kATm && p.a_tmem;
+  const uint32_t tmem_cols = a_tmem ? 512u : (uint32_t)kTmemCols;
   constexpr int kTcStages = kTcBarSlots;                                   // barrier slots per ring
   const int num_stages = p.stages;
   // barriers: full[S], empty[S], lo_full[4], lo_empty[4], tmem_full[2], tmem_empty[2], epilogue
@@ -210,7 +215,7 @@ gemm_tc_kernel(const __grid_constant__ TcParams p, const __grid_constant__ CUten
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 0) {   // one warp allocates TMEM (256 columns) and later frees it
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(kTmemCols));
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(tmem_cols));
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
   }
   tc_fence_before();
@@ -284,8 +289,10 @@ gemm_tc_kernel(const __grid_constant__ TcParams p, const __grid_constant__ CUten
       constexpr uint32_t kStageW = kTcStageBytes >> 4, kOperandW = (kTcBM * kTcBK * 4) >> 4;
       const uint32_t a_raw0 = (smem_base >> 4) | ((A_MN ? 256u : 1u) << 16);
       const uint32_t b_raw0 = ((smem_base >> 4) + kOperandW) | ((B_MN ? 256u : 1u) << 16);
+      const uint32_t kLoW = (uint32_t)p.lo_slot >> 4;
       const uint32_t a_lo0 = (lo_base >> 4) | ((A_MN ? 256u : 1u) << 16);
-      const uint32_t b_lo0 = ((lo_base >> 4) + kOperandW) | ((B_MN ? 256u : 1u) << 16);
+      const uint32_t b_lo0 = ((lo_base >> 4) + (a_tmem ? 0u : kOperandW)) | ((B_MN ? 256u : 1u) << 16);
+      const uint32_t tmem_a0 = tmem_base + (uint32_t)kTmemCols;    // A ring in tensor memory: [lo_stages][hi 32 | lo 32] columns
       int stage = 0, lstage = 0;
       uint32_t phase = 0, lphase = 0;
       int iter = 0;
@@ -301,8 +308,18 @@ gemm_tc_kernel(const __grid_constant__ TcParams p, const __grid_constant__ CUten
           if (X3) mbar_wait(lofull_bar(lstage), lphase);     // hi (in place) and lo images are ready
           else mbar_wait(full_bar(stage), phase);
           const uint32_t da = a_raw0 + stage * kStageW, db = b_raw0 + stage * kStageW;
-          const uint32_t la = a_lo0 + lstage * kStageW, lb = b_lo0 + lstage * kStageW;
-          if (!(p.dbg & 1)) {
+          const uint32_t la = a_lo0 + lstage * kLoW, lb = b_lo0 + lstage * kLoW;
+          if (kATm && a_tmem) {
+            tc_fence_after();                              // the A images were written with tcgen05.st by other warps
+            const uint32_t ta = tmem_a0 + (uint32_t)(lstage * 2 * kTcBK);
+#pragma unroll
+            for (int j = 0; j < kTcBK / 8; ++j) {
+              tc_mma_tf32_ts(tmem_d, ta + 8 * j, db + j * b_step, b_hi, idesc, acc);
+              acc = 1;
+              tc_mma_tf32_ts(tmem_d, ta + 8 * j, lb + j * b_step, b_hi, idesc, 1u);
+              tc_mma_tf32_ts(tmem_d, ta + kTcBK + 8 * j, db + j * b_step, b_hi, idesc, 1u);
+            }
+          } else if (!(p.dbg & 1)) {
 #pragma unroll
             for (int j = 0; j < kTcBK / 8; ++j) {
               tc_mma_tf32_w(tmem_d, da + j * a_step, a_hi, db + j * b_step, b_hi, idesc, acc);
@@ -345,8 +362,45 @@ gemm_tc_kernel(const __grid_constant__ TcParams p, const __grid_constant__ CUten
         mbar_wait(full_bar(stage), phase);                       // TMA bytes have landed
         mbar_wait(loempty_bar(lstage), lphase ^ 1u);             // the MMAs that read this lo slot retired
         const uint32_t src = smem_base + stage * kTcStageBytes + ct * 16;
-        const uint32_t dst = lo_base + lstage * kTcStageBytes + ct * 16;
-        if (!(p.dbg & 8)) {
+        const uint32_t dst = lo_base + lstage * p.lo_slot + ct * 16;
+        if (kATm && a_tmem) {
+          // A rows -> tensor memory.  Converter warp q may access TMEM lanes 32q..32q+31, so thread (q, lane)
+          // takes row 32q + lane of the staged K-major tile (eight swizzled 16-byte chunks), writes
+          // hi = trunc(x) to 32 columns and lo = x - hi to the next 32.  B: lo image into the lo ring.
+          tc_fence_after();                                      // TMEM slot freed by retired MMAs (mbarrier observed)
+          const int q = warp - kTcEpiWarps, r = 32 * q + lane;
+          const uint32_t rowp = smem_base + stage * kTcStageBytes + r * 128;
+          uint32_t x[32];
+#pragma unroll
+          for (int c = 0; c < 8; ++c)
+            asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                         : "=r"(x[4 * c]), "=r"(x[4 * c + 1]), "=r"(x[4 * c + 2]), "=r"(x[4 * c + 3])
+                         : "r"(rowp + (uint32_t)((c ^ (r & 7)) << 4)));
+          uint32_t y[32];
+#pragma unroll
+          for (int e = 0; e < 32; ++e) y[e] = x[e] & 0xffffe000u;
+          const uint32_t ta = tmem_base + (uint32_t)kTmemCols + (uint32_t)(lstage * 2 * kTcBK) + ((uint32_t)(32 * q) << 16);
+          tc_st32(ta, y);
+#pragma unroll
+          for (int e = 0; e < 32; ++e) y[e] = __float_as_uint(__uint_as_float(x[e]) - __uint_as_float(y[e]));
+          tc_st32(ta + kTcBK, y);
+          const uint32_t srcb = src + kTcBM * kTcBK * 4;
+          uint32_t v[8][4];
+#pragma unroll
+          for (int u = 0; u < 8; ++u)
+            asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                         : "=r"(v[u][0]), "=r"(v[u][1]), "=r"(v[u][2]), "=r"(v[u][3]) : "r"(srcb + u * 2048));
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            uint32_t lo[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e)
+              lo[e] = __float_as_uint(__uint_as_float(v[u][e]) - __uint_as_float(v[u][e] & 0xffffe000u));
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst + u * 2048), "r"(lo[0]), "r"(lo[1]), "r"(lo[2]), "r"(lo[3]) : "memory");
+          }
+          tc_st_wait();
+          tc_fence_before();
+        } else if (!(p.dbg & 8)) {
 #pragma unroll
           for (int i0 = 0; i0 < kIters; i0 += 8) {               // eight 128-bit loads in flight per thread
             uint32_t v[8][4];
@@ -546,7 +600,7 @@ gemm_tc_kernel(const __grid_constant__ TcParams p, const __grid_constant__ CUten
   __syncthreads();
   if (warp == 0) {
     tc_fence_after();
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kTmemCols));
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(tmem_cols));
   }
 }
 
@@ -674,16 +728,30 @@ int gemm_tc_launch(const gsc_gemm_args* a, int64_t M, int64_t N, float* C, int64
       p.epi_tma = 1; p.epi_kind = kind;
     }
   }
-  if (x3) {
+  static const int atm_env = [] { const char* e = getenv("GSC_X3_ATMEM"); return (e && e[0] == '0') ? 0 : 1; }();
+  p.a_tmem = (x3 && !a_mn && atm_env) ? 1 : 0;
+  if (p.a_tmem) {
+    // A operand in tensor memory: the lo ring holds B only (16 KB slots), so the raw ring can be deeper
+    p.stages = p.epi_tma ? 4 : 5;
+    p.lo_stages = p.epi_tma ? 2 : 4;
+    p.lo_slot = kTcBN * kTcBK * 4;
+    p.lo_off = p.stages * kTcStageBytes;
+    p.ebuf_off = p.lo_off + p.lo_stages * p.lo_slot;
+    p.bar_off = kTcX3Slots * kTcStageBytes;
+  } else if (x3) {
     p.stages = p.epi_tma ? kTcX3RawEpi : kTcX3RawSplit;
     p.lo_stages = p.epi_tma ? kTcX3LoEpi : kTcX3LoSplit;
-    p.ebuf_slot = kTcX3RawEpi + kTcX3LoEpi;
-    p.bar_slot = kTcX3Slots;
+    p.lo_slot = kTcStageBytes;
+    p.lo_off = p.stages * kTcStageBytes;
+    p.ebuf_off = (kTcX3RawEpi + kTcX3LoEpi) * kTcStageBytes;
+    p.bar_off = kTcX3Slots * kTcStageBytes;
   } else {
     p.stages = p.epi_tma ? kTcEpiStages : kTcMaxStages;
     p.lo_stages = 0;
-    p.ebuf_slot = kTcEpiStages;
-    p.bar_slot = kTcMaxStages;
+    p.lo_slot = 0;
+    p.lo_off = p.stages * kTcStageBytes;
+    p.ebuf_off = kTcEpiStages * kTcStageBytes;
+    p.bar_off = kTcMaxStages * kTcStageBytes;
   }
   { const char* e = getenv("GSC_TC_DBG"); p.dbg = e ? atoi(e) : 0; }
   const int64_t work = tiles * p.splits;
