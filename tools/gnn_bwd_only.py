@@ -14,4 +14,14 @@ d_emb = torch.randn_like(emb)
 for it in range(3):
     ops.gnn_embed_bwd(gb.x, rp, col, gp, B, gb.max_nodes, gnn, 22, 2, 2, saved, d_emb, pack_stats=gb.pack_stats())
 torch.cuda.synchronize()
-print("ok")
+e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+e0.record()
+for it in range(10):
+    ops.gnn_embed_bwd(gb.x, rp, col, gp, B, gb.max_nodes, gnn, 22, 2, 2, saved, d_emb, pack_stats=gb.pack_stats())
+e1.record(); torch.cuda.synchronize()
+print("gnn_bwd us/call", e0.elapsed_time(e1) * 100)
+e0.record()
+for it in range(10):
+    ops.gnn_embed_fwd(gb.x, rp, col, gp, B, gb.max_nodes, gnn, 22, 2, 2, save=True)
+e1.record(); torch.cuda.synchronize()
+print("gnn_fwd us/call", e0.elapsed_time(e1) * 100)
