@@ -1291,10 +1291,14 @@ __global__ void __launch_bounds__(kGnnThreads, 1) gnn_bwd_tc_kernel(const GnnArg
 // for occupancy instead of tensor cores: the edge passes are chains of dependent shared-memory
 // gathers and short FMA sequences, i.e. latency, and what hides latency is more resident warps.
 //   * CTA = 128 threads = 128 node slots (one thread owns one node for a whole chunk of graphs);
-//   * shared memory per CTA: three row arrays (xl, xr, g; the gradients d_xl / d_xr / d_h stay in the
-//     owner's registers), the per-edge (alpha, ds) pair, the chunk's CSR with its reverse index and
-//     ONE c-major copy of every conv's weights -- ~60 KB, so three CTAs (12 warps, 170 registers
-//     per thread) share an SM where the tcgen05 variant, with its operand images, fits one;
+//   * shared memory per CTA: two row arrays (xl, gathered by the target pass; g = d_out/deg, gathered by
+//     the source pass), per edge the (alpha, ds) pair and ONE WORD OF SIGN BITS -- the LeakyReLU branch of
+//     every channel of u = xl_j + xr_i, which is all that the two gradient loops need of xr and xl -- the
+//     chunk's CSR with its reverse index and one c-major copy of every conv's weights: ~50 KB, so FOUR
+//     CTAs (16 warps, 128 registers per thread) share an SM where the tcgen05 variant, with its operand
+//     images, fits one; 1024 graphs then take two rounds of 592 resident CTAs instead of three of 444;
+//   * the d_xl / d_xr / d_h gradients and the own xr row stay in the owner's registers; the MMA operand
+//     rows are staged in the row arrays themselves, in the window where nobody gathers from them;
 //   * the node transforms ([32 nodes of a warp] x [HP] x [2HP] and back) run as warp-level 3xTF32
 //     mma.sync m16n8k8 through a small warp-private tile: ~110 instructions per warp instead of the
 //     ~1400 of the FMA form, and none of the operand staging, TMEM round trips and CTA barriers that
@@ -1308,18 +1312,16 @@ __global__ void __launch_bounds__(kGnnThreads, 1) gnn_bwd_tc_kernel(const GnnArg
 constexpr int kGbEdgeUnroll = GSC_EDGE_UNROLL;   // edge loops of the gather kernel
 constexpr int kGbThreads = 128;
 constexpr int kGbEdgesPerNode = 6;       // per-edge arrays per node slot (self-loops included)
+constexpr int kGbCtasPerSm = 4;          // resident CTAs per SM the shared-memory layout and register budget are sized for
 
 template <int HP>
 struct GbL {
-  static constexpr int kConvFloats = 2 * HP * HP + 4 * HP;     // Wl[c][k], Wr[c][k], bl, br, att, (pad)
+  static constexpr int kConvFloats = 2 * HP * HP + 4 * HP;     // Wl[c][k], Wr[c][k], bl, br, att, 0.4 att
   static constexpr int kSlotFloats = (kGbThreads / 32) * 2 * HP;   // per-warp d_att | d_bias sums, per conv
-  static constexpr int kTS = HP + 4;                           // row stride of the warp tiles (conflict-free fragments)
-  static constexpr int kTileFloats = 32 * kTS;                 // one [32 node slots][HP] tile per warp
   __host__ __device__ static constexpr size_t bytes(int num_convs) {
-    return (size_t)num_convs * (kConvFloats + kSlotFloats) * 4 + 3 * (size_t)kGbThreads * HP * 4 +
-           (size_t)(kGbThreads / 32) * kTileFloats * 4 +
-           (size_t)kGbThreads * 8 /*pq*/ + ((size_t)kGbThreads + 4) * 4 /*rp*/ +
-           (size_t)kGbEdgesPerNode * kGbThreads * (4 + 4 + 2 + 2) + (size_t)kGbThreads * 2 /*perm*/ + 64 * 4;
+    return (size_t)num_convs * (kConvFloats + kSlotFloats) * 4 + 2 * (size_t)kGbThreads * HP * 4 /*xl, g rows*/ +
+           (size_t)kGbThreads * 4 /*p*/ + ((size_t)kGbThreads + 4) * 4 /*rp*/ +
+           (size_t)kGbEdgesPerNode * kGbThreads * (4 + 4 + 4 + 2 + 2) + (size_t)kGbThreads * 2 /*perm*/ + 64 * 4;
   }
 };
 
@@ -1370,30 +1372,28 @@ __device__ __forceinline__ void warp_gemm_3xtf32(float (&acc)[2][NT][4], const f
 }
 
 template <int HP>
-__global__ void __launch_bounds__(kGbThreads, 3) gnn_bwd_gather_kernel(const GnnArgs p) {
+__global__ void __launch_bounds__(kGbThreads, 4) gnn_bwd_gather_kernel(const GnnArgs p) {
   using L = GbL<HP>;
   constexpr int cap = kGbThreads, emax = kGbEdgesPerNode * kGbThreads;
   extern __shared__ float4 smem4[];
   float* wsm = reinterpret_cast<float*>(smem4);                     // [num_convs][kConvFloats]
   float* slot_s = wsm + p.num_convs * L::kConvFloats;               // [num_convs][warps][2HP]
-  float* xl_s = slot_s + p.num_convs * L::kSlotFloats;              // [cap][HP]
-  float* xr_s = xl_s + cap * HP;
-  float* g_s = xr_s + cap * HP;
-  float* tile_s = g_s + cap * HP;                                   // [warps][32][kTS] warp-private MMA operand tiles
-  float2* pq_s = reinterpret_cast<float2*>(tile_s + (kGbThreads / 32) * L::kTileFloats);   // [cap] 0.6 att.xl_j, 0.6 att.xr_i
-  int* rp_s = reinterpret_cast<int*>(pq_s + cap);                   // [cap + 4]
+  float* xl_s = slot_s + p.num_convs * L::kSlotFloats;              // [cap][HP] xl rows by node; step 4: MMA staging by slot
+  float* g_s = xl_s + cap * HP;                                     // [cap][HP] g rows by node; step 1: MMA staging by slot
+  float* p_s = g_s + cap * HP;                                      // [cap] 0.6 att.xl_j
+  int* rp_s = reinterpret_cast<int*>(p_s + cap);                    // [cap + 4]
   float* es_s = reinterpret_cast<float*>(rp_s + cap + 4);           // [emax] score, then alpha
   float* eda_s = es_s + emax;                                       // [emax] g_i.xl_j, then d_score
-  uint16_t* col_s = reinterpret_cast<uint16_t*>(eda_s + emax);      // [emax]
+  uint32_t* sb_s = reinterpret_cast<uint32_t*>(eda_s + emax);       // [emax] bit c: sign of xl_j,c + xr_i,c (LeakyReLU branch)
+  uint16_t* col_s = reinterpret_cast<uint16_t*>(sb_s + emax);       // [emax]
   uint16_t* rev_s = col_s + emax;                                   // [emax]
   uint16_t* perm_s = rev_s + emax;                                  // [cap]
   int* hist_s = reinterpret_cast<int*>(perm_s + cap);               // [64]
   if (p.stats == nullptr || p.stats[3] != 0 || p.flags[0] != 0) return;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  float* tile = tile_s + warp * L::kTileFloats;
   const int gid = lane >> 2, tig = lane & 3;
 
-  // ---- weights, c-major and zero padded: Wl[c][k] at wsm[c*HP + k], Wr behind it, then bl, br, att ----
+  // ---- weights, c-major and zero padded: Wl[c][k] at wsm[c*HP + k], Wr behind it, then bl, br, att, 0.4 att ----
   for (int cv = 0; cv < p.num_convs; ++cv) {
     const int in = cv == 0 ? p.in_dim : p.H, H = p.H;
     const float* src = p.params + conv_param_offset(cv, p.in_dim, p.H);
@@ -1412,7 +1412,7 @@ __global__ void __launch_bounds__(kGbThreads, 3) gnn_bwd_gather_kernel(const Gnn
       w[2 * HP * HP + t] = ok ? bl[t] : 0.f;
       w[2 * HP * HP + HP + t] = ok ? br[t] : 0.f;
       w[2 * HP * HP + 2 * HP + t] = ok ? att[t] : 0.f;
-      w[2 * HP * HP + 3 * HP + t] = 0.f;
+      w[2 * HP * HP + 3 * HP + t] = ok ? 0.4f * att[t] : 0.f;
     }
     for (int t = tid; t < L::kSlotFloats; t += kGbThreads) slot_s[cv * L::kSlotFloats + t] = 0.f;
   }
@@ -1482,10 +1482,14 @@ __global__ void __launch_bounds__(kGbThreads, 3) gnn_bwd_gather_kernel(const Gnn
       const float* w = wsm + cv * L::kConvFloats;
       const float* vec = w + 2 * HP * HP;                // bl | br | att
       float* slot = slot_s + cv * L::kSlotFloats + warp * 2 * HP;
-      // ---- 1. recompute [xl | xr] = h_in [Wl ; Wr]^T on the warp's 32 node slots (3xTF32 mma.sync):
-      //         own input row -> warp tile -> A fragments; B fragments straight from the c-major weights;
-      //         the accumulator fragments (+ bias) go to the xl / xr rows of their nodes ----
+      // ---- 1. recompute [xl | xr] = h_in [Wl ; Wr]^T on the warp's 32 node slots (3xTF32 mma.sync).  The own
+      //         input row is staged in this warp's slot rows of g_s (nobody reads g rows between the last
+      //         barrier and the next one); B fragments come straight from the c-major weights; the xl
+      //         fragments (+ bias) go to the xl rows of their nodes, the xr fragments return to their owner
+      //         through the same slot rows ----
+      float xr[HP];
       {
+        float* stage_rows = g_s + warp * 32 * HP;
         {
           float hin[HP];
 #pragma unroll
@@ -1498,7 +1502,7 @@ __global__ void __launch_bounds__(kGbThreads, 3) gnn_bwd_gather_kernel(const Gnn
               load_row<HP>(p.saved + ((size_t)(a - 1) * p.Nt + node) * HP, hin);
             }
           }
-          store_row<HP>(tile + lane * L::kTS, hin);
+          store_row<HP>(stage_rows + lane * HP, hin);
         }
         __syncwarp();
         float acc[2][2 * HP / 8][4];
@@ -1508,31 +1512,38 @@ __global__ void __launch_bounds__(kGbThreads, 3) gnn_bwd_gather_kernel(const Gnn
           for (int nt = 0; nt < 2 * HP / 8; ++nt)
 #pragma unroll
             for (int q = 0; q < 4; ++q) acc[mt][nt][q] = 0.f;
-        if (a == 0 && p.in_dim <= 8) warp_gemm_3xtf32<1, 2 * HP / 8, L::kTS>(acc, tile, w, HP, 1, lane);
-        else warp_gemm_3xtf32<HP / 8, 2 * HP / 8, L::kTS>(acc, tile, w, HP, 1, lane);
+        if (a == 0 && p.in_dim <= 8) warp_gemm_3xtf32<1, 2 * HP / 8, HP>(acc, stage_rows, w, HP, 1, lane);
+        else warp_gemm_3xtf32<HP / 8, 2 * HP / 8, HP>(acc, stage_rows, w, HP, 1, lane);
+        __syncwarp();                                    // every lane is done reading the staged rows
         // rows (16 mt + gid) and (+ 8), channels 8 nt + 2 tig (+ 1): nt < HP/8 is xl, the rest xr
 #pragma unroll
         for (int mt = 0; mt < 2; ++mt)
 #pragma unroll
           for (int hrow = 0; hrow < 2; ++hrow) {
-            const int slot_i = warp * 32 + 16 * mt + 8 * hrow + gid;
+            const int sl = 16 * mt + 8 * hrow + gid;
+            const int slot_i = warp * 32 + sl;
             const bool live = slot_i < nc;
             const int ni = live ? perm_s[slot_i] : 0;
-            float pl = 0.f, pr = 0.f;
+            float pl = 0.f;
 #pragma unroll
             for (int nt = 0; nt < 2 * HP / 8; ++nt) {
               const int ch = (8 * nt + 2 * tig) % HP;
               const bool is_r = nt >= HP / 8;
-              const float b0 = vec[(is_r ? HP : 0) + ch], b1 = vec[(is_r ? HP : 0) + ch + 1];
-              const float v0 = acc[mt][nt][2 * hrow] + b0, v1 = acc[mt][nt][2 * hrow + 1] + b1;
-              const float d = fmaf(vec[2 * HP + ch], v0, vec[2 * HP + ch + 1] * v1);
-              if (is_r) pr += d; else pl += d;
-              if (live) *reinterpret_cast<float2*>((is_r ? xr_s : xl_s) + ni * HP + ch) = make_float2(v0, v1);
+              const float v0 = acc[mt][nt][2 * hrow] + vec[(is_r ? HP : 0) + ch];
+              const float v1 = acc[mt][nt][2 * hrow + 1] + vec[(is_r ? HP : 0) + ch + 1];
+              if (is_r) {
+                *reinterpret_cast<float2*>(stage_rows + sl * HP + ch) = make_float2(v0, v1);
+              } else {
+                pl = fmaf(vec[2 * HP + ch], v0, fmaf(vec[2 * HP + ch + 1], v1, pl));
+                if (live) *reinterpret_cast<float2*>(xl_s + ni * HP + ch) = make_float2(v0, v1);
+              }
             }
-            pl += __shfl_xor_sync(0xffffffffu, pl, 1); pr += __shfl_xor_sync(0xffffffffu, pr, 1);
-            pl += __shfl_xor_sync(0xffffffffu, pl, 2); pr += __shfl_xor_sync(0xffffffffu, pr, 2);
-            if (live && tig == 0) pq_s[ni] = make_float2(0.6f * pl, 0.6f * pr);     // score scalars p_j, q_i
+            pl += __shfl_xor_sync(0xffffffffu, pl, 1);
+            pl += __shfl_xor_sync(0xffffffffu, pl, 2);
+            if (live && tig == 0) p_s[ni] = 0.6f * pl;                  // score scalar p_j
           }
+        __syncwarp();
+        load_row<HP>(stage_rows + lane * HP, xr);
         // g = relu'(out) d_out / deg of the own node; conv-bias gradient
         float dbias[HP];
 #pragma unroll
@@ -1546,7 +1557,6 @@ __global__ void __launch_bounds__(kGbThreads, 3) gnn_bwd_gather_kernel(const Gnn
           }
 #pragma unroll
           for (int c = 0; c < HP; ++c) { dbias[c] = g[c]; g[c] *= inv_deg; }
-          store_row<HP>(g_s + i * HP, g);
         }
 #pragma unroll
         for (int c = 0; c < HP; ++c) {
@@ -1556,32 +1566,40 @@ __global__ void __launch_bounds__(kGbThreads, 3) gnn_bwd_gather_kernel(const Gnn
       }
       __syncthreads();
 
-      // ---- 2. target side (see gnn_bwd_tc_kernel 4T): alpha_e, ds_e of every in-edge, d_xr ----
-      float datt[HP], dxr[HP];
+      // ---- 2. target side: per in-edge score, g.xl_j and the LeakyReLU branch signs (one word per edge);
+      //         softmax statistics; alpha_e, ds_e left per edge; d_xr.  With lrelu(u) = (0.6 + 0.4 sgn u) u and
+      //         w_c = sum_e ds_e (0.6 + 0.4 sgn u_e,c):  d_xr = att o w_in,  d_xl = sum alpha g + att o w_out,
+      //         d_att = sum_i xr_i o w_in,i + sum_j xl_j o w_out,j ----
+      float datt[HP], vown[HP];
+      float* dxa = p.dx + ((size_t)a * p.Nt + node) * (2 * HP);      // [dxl | dxr] row of the own node (gnn_wgrad_kernel)
 #pragma unroll
-      for (int c = 0; c < HP; ++c) { datt[c] = 0.f; dxr[c] = 0.f; }
+      for (int c = 0; c < HP; ++c) { datt[c] = 0.f; vown[c] = 0.f; }
       if (active) {
-        float xr[HP], sg[HP];
-        load_row<HP>(xr_s + i * HP, xr);
-        const float q_i = pq_s[i].y;
+        store_row<HP>(g_s + i * HP, g);                  // read by the neighbours' source passes (after the next barrier)
+        float sg[HP];
+        const float q_i = 0.6f * dot4<HP>(*reinterpret_cast<const float(*)[HP]>(vec + 2 * HP), xr);
         float m = -INFINITY;
-        {
-          float b[HP];
-          load_row<HP>(vec + 2 * HP, b);
+#pragma unroll 1
+        for (int e = e0; e < e1; ++e) {
+          const int j = col_s[e];
+          float v[HP];
+          load_row<HP>(xl_s + j * HP, v);
+          float s0 = 0.f, s1 = 0.f, d0 = 0.f, d1 = 0.f;
+          uint32_t bits = 0;
 #pragma unroll
-          for (int c = 0; c < HP; ++c) b[c] *= 0.4f;
-          // scores and g.xl_j of every in-edge: iterations are independent (the softmax statistics
-          // are taken from shared memory afterwards), so the loads of the next edge overlap this one
-#pragma unroll(kGbEdgeUnroll)
-          for (int e = e0; e < e1; ++e) {
-            const int j = col_s[e];
-            float v[HP];
-            load_row<HP>(xl_s + j * HP, v);
-            const float sc_e = pq_s[j].x + q_i + abs_score<HP>(v, xr, b);
-            es_s[e] = sc_e;
-            eda_s[e] = dot4<HP>(g, v);
-            m = fmaxf(m, sc_e);
+          for (int c = 0; c < HP; c += 2) {
+            const float t0 = v[c] + xr[c], t1 = v[c + 1] + xr[c + 1];
+            s0 = fmaf(vec[3 * HP + c], fabsf(t0), s0);
+            s1 = fmaf(vec[3 * HP + c + 1], fabsf(t1), s1);
+            d0 = fmaf(g[c], v[c], d0);
+            d1 = fmaf(g[c + 1], v[c + 1], d1);
+            bits |= ((__float_as_uint(t0) >> 31) << c) | ((__float_as_uint(t1) >> 31) << (c + 1));
           }
+          const float sc_e = p_s[j] + q_i + (s0 + s1);
+          es_s[e] = sc_e;
+          eda_s[e] = d0 + d1;
+          sb_s[e] = bits;
+          m = fmaxf(m, sc_e);
         }
         float l = 0.f, dot = 0.f;
         for (int e = e0; e < e1; ++e) {
@@ -1595,73 +1613,79 @@ __global__ void __launch_bounds__(kGbThreads, 3) gnn_bwd_gather_kernel(const Gnn
         float ds_sum = 0.f;
 #pragma unroll
         for (int c = 0; c < HP; ++c) sg[c] = 0.f;
-#pragma unroll(kGbEdgeUnroll)
+#pragma unroll 1
         for (int e = e0; e < e1; ++e) {
-          const int j = col_s[e];
-          float v[HP];
-          load_row<HP>(xl_s + j * HP, v);
           const float alpha = es_s[e] * inv_l;
           const float ds = alpha * (eda_s[e] - dot);
+          const uint32_t bits = sb_s[e];
           es_s[e] = alpha;
           eda_s[e] = ds;
           ds_sum += ds;
 #pragma unroll
-          for (int c = 0; c < HP; ++c) sg[c] += signed_by(ds, v[c] + xr[c]);
+          for (int c = 0; c < HP; ++c)
+            sg[c] += __uint_as_float(__float_as_uint(ds) ^ ((bits << (31 - c)) & 0x80000000u));
         }
         const float base = 0.6f * ds_sum;
 #pragma unroll
         for (int c = 0; c < HP; ++c) {
           const float wv = fmaf(0.4f, sg[c], base);
           datt[c] = xr[c] * wv;
-          dxr[c] = vec[2 * HP + c] * wv;
+          sg[c] = vec[2 * HP + c] * wv;                  // d_xr
         }
+        store_row<HP>(dxa + HP, sg);                     // read back in step 4 (registers are short at 4 CTAs per SM)
+        load_row<HP>(xl_s + i * HP, vown);               // own xl row for the source pass: xl_s is free after the barrier
+      }
+#pragma unroll
+      for (int c = 0; c < HP; ++c) {                     // target half of d_att
+        const float sa = warp_sum(datt[c]);
+        if (lane == (c & 31)) slot[c] += sa;
+        datt[c] = 0.f;
       }
       __syncthreads();
 
-      // ---- 3. source side (4S): d_xl over the out-edges = this node's own CSR row of a symmetric graph ----
+      // ---- 3. source side: d_xl over the out-edges = this node's own CSR row of a symmetric graph; what the
+      //         target pass left for edge j -> i (alpha, ds, branch signs) is found through the reverse index ----
       float dxl[HP];
 #pragma unroll
       for (int c = 0; c < HP; ++c) dxl[c] = 0.f;
       if (active) {
-        float v[HP], sg[HP];
-        load_row<HP>(xl_s + i * HP, v);
+        float sg[HP];
 #pragma unroll
         for (int c = 0; c < HP; ++c) sg[c] = 0.f;
         float ds_sum = 0.f;
-#pragma unroll(kGbEdgeUnroll)
+#pragma unroll 1
         for (int e = e0; e < e1; ++e) {
           const int ti = col_s[e], r = rev_s[e];
           const float alpha = es_s[r], ds = eda_s[r];
-          float xr[HP], gi[HP];
-          load_row<HP>(xr_s + ti * HP, xr);
+          const uint32_t bits = sb_s[r];
+          float gi[HP];
           load_row<HP>(g_s + ti * HP, gi);
           ds_sum += ds;
 #pragma unroll
           for (int c = 0; c < HP; ++c) {
             dxl[c] = fmaf(alpha, gi[c], dxl[c]);
-            sg[c] += signed_by(ds, v[c] + xr[c]);
+            sg[c] += __uint_as_float(__float_as_uint(ds) ^ ((bits << (31 - c)) & 0x80000000u));
           }
         }
         const float base = 0.6f * ds_sum;
 #pragma unroll
         for (int c = 0; c < HP; ++c) {
           const float wv = fmaf(0.4f, sg[c], base);
-          datt[c] = fmaf(v[c], wv, datt[c]);
+          datt[c] = vown[c] * wv;
           dxl[c] = fmaf(vec[2 * HP + c], wv, dxl[c]);
         }
-        // [dxl | dxr] row -> workspace (gnn_wgrad_kernel)
-        float* dxa = p.dx + ((size_t)a * p.Nt + node) * (2 * HP);
         store_row<HP>(dxa, dxl);
-        store_row<HP>(dxa + HP, dxr);
       }
 #pragma unroll
       for (int c = 0; c < HP; ++c) {
         const float sa = warp_sum(datt[c]);
         if (lane == (c & 31)) slot[c] += sa;
       }
-      // ---- 4. d_h_in = d_xl Wl + d_xr Wr -> d_out of application a-1: two [32 x HP] x [HP x HP] products
-      //         through the warp tile (d_xl rows, then d_xr rows); the result rows return through the tile ----
+      // ---- 4. d_h_in = d_xl Wl + d_xr Wr -> d_out of application a-1: two [32 x HP] x [HP x HP] products; the
+      //         operand rows are staged in this warp's slot rows of xl_s (no xl row is read after the last
+      //         barrier), and the result rows return to their owners the same way ----
       if (a > 0) {
+        float* stage_rows = xl_s + warp * 32 * HP;
         float acc[2][HP / 8][4];
 #pragma unroll
         for (int mt = 0; mt < 2; ++mt)
@@ -1669,24 +1693,35 @@ __global__ void __launch_bounds__(kGbThreads, 3) gnn_bwd_gather_kernel(const Gnn
           for (int nt = 0; nt < HP / 8; ++nt)
 #pragma unroll
             for (int q = 0; q < 4; ++q) acc[mt][nt][q] = 0.f;
+        store_row<HP>(stage_rows + lane * HP, dxl);
         __syncwarp();
-        store_row<HP>(tile + lane * L::kTS, dxl);
+        warp_gemm_3xtf32<HP / 8, HP / 8, HP>(acc, stage_rows, w, 1, HP, lane);               // B(k = c, n) = Wl[c][n]
         __syncwarp();
-        warp_gemm_3xtf32<HP / 8, HP / 8, L::kTS>(acc, tile, w, 1, HP, lane);               // B(k = c, n) = Wl[c][n]
+        {
+          float dxr[HP];
+#pragma unroll
+          for (int c = 0; c < HP; ++c) dxr[c] = 0.f;
+          if (active) {                                  // this thread's own store of step 2, from L2
+#pragma unroll
+            for (int c4 = 0; c4 < HP / 4; ++c4) {
+              const float4 t4 = __ldcg(reinterpret_cast<const float4*>(dxa + HP) + c4);
+              dxr[4 * c4] = t4.x; dxr[4 * c4 + 1] = t4.y; dxr[4 * c4 + 2] = t4.z; dxr[4 * c4 + 3] = t4.w;
+            }
+          }
+          store_row<HP>(stage_rows + lane * HP, dxr);
+        }
         __syncwarp();
-        store_row<HP>(tile + lane * L::kTS, dxr);
-        __syncwarp();
-        warp_gemm_3xtf32<HP / 8, HP / 8, L::kTS>(acc, tile, w + HP * HP, 1, HP, lane);     // ... + d_xr Wr
+        warp_gemm_3xtf32<HP / 8, HP / 8, HP>(acc, stage_rows, w + HP * HP, 1, HP, lane);     // ... + d_xr Wr
         __syncwarp();
 #pragma unroll
         for (int mt = 0; mt < 2; ++mt)
 #pragma unroll
           for (int nt = 0; nt < HP / 8; ++nt) {
-            *reinterpret_cast<float2*>(tile + (16 * mt + gid) * L::kTS + 8 * nt + 2 * tig) = make_float2(acc[mt][nt][0], acc[mt][nt][1]);
-            *reinterpret_cast<float2*>(tile + (16 * mt + 8 + gid) * L::kTS + 8 * nt + 2 * tig) = make_float2(acc[mt][nt][2], acc[mt][nt][3]);
+            *reinterpret_cast<float2*>(stage_rows + (16 * mt + gid) * HP + 8 * nt + 2 * tig) = make_float2(acc[mt][nt][0], acc[mt][nt][1]);
+            *reinterpret_cast<float2*>(stage_rows + (16 * mt + 8 + gid) * HP + 8 * nt + 2 * tig) = make_float2(acc[mt][nt][2], acc[mt][nt][3]);
           }
         __syncwarp();
-        load_row<HP>(tile + lane * L::kTS, g);
+        load_row<HP>(stage_rows + lane * HP, g);
       }
       __syncthreads();        // the rows are rewritten by the next application / chunk
     }
@@ -2045,16 +2080,16 @@ static int launch_bwd_both(GnnArgs a, int max_nodes, float* d_params, cudaStream
   GSC_CUDA_TRY(cudaMemsetAsync(const_cast<int32_t*>(a.flags), 0, sizeof(int32_t), st));
   const size_t smem_g = GbL<HP>::bytes(a.num_convs);
   const bool gather_fma = gnn_bwd_variant() != 1 && a.stats != nullptr && max_nodes <= kGbThreads &&
-                          3 * (smem_g + 1024) <= 227 * 1024;
+                          kGbCtasPerSm * (smem_g + 1024) <= 227 * 1024;
   if (gather_fma) {
     GnnArgs t = a;
     t.cap = kGbThreads;
-    t.G = graphs_per_cta(kGbThreads, max_nodes, t.B, 3);
+    t.G = graphs_per_cta(kGbThreads, max_nodes, t.B, kGbCtasPerSm);
     const int chunks_t = (t.B + t.G - 1) / t.G;
     gnn_chunk_edges_kernel<<<(chunks_t + 255) / 256, 256, 0, st>>>(t.rowptr, t.graph_ptr, t.B, t.G,
                                                                    kGbEdgesPerNode * kGbThreads, const_cast<int32_t*>(a.flags));
     GSC_LAUNCH_CHECK("gnn_chunk_edges_kernel");
-    int grid_g = 3 * (kNumSMs - sm_reserve());
+    int grid_g = kGbCtasPerSm * (kNumSMs - sm_reserve());
     if (chunks_t < grid_g) grid_g = chunks_t;
     grid = grid_g > grid_f ? grid_g : grid_f;       // one partial row per CTA of either kernel
     GSC_CUDA_TRY(cudaFuncSetAttribute(gnn_bwd_gather_kernel<HP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_g));
@@ -2146,8 +2181,8 @@ extern "C" int gsc_gnn_embed_fwd(const float* x, int64_t Nt, int in_dim, const i
 }
 
 // Partial gradients of every CTA, plus (graphs too large for shared memory) the node-row scratch.
-static size_t bwd_partials_bytes(int in_dim, int H, int num_layers) {   // one row per CTA, up to 3 CTAs per SM
-  return ((size_t)3 * kNumSMs * (size_t)conv_param_offset(num_layers, in_dim, H) * 4 + 255) / 256 * 256;
+static size_t bwd_partials_bytes(int in_dim, int H, int num_layers) {   // one row per CTA, up to 4 CTAs per SM
+  return ((size_t)4 * kNumSMs * (size_t)conv_param_offset(num_layers, in_dim, H) * 4 + 255) / 256 * 256;
 }
 constexpr size_t kBwdFlagBytes = 256;    // kernel-selection flags, between the partials and the node-row scratch
 static bool bwd_rows_in_global(int max_nodes, int H, int num_layers) {
