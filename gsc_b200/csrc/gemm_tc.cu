@@ -69,15 +69,18 @@ struct TcParams {
   int flags, num_seg;
   int kb_end[3];          // exclusive prefix of 32-wide k-blocks per segment
   int kb_total, kb_per_split, splits, tiles_m, tiles_n;
+  int kb_interleave;      // split-K items take every splits-th k-block instead of a contiguous range
+  int bn;                 // N extent of the tile: 128, or 64 when N <= 64 (half the MMA and B traffic)
   int stages;             // operand ring depth: kTcEpiStages with the TMA epilogue, kTcMaxStages without
   int lo_stages;          // 3xTF32: depth of the lo ring (0 otherwise)
   int lo_off, lo_slot;    // 3xTF32: byte offset of the lo ring and bytes per slot
   int ebuf_off;           // byte offset of the epilogue tile
   int bar_off;            // byte offset of the barriers
-  int a_tmem;             // 3xTF32, K-major A: the A operand (hi and lo images) lives in tensor memory
+  int a_tmem;             // 3xTF32: the A operand (hi and lo images) lives in tensor memory
   int dbg;                // GSC_TC_DBG experiment bits: 1 no MMAs, 2 no TMA loads, 4 no epilogue body, 8 no conversion
   int epi_tma;            // 1: output tile leaves through shared memory + TMA store (coalesced, asynchronous)
   int epi_kind;           // operand streamed in by TMA for the epilogue: 0 none, 1 mul, 2 gate
+  int epi_sf;             // flag combination with a compile-time instance of the TMA epilogue, or -1
 };
 
 __device__ __forceinline__ float smask_apply(const TcParams& p, float v, int nb, int64_t j) {
@@ -146,8 +149,13 @@ __device__ __forceinline__ float tc_epilogue(const TcParams& p, float v, int64_t
 }
 
 struct WorkItem {
-  int m0, n0, split, kb_begin, kb_end;
+  int m0, n0, split, kb_first, kb_step, kb_count;
 };
+// Split-K work items walk the k-blocks either as one contiguous range each or INTERLEAVED (item s takes
+// k-blocks s, s + splits, ...).  Interleaved, the CTAs that share an m-tile read neighbouring 128-byte
+// pieces of the same operand rows at about the same time: for a K-major [1024 x 30000] operand (row
+// pitch 120 KB) that is what lets the DRAM controller serve them from open pages instead of
+// activating a page per 128 (256 with L2 promotion) bytes.
 __device__ __forceinline__ WorkItem decode_work(const TcParams& p, int w) {
   WorkItem it;
   const int tm = w % p.tiles_m;
@@ -155,10 +163,158 @@ __device__ __forceinline__ WorkItem decode_work(const TcParams& p, int w) {
   const int tn = rest % p.tiles_n;
   it.split = rest / p.tiles_n;
   it.m0 = tm * kTcBM;
-  it.n0 = tn * kTcBN;
-  it.kb_begin = it.split * p.kb_per_split;
-  it.kb_end = min(p.kb_total, it.kb_begin + p.kb_per_split);
+  it.n0 = tn * p.bn;
+  if (p.kb_interleave) {
+    it.kb_first = it.split;
+    it.kb_step = p.splits;
+    it.kb_count = (p.kb_total - it.split + p.splits - 1) / p.splits;
+  } else {
+    it.kb_first = it.split * p.kb_per_split;
+    it.kb_step = 1;
+    it.kb_count = min(p.kb_total, it.kb_first + p.kb_per_split) - it.kb_first;
+  }
   return it;
+}
+
+// lo = x - trunc(x) of U x 2 KB of a staged tile (16 bytes per thread and 2 KB slice), all loads first
+template <int U>
+__device__ __forceinline__ void lo_image(uint32_t src, uint32_t dst) {
+  uint32_t v[U][4];
+#pragma unroll
+  for (int u = 0; u < U; ++u)
+    asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(v[u][0]), "=r"(v[u][1]), "=r"(v[u][2]), "=r"(v[u][3]) : "r"(src + u * 2048));
+#pragma unroll
+  for (int u = 0; u < U; ++u) {
+    uint32_t lo[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e)
+      lo[e] = __float_as_uint(__uint_as_float(v[u][e]) - __uint_as_float(v[u][e] & 0xffffe000u));
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst + u * 2048), "r"(lo[0]), "r"(lo[1]), "r"(lo[2]), "r"(lo[3]) : "memory");
+  }
+}
+
+// TMA epilogue of one 128 x 128 tile: accumulators (+ prefetched mask/gate tile) -> smem tile in place ->
+// TMA store.  SF >= 0: the GSC_EPI_* bits of this launch, known at compile time, no operand tile
+// (epi_kind == 0); SF = -1: flags read at run time (any combination, mask / gate tile included).
+template <int SF>
+__device__ __forceinline__ void epi_tma_tile(const TcParams& p, const CUtensorMap* mapC, const WorkItem& it, int as, int iter,
+                                             int warp, int lane, uint32_t ebuf, uint32_t tmem_base, uint32_t tempty,
+                                             uint32_t efull_bar, uint32_t eempty_bar) {
+  constexpr bool kDyn = SF < 0;
+  const int quad = warp & 3;
+  const int c_begin = (warp >> 2) * (kTcBN / 64);
+  const int epi_kind = kDyn ? p.epi_kind : 0;
+  if (epi_kind) mbar_wait(efull_bar, (uint32_t)iter & 1u);
+  const int lrow = quad * 32 + lane;
+  const int64_t grow = (int64_t)it.m0 + lrow;
+  const bool f_table = kDyn ? (p.flags & GSC_EPI_ROWTABLE) != 0 : (SF & GSC_EPI_ROWTABLE) != 0;
+  const bool f_bias = kDyn ? (p.flags & GSC_EPI_BIAS) != 0 : (SF & GSC_EPI_BIAS) != 0;
+  const bool f_relu = kDyn ? (p.flags & GSC_EPI_RELU) != 0 : (SF & GSC_EPI_RELU) != 0;
+  const bool f_smask = kDyn ? (p.flags & GSC_EPI_SMASK) != 0 : (SF & GSC_EPI_SMASK) != 0;
+  const bool f_clamp = kDyn ? (p.flags & GSC_EPI_CLAMP1) != 0 : (SF & GSC_EPI_CLAMP1) != 0;
+  const bool f_gate_direct = kDyn && (p.flags & GSC_EPI_GATE) && p.epi_kind != 2;
+  const int nb = ((f_table || f_smask) && grow < p.M) ? p.row_n[grow] : 0;
+  const float* trow = f_table ? p.row_table + (int64_t)nb * p.ld_table : nullptr;
+  const bool vec_ok = (!f_table || ((reinterpret_cast<uintptr_t>(trow) & 15) == 0)) &&
+                      (!f_bias || ((reinterpret_cast<uintptr_t>(p.bias) & 15) == 0));
+  const int ncols = (int)p.N;                                  // the tensor-core path requires N < 2^31
+#pragma unroll 1
+  for (int cc = 0; cc < kTcBN / 64; ++cc) {
+    const int c = c_begin + cc;
+    const int col0 = it.n0 + c * 32;
+    // Columns past N compute garbage that the TMA store clips; only their loads are guarded.
+    // Additive per-column terms (bias, per-n table row) are fetched before waiting for TMEM.
+    float tadd[32], badd[32];                          // raw loads: consumed only after the TMEM wait
+    if (f_table || f_bias) {
+      if (vec_ok && col0 + 32 <= ncols) {
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          if (f_table) {
+            const float4 t4 = *reinterpret_cast<const float4*>(trow + col0 + 4 * q);
+            tadd[4 * q] = t4.x; tadd[4 * q + 1] = t4.y; tadd[4 * q + 2] = t4.z; tadd[4 * q + 3] = t4.w;
+          }
+          if (f_bias) {
+            const float4 b4 = *reinterpret_cast<const float4*>(p.bias + col0 + 4 * q);
+            badd[4 * q] = b4.x; badd[4 * q + 1] = b4.y; badd[4 * q + 2] = b4.z; badd[4 * q + 3] = b4.w;
+          }
+        }
+      } else {
+#pragma unroll
+        for (int q = 0; q < 32; ++q) {
+          const int cl = min(col0 + q, ncols - 1);
+          if (f_table) tadd[q] = trow[cl];
+          if (f_bias) badd[q] = p.bias[cl];
+        }
+      }
+    }
+    const uint32_t keep = f_smask ? smask_bits(p, nb, col0) : 0xffffffffu;
+    float v[32];
+    tc_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(as * kTcBN + c * 32), v);
+    if (cc == kTcBN / 64 - 1) {                                 // last TMEM read of this tile:
+      tc_fence_before();                                        // the accumulator buffer is free again
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tempty);
+    }
+    const uint32_t rbase = ebuf + c * 16384 + lrow * 128;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+      const uint32_t addr = rbase + (uint32_t)((q ^ (lrow & 7)) << 4);          // 128 B swizzle
+      float4 e = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (epi_kind) asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(e.x), "=f"(e.y), "=f"(e.z), "=f"(e.w) : "r"(addr));
+      const float ev[4] = {e.x, e.y, e.z, e.w};
+      float o[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        float t = v[4 * q + u];
+        if (f_table) t += tadd[4 * q + u];
+        if (f_bias) t += badd[4 * q + u];
+        if (f_relu) t = fmaxf(t, 0.f);
+        if (epi_kind == 1) t *= ev[u];
+        if (f_smask) t = (keep & (1u << (4 * q + u))) ? t : 0.f;
+        if (epi_kind == 2) t = ev[u] > 0.f ? t : 0.f;
+        if (f_gate_direct) {
+          const int col = col0 + 4 * q + u;
+          if (grow < p.M && col < ncols) t = p.gate[grow * p.ld_gate + col] > 0.f ? t : 0.f;
+        }
+        if (f_clamp) t = fminf(fmaxf(t, -1.f), 1.f);
+        o[u] = t;
+      }
+      asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(o[0]), "f"(o[1]), "f"(o[2]), "f"(o[3]) : "memory");
+    }
+    if (epi_kind == 0) {
+      // No prefetched operand tile: every 32-column chunk has its own 16 KB buffer and leaves with
+      // its own TMA store, which drains while the next chunk is computed.  One named barrier per
+      // chunk: before it the issuing thread makes sure the previous store of this column half has
+      // been read out of shared memory (its buffer is the next one to be overwritten).
+      fence_proxy_async_smem();                                  // st.shared -> visible to the TMA store
+      const bool issuer = (warp & 3) == 0 && lane == 0;
+      if (issuer) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+      asm volatile("bar.sync %0, 128;" ::"r"(1 + (warp >> 2)) : "memory");
+      if (issuer && col0 < ncols && !(p.dbg & 32)) {
+        asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(
+                         reinterpret_cast<uint64_t>(mapC)), "r"(ebuf + c * 16384), "r"(col0), "r"(it.m0) : "memory");
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+      }
+    }
+  }
+  if (epi_kind == 0) return;
+  fence_proxy_async_smem();                                    // st.shared -> visible to the TMA store
+  // the two column halves (warps 0..3 / 4..7) own their half of the tile buffer, their own named
+  // barrier and their own TMA store: one half computes while the other drains
+  const int half = warp >> 2;
+  asm volatile("bar.sync %0, 128;" ::"r"(1 + half) : "memory");
+  if ((warp & 3) == 0 && lane == 0) {
+#pragma unroll 1
+    for (int c = c_begin; c < c_begin + kTcBN / 64; ++c)
+      if (it.n0 + 32 * c < p.N && !(p.dbg & 32))
+        asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(
+                         reinterpret_cast<uint64_t>(mapC)), "r"(ebuf + c * 16384), "r"(it.n0 + 32 * c), "r"(it.m0) : "memory");
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+    asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // smem tile may be overwritten
+    if (p.epi_kind) mbar_arrive(eempty_bar);
+  }
+  asm volatile("bar.sync %0, 128;" ::"r"(1 + half) : "memory");
 }
 
 // Warp roles.  The two single-thread control loops (TMA producer, MMA issuer) are pure instruction
@@ -183,7 +339,7 @@ gemm_tc_kernel(const __grid_constant__ TcParams p, const __grid_constant__ CUten
   const uint32_t ebuf = smem_base + p.ebuf_off;                            // epilogue tile, 4 x [128 rows x 128 B]
   const uint32_t lo_base = smem_base + p.lo_off;                           // 3xTF32: lo ring behind the raw ring
   const uint32_t bar_base = smem_base + p.bar_off;
-  constexpr bool kATm = X3 && !A_MN;                                       // A-from-TMEM variant exists for K-major A
+  constexpr bool kATm = X3;                                                // A-from-TMEM (hi and lo images), either major-ness
   const bool a_tmem = kATm && p.a_tmem;
   const uint32_t tmem_cols = a_tmem ? 512u : (uint32_t)kTmemCols;
   constexpr int kTcStages = kTcBarSlots;                                   // barrier slots per ring
@@ -230,38 +386,35 @@ gemm_tc_kernel(const __grid_constant__ TcParams p, const __grid_constant__ CUten
       uint32_t phase = 0, ephase = 0;
       for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
         const WorkItem it = decode_work(p, w);
+        const uint32_t stage_tx = (uint32_t)(kTcBM + p.bn) * kTcBK * 4;
 #pragma unroll 1
-        for (int s = 0; s < p.num_seg; ++s) {
-          const int seg_begin = s ? p.kb_end[s - 1] : 0;
-          const int lo = max(it.kb_begin, seg_begin), hi = min(it.kb_end, p.kb_end[s]);
-          if (lo >= hi) continue;
+        for (int i = 0, kb = it.kb_first; i < it.kb_count; ++i, kb += it.kb_step) {
+          const int s = (kb >= p.kb_end[0]) + (kb >= p.kb_end[1]);          // K segment of this k-block
+          const int seg_begin = s == 0 ? 0 : (s == 1 ? p.kb_end[0] : p.kb_end[1]);
           const CUtensorMap* mA = s == 0 ? &mapA0 : (s == 1 ? &mapA1 : &mapA2);
           const CUtensorMap* mB = s == 0 ? &mapB0 : (s == 1 ? &mapB1 : &mapB2);
-          int k0 = (lo - seg_begin) * kTcBK;
-#pragma unroll 1
-          for (int kb = lo; kb < hi; ++kb, k0 += kTcBK) {
-            const uint32_t fb = full_bar(stage);
-            mbar_wait(empty_bar(stage), phase ^ 1u);
-            if (p.dbg & 2) { mbar_arrive(fb); if (++stage == num_stages) { stage = 0; phase ^= 1u; } continue; }
-            mbar_expect_tx(fb, kTcStageBytes);
-            const uint32_t sa = smem_base + stage * kTcStageBytes;
-            const uint32_t sb = sa + kTcBM * kTcBK * 4;
-            if (!A_MN) {
-              tma_load_2d(sa, mA, fb, k0, it.m0);                                   // box {32 k, 128 m}
-            } else {
+          const int k0 = (kb - seg_begin) * kTcBK;
+          const uint32_t fb = full_bar(stage);
+          mbar_wait(empty_bar(stage), phase ^ 1u);
+          if (p.dbg & 2) { mbar_arrive(fb); if (++stage == num_stages) { stage = 0; phase ^= 1u; } continue; }
+          mbar_expect_tx(fb, stage_tx);
+          const uint32_t sa = smem_base + stage * kTcStageBytes;
+          const uint32_t sb = sa + kTcBM * kTcBK * 4;
+          if (!A_MN) {
+            tma_load_2d(sa, mA, fb, k0, it.m0);                                   // box {32 k, 128 m}
+          } else {
 #pragma unroll
-              for (int b = 0; b < kTcBM / 32; ++b)                                  // box {32 m, 32 k}
-                tma_load_2d(sa + b * 4096, mA, fb, it.m0 + 32 * b, k0);
-            }
-            if (!B_MN) {
-              tma_load_2d(sb, mB, fb, k0, it.n0);                                   // box {32 k, 128 n}
-            } else {
-#pragma unroll
-              for (int b = 0; b < kTcBN / 32; ++b)                                  // box {32 n, 32 k}
-                tma_load_2d(sb + b * 4096, mB, fb, it.n0 + 32 * b, k0);
-            }
-            if (++stage == num_stages) { stage = 0; phase ^= 1u; }
+            for (int b = 0; b < kTcBM / 32; ++b)                                  // box {32 m, 32 k}
+              tma_load_2d(sa + b * 4096, mA, fb, it.m0 + 32 * b, k0);
           }
+          if (!B_MN) {
+            tma_load_2d(sb, mB, fb, k0, it.n0);                                   // box {32 k, bn n}
+          } else {
+#pragma unroll
+            for (int b = 0; b < kTcBN / 32; ++b)                                  // box {32 n, 32 k}
+              if (32 * b < p.bn) tma_load_2d(sb + b * 4096, mB, fb, it.n0 + 32 * b, k0);
+          }
+          if (++stage == num_stages) { stage = 0; phase ^= 1u; }
         }
         if (p.epi_tma && p.epi_kind) {             // prefetch the mask / gate tile of this work item
           mbar_wait(eempty_bar, ephase ^ 1u);
@@ -275,9 +428,9 @@ gemm_tc_kernel(const __grid_constant__ TcParams p, const __grid_constant__ CUten
   } else if (warp == kMmaWarp) {
     // ===================== MMA issuer =====================
     if (elect_one()) {
-      // instruction descriptor: D=f32, A=B=tf32, M=128, N=128, major bits
-      const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((A_MN ? 1u : 0u) << 15) |
-                             ((B_MN ? 1u : 0u) << 16) | ((uint32_t)(kTcBN >> 3) << 17) |
+      // instruction descriptor: D=f32, A=B=tf32, M=128, N=bn, major bits
+      const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | (((A_MN && !a_tmem) ? 1u : 0u) << 15) |
+                             ((B_MN ? 1u : 0u) << 16) | ((uint32_t)(p.bn >> 3) << 17) |
                              ((uint32_t)(kTcBM >> 4) << 24);
       // shared-memory descriptors as (low word, high word): the high word is constant per operand, the
       // low word = (address >> 4) | LBO << 16 advances by constants (see smem_desc in tc_ptx.cuh).
@@ -304,7 +457,7 @@ gemm_tc_kernel(const __grid_constant__ TcParams p, const __grid_constant__ CUten
         const uint32_t tmem_d = tmem_base + (uint32_t)(as * kTcBN);
         uint32_t acc = 0;
 #pragma unroll 1
-        for (int kb = it.kb_begin; kb < it.kb_end; ++kb) {
+        for (int kb = 0; kb < it.kb_count; ++kb) {
           if (X3) mbar_wait(lofull_bar(lstage), lphase);     // hi (in place) and lo images are ready
           else mbar_wait(full_bar(stage), phase);
           const uint32_t da = a_raw0 + stage * kStageW, db = b_raw0 + stage * kStageW;
@@ -358,7 +511,7 @@ gemm_tc_kernel(const __grid_constant__ TcParams p, const __grid_constant__ CUten
     for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
       const WorkItem it = decode_work(p, w);
 #pragma unroll 1
-      for (int kb = it.kb_begin; kb < it.kb_end; ++kb) {
+      for (int kb = 0; kb < it.kb_count; ++kb) {
         mbar_wait(full_bar(stage), phase);                       // TMA bytes have landed
         mbar_wait(loempty_bar(lstage), lphase ^ 1u);             // the MMAs that read this lo slot retired
         const uint32_t src = smem_base + stage * kTcStageBytes + ct * 16;
@@ -371,11 +524,21 @@ gemm_tc_kernel(const __grid_constant__ TcParams p, const __grid_constant__ CUten
           const int q = warp - kTcEpiWarps, r = 32 * q + lane;
           const uint32_t rowp = smem_base + stage * kTcStageBytes + r * 128;
           uint32_t x[32];
+          if (!A_MN) {
 #pragma unroll
-          for (int c = 0; c < 8; ++c)
-            asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
-                         : "=r"(x[4 * c]), "=r"(x[4 * c + 1]), "=r"(x[4 * c + 2]), "=r"(x[4 * c + 3])
-                         : "r"(rowp + (uint32_t)((c ^ (r & 7)) << 4)));
+            for (int c = 0; c < 8; ++c)
+              asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                           : "=r"(x[4 * c]), "=r"(x[4 * c + 1]), "=r"(x[4 * c + 2]), "=r"(x[4 * c + 3])
+                           : "r"(rowp + (uint32_t)((c ^ (r & 7)) << 4)));
+          } else {
+            // MN-major tile: four boxes of [32 k][32 m], 128-byte rows swizzled in 32-byte atoms with a
+            // period of four rows (atom ^= k & 3).  A warp reads one 128-byte row per k: conflict-free.
+            const uint32_t colp = smem_base + stage * kTcStageBytes + (uint32_t)q * 4096u;
+#pragma unroll
+            for (int k = 0; k < 32; ++k)
+              asm volatile("ld.shared.b32 %0, [%1];" : "=r"(x[k])
+                           : "r"(colp + (uint32_t)(k * 128) + (uint32_t)((lane * 4) ^ ((k & 3) << 5))));
+          }
           uint32_t y[32];
 #pragma unroll
           for (int e = 0; e < 32; ++e) y[e] = x[e] & 0xffffe000u;
@@ -385,19 +548,8 @@ gemm_tc_kernel(const __grid_constant__ TcParams p, const __grid_constant__ CUten
           for (int e = 0; e < 32; ++e) y[e] = __float_as_uint(__uint_as_float(x[e]) - __uint_as_float(y[e]));
           tc_st32(ta + kTcBK, y);
           const uint32_t srcb = src + kTcBM * kTcBK * 4;
-          uint32_t v[8][4];
-#pragma unroll
-          for (int u = 0; u < 8; ++u)
-            asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
-                         : "=r"(v[u][0]), "=r"(v[u][1]), "=r"(v[u][2]), "=r"(v[u][3]) : "r"(srcb + u * 2048));
-#pragma unroll
-          for (int u = 0; u < 8; ++u) {
-            uint32_t lo[4];
-#pragma unroll
-            for (int e = 0; e < 4; ++e)
-              lo[e] = __float_as_uint(__uint_as_float(v[u][e]) - __uint_as_float(v[u][e] & 0xffffe000u));
-            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst + u * 2048), "r"(lo[0]), "r"(lo[1]), "r"(lo[2]), "r"(lo[3]) : "memory");
-          }
+          if (p.bn == kTcBN) lo_image<8>(srcb, dst);
+          else lo_image<4>(srcb, dst);                          // bn = 64: the B tile is 8 KB
           tc_st_wait();
           tc_fence_before();
         } else if (!(p.dbg & 8)) {
@@ -447,114 +599,19 @@ gemm_tc_kernel(const __grid_constant__ TcParams p, const __grid_constant__ CUten
         continue;
       }
       if (p.epi_tma) {
-        // ---- TMA epilogue: accumulators (+ prefetched mask/gate tile) -> smem tile in place -> TMA store ----
-        if (p.epi_kind) mbar_wait(efull_bar, (uint32_t)iter & 1u);
-        const int lrow = quad * 32 + lane;
-        const int64_t grow = (int64_t)it.m0 + lrow;
-        const bool f_table = p.flags & GSC_EPI_ROWTABLE, f_bias = p.flags & GSC_EPI_BIAS;
-        const bool f_relu = p.flags & GSC_EPI_RELU, f_smask = p.flags & GSC_EPI_SMASK;
-        const bool f_clamp = p.flags & GSC_EPI_CLAMP1;
-        const bool f_gate_direct = (p.flags & GSC_EPI_GATE) && p.epi_kind != 2;
-        const int nb = ((f_table || f_smask) && grow < p.M) ? p.row_n[grow] : 0;
-        const float* trow = f_table ? p.row_table + (int64_t)nb * p.ld_table : nullptr;
-        const bool vec_ok = (!f_table || ((reinterpret_cast<uintptr_t>(trow) & 15) == 0)) &&
-                            (!f_bias || ((reinterpret_cast<uintptr_t>(p.bias) & 15) == 0));
-        const int ncols = (int)p.N;                                  // the tensor-core path requires N < 2^31
-#pragma unroll 1
-        for (int c = c_begin; c < c_end; ++c) {
-          const int col0 = it.n0 + c * 32;
-          // Columns past N compute garbage that the TMA store clips; only their loads are guarded.
-          // Additive per-column terms (bias, per-n table row) are fetched before waiting for TMEM.
-          float tadd[32], badd[32];                          // raw loads: consumed only after the TMEM wait
-#pragma unroll
-          for (int q = 0; q < 32; ++q) { tadd[q] = 0.f; badd[q] = 0.f; }
-          if (f_table || f_bias) {
-            if (vec_ok && col0 + 32 <= ncols) {
-#pragma unroll
-              for (int q = 0; q < 8; ++q) {
-                if (f_table) {
-                  const float4 t4 = *reinterpret_cast<const float4*>(trow + col0 + 4 * q);
-                  tadd[4 * q] = t4.x; tadd[4 * q + 1] = t4.y; tadd[4 * q + 2] = t4.z; tadd[4 * q + 3] = t4.w;
-                }
-                if (f_bias) {
-                  const float4 b4 = *reinterpret_cast<const float4*>(p.bias + col0 + 4 * q);
-                  badd[4 * q] = b4.x; badd[4 * q + 1] = b4.y; badd[4 * q + 2] = b4.z; badd[4 * q + 3] = b4.w;
-                }
-              }
-            } else {
-#pragma unroll
-              for (int q = 0; q < 32; ++q) {
-                const int cc = min(col0 + q, ncols - 1);
-                if (f_table) tadd[q] = trow[cc];
-                if (f_bias) badd[q] = p.bias[cc];
-              }
-            }
-          }
-          const uint32_t keep = f_smask ? smask_bits(p, nb, col0) : 0xffffffffu;
-          float v[32];
-          tc_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(as * kTcBN + c * 32), v);
-          if (c == c_end - 1) {                                       // last TMEM read of this tile:
-            tc_fence_before();                                        // the accumulator buffer is free again
-            __syncwarp();
-            if (lane == 0) mbar_arrive(tempty_bar(as));
-          }
-          const uint32_t rbase = ebuf + c * 16384 + lrow * 128;
-#pragma unroll
-          for (int q = 0; q < 8; ++q) {
-            const uint32_t addr = rbase + (uint32_t)((q ^ (lrow & 7)) << 4);          // 128 B swizzle
-            float4 e = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (p.epi_kind) asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(e.x), "=f"(e.y), "=f"(e.z), "=f"(e.w) : "r"(addr));
-            const float ev[4] = {e.x, e.y, e.z, e.w};
-            float o[4];
-#pragma unroll
-            for (int u = 0; u < 4; ++u) {
-              float t = (v[4 * q + u] + tadd[4 * q + u]) + badd[4 * q + u];
-              if (f_relu) t = fmaxf(t, 0.f);
-              if (p.epi_kind == 1) t *= ev[u];
-              if (f_smask) t = ((keep >> (4 * q + u)) & 1u) ? t : 0.f;
-              if (p.epi_kind == 2) t = ev[u] > 0.f ? t : 0.f;
-              if (f_gate_direct) {
-                const int col = col0 + 4 * q + u;
-                if (grow < p.M && col < ncols) t = p.gate[grow * p.ld_gate + col] > 0.f ? t : 0.f;
-              }
-              if (f_clamp) t = fminf(fmaxf(t, -1.f), 1.f);
-              o[u] = t;
-            }
-            asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(o[0]), "f"(o[1]), "f"(o[2]), "f"(o[3]) : "memory");
-          }
-          if (p.epi_kind == 0) {
-            // No prefetched operand tile: every 32-column chunk has its own 16 KB buffer and leaves with
-            // its own TMA store, which drains while the next chunk is computed.  One named barrier per
-            // chunk: before it the issuing thread makes sure the previous store of this column half has
-            // been read out of shared memory (its buffer is the next one to be overwritten).
-            fence_proxy_async_smem();                                  // st.shared -> visible to the TMA store
-            const bool issuer = (warp & 3) == 0 && lane == 0;
-            if (issuer) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
-            asm volatile("bar.sync %0, 128;" ::"r"(1 + (warp >> 2)) : "memory");
-            if (issuer && col0 < ncols) {
-              asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(
-                               reinterpret_cast<uint64_t>(&mapC)), "r"(ebuf + c * 16384), "r"(col0), "r"(it.m0) : "memory");
-              asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-            }
-          }
+        // the flag combinations of the large-output layers have their own compile-time instance: the
+        // run-time-flag form costs ~54 instructions per output element, which made these layers
+        // issue-bound in their epilogue warps (8 000 cycles per 128 x 128 tile)
+        const uint32_t te = tempty_bar(as);
+        switch (p.epi_sf) {
+          case 0: epi_tma_tile<0>(p, &mapC, it, as, iter, warp, lane, ebuf, tmem_base, te, efull_bar, eempty_bar); break;
+          case GSC_EPI_SMASK: epi_tma_tile<GSC_EPI_SMASK>(p, &mapC, it, as, iter, warp, lane, ebuf, tmem_base, te, efull_bar, eempty_bar); break;
+          case GSC_EPI_BIAS: epi_tma_tile<GSC_EPI_BIAS>(p, &mapC, it, as, iter, warp, lane, ebuf, tmem_base, te, efull_bar, eempty_bar); break;
+          case GSC_EPI_BIAS | GSC_EPI_RELU: epi_tma_tile<GSC_EPI_BIAS | GSC_EPI_RELU>(p, &mapC, it, as, iter, warp, lane, ebuf, tmem_base, te, efull_bar, eempty_bar); break;
+          case GSC_EPI_BIAS | GSC_EPI_SMASK: epi_tma_tile<GSC_EPI_BIAS | GSC_EPI_SMASK>(p, &mapC, it, as, iter, warp, lane, ebuf, tmem_base, te, efull_bar, eempty_bar); break;
+          case GSC_EPI_BIAS | GSC_EPI_SMASK | GSC_EPI_CLAMP1: epi_tma_tile<GSC_EPI_BIAS | GSC_EPI_SMASK | GSC_EPI_CLAMP1>(p, &mapC, it, as, iter, warp, lane, ebuf, tmem_base, te, efull_bar, eempty_bar); break;
+          default: epi_tma_tile<-1>(p, &mapC, it, as, iter, warp, lane, ebuf, tmem_base, te, efull_bar, eempty_bar); break;
         }
-        if (p.epi_kind == 0) continue;
-        fence_proxy_async_smem();                                    // st.shared -> visible to the TMA store
-        // the two column halves (warps 0..3 / 4..7) own their half of the tile buffer, their own named
-        // barrier and their own TMA store: one half computes while the other drains
-        const int half = warp >> 2;
-        asm volatile("bar.sync %0, 128;" ::"r"(1 + half) : "memory");
-        if ((warp & 3) == 0 && lane == 0) {
-#pragma unroll 1
-          for (int c = c_begin; c < c_end; ++c)
-            if (it.n0 + 32 * c < p.N)
-              asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(
-                               reinterpret_cast<uint64_t>(&mapC)), "r"(ebuf + c * 16384), "r"(it.n0 + 32 * c), "r"(it.m0) : "memory");
-          asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-          asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // smem tile may be overwritten
-          if (p.epi_kind) mbar_arrive(eempty_bar);
-        }
-        asm volatile("bar.sync %0, 128;" ::"r"(1 + half) : "memory");
         continue;
       }
       const int64_t row = (int64_t)it.m0 + quad * 32 + lane;
@@ -677,6 +734,8 @@ static int tc_round_mode() {
 int gemm_tc_launch(const gsc_gemm_args* a, int64_t M, int64_t N, float* C, int64_t ldc, void* workspace,
                    size_t workspace_bytes, bool a_mn, bool b_mn, bool x3, cudaStream_t st, int* used_splits) {
   TcParams p{};
+  static const int bn64_env = [] { const char* e = getenv("GSC_GEMM_BN64"); return (e && e[0] == '0') ? 0 : 1; }();
+  const int bn = (N <= 64 && bn64_env) ? 64 : kTcBN;
   CUtensorMap maps[8];
   memset(maps, 0, sizeof(maps));
   int kb = 0;
@@ -686,7 +745,7 @@ int gemm_tc_launch(const gsc_gemm_args* a, int64_t M, int64_t N, float* C, int64
     if (!a_mn) rc = make_map(&maps[s], a->A[s], a->K[s], M, a->a_rs[s], kTcBK, kTcBM, rnd, false);
     else rc = make_map(&maps[s], a->A[s], M, a->K[s], a->a_cs[s], 32, kTcBK, rnd, true);
     if (rc) return rc;
-    if (!b_mn) rc = make_map(&maps[3 + s], a->B[s], a->K[s], N, a->b_cs[s], kTcBK, kTcBN, rnd, false);
+    if (!b_mn) rc = make_map(&maps[3 + s], a->B[s], a->K[s], N, a->b_cs[s], kTcBK, bn, rnd, false);
     else rc = make_map(&maps[3 + s], a->B[s], N, a->K[s], a->b_rs[s], 32, kTcBK, rnd, true);
     if (rc) return rc;
     kb += (int)ceil_div(a->K[s], kTcBK);
@@ -698,7 +757,8 @@ int gemm_tc_launch(const gsc_gemm_args* a, int64_t M, int64_t N, float* C, int64
   p.row_table = a->row_table; p.row_n = a->row_n; p.ld_table = a->ld_table; p.n_max = a->n_max; p.groups = a->groups;
   p.kb_total = kb;
   p.tiles_m = (int)ceil_div(M, kTcBM);
-  p.tiles_n = (int)ceil_div(N, kTcBN);
+  p.tiles_n = (int)ceil_div(N, bn);
+  p.bn = bn;
   const int64_t tiles = (int64_t)p.tiles_m * p.tiles_n;
   // split K when the output tiles alone cannot fill the machine; keep >= 4 k-blocks per split
   // (tiles * splits work items on kNumSMs persistent CTAs: never more items than CTAs, or a few CTAs
@@ -708,13 +768,15 @@ int gemm_tc_launch(const gsc_gemm_args* a, int64_t M, int64_t N, float* C, int64
   if (want > max_by_k) want = max_by_k;
   if (workspace == nullptr) want = 1;
   while (want > 1 && (size_t)want * (size_t)M * (size_t)N * 4 > workspace_bytes) --want;
+  static const int il_env = [] { const char* e = getenv("GSC_SPLITK_INTERLEAVE"); return (e && e[0] == '0') ? 0 : 1; }();
+  p.kb_interleave = il_env;
   p.kb_per_split = (int)ceil_div(kb, want);
-  p.splits = (int)ceil_div(kb, p.kb_per_split);
+  p.splits = p.kb_interleave ? (int)want : (int)ceil_div(kb, p.kb_per_split);
   p.partial = (float*)workspace;
   *used_splits = p.splits;
   // TMA epilogue: needs a TMA-mappable output (and mask/gate operand); split-K partials keep direct stores
   maps[6] = maps[0]; maps[7] = maps[0];
-  p.epi_tma = 0; p.epi_kind = 0;
+  p.epi_tma = 0; p.epi_kind = 0; p.epi_sf = -1;
   const char* no_tma_epi = getenv("GSC_GEMM_DIRECT_EPILOGUE");
   if (p.splits == 1 && !(no_tma_epi && no_tma_epi[0] == '1') && aligned16(C) && ldc % 4 == 0) {
     const float* e = nullptr; int64_t lde = 0; int kind = 0;
@@ -726,10 +788,14 @@ int gemm_tc_launch(const gsc_gemm_args* a, int64_t M, int64_t N, float* C, int64
       if (rc) return rc;
       if (kind) { rc = make_map(&maps[7], e, N, M, lde, 32, kTcBM, 0, false); if (rc) return rc; }
       p.epi_tma = 1; p.epi_kind = kind;
+      const int ef = a->flags & ~(GSC_EPI_TF32 | GSC_EPI_TF32X3);
+      static const int sf_env = [] { const char* e = getenv("GSC_GEMM_DYNAMIC_EPILOGUE"); return (e && e[0] == '1') ? 0 : 1; }();
+      p.epi_sf = (kind == 0 && sf_env && (ef & ~(GSC_EPI_BIAS | GSC_EPI_RELU | GSC_EPI_SMASK | GSC_EPI_CLAMP1)) == 0) ? ef : -1;
     }
   }
   static const int atm_env = [] { const char* e = getenv("GSC_X3_ATMEM"); return (e && e[0] == '0') ? 0 : 1; }();
-  p.a_tmem = (x3 && !a_mn && atm_env) ? 1 : 0;
+  static const int atm_mn_env = [] { const char* e = getenv("GSC_X3_ATMEM_MN"); return (e && e[0] == '0') ? 0 : 1; }();
+  p.a_tmem = (x3 && atm_env && (!a_mn || atm_mn_env)) ? 1 : 0;
   if (p.a_tmem) {
     // A operand in tensor memory: the lo ring holds B only (16 KB slots), so the raw ring can be deeper
     p.stages = p.epi_tma ? 4 : 5;

@@ -50,19 +50,22 @@ for prec in ("tf32", "tf32x3", "fp32"):
 
 names = {0: "full", 1: "no MMAs", 2: "no TMA loads", 4: "no epilogue", 5: "no MMAs, no epilogue", 6: "no loads, no epilogue",
          8: "no conversion", 12: "no conversion, no epilogue", 10: "no loads, no conversion", 14: "MMAs only"}
-for prec in ("tf32", "tf32x3"):
-    ops.precision = prec
-    for dbg, label in names.items():
-        if prec == "tf32" and dbg & 8:
-            continue
-        os.environ["GSC_TC_DBG"] = str(dbg)
-        print(f"ablate {prec:7s} actor_l2 fwd  dbg={dbg:2d} ({label:28s}) {timeit(cases['actor_l2 fwd [1024x30000x256] smask']):8.1f} us", flush=True)
-ops.precision = "tf32"
-for dbg, label in ((6, "MMAs only"), (6 + 32, "MMAs only, no wait, no commit"), (6 + 64, "MMAs only, no wait")):
-    os.environ["GSC_TC_DBG"] = str(dbg)
-    print(f"handshake tf32 actor_l2 fwd dbg={dbg:3d} ({label:30s}) {timeit(cases['actor_l2 fwd [1024x30000x256] smask']):8.1f} us", flush=True)
-os.environ["GSC_TC_DBG"] = "16"
+which = sys.argv[1:] or ["actor_l2 fwd"]
+names[32] = "no TMA stores"
+outp = torch.empty(M, A + 16, device=dev)[:, :A]
+cases["dgrad action, ld 30016"] = lambda: ops.linear_dgrad(dh, W1, 24 + A, A, smask=(n, nm, 3), out=outp)
+cases["actor_l2 fwd, ld 30016"] = lambda: ops.linear_fwd([h], W2, b2, smask=(n, nm, 3), out=outp)
+print(f"fill_ [1024x30000] fp32 {timeit(lambda: out.fill_(1.0)):8.1f} us;  copy_ {timeit(lambda: out.copy_(dy)):8.1f} us", flush=True)
 ops.precision = "tf32x3"
+table = ops.mask_table(W1[:, 24:24 + A], nm, 3)
 for name, fn in cases.items():
-    print(f"x3 in-place rounded split  {name:45s} {timeit(fn):8.1f} us", flush=True)
+    if not any(w in name for w in which):
+        continue
+    for prec in ("tf32", "tf32x3"):
+        ops.precision = prec
+        for dbg, label in names.items():
+            if prec == "tf32" and dbg & 8:
+                continue
+            os.environ["GSC_TC_DBG"] = str(dbg)
+            print(f"ablate {prec:7s} {name[:28]:28s} dbg={dbg:2d} ({label:28s}) {timeit(fn):8.1f} us", flush=True)
 os.environ["GSC_TC_DBG"] = "0"
