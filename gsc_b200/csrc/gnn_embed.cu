@@ -1325,6 +1325,38 @@ struct GbL {
   }
 };
 
+// Column sums of a [32 lanes x N] register matrix, added to dst[0..N).  Instead of one 5-step butterfly
+// per column (10 N instructions), every step with an even column count exchanges HALF of the columns
+// with the partner lane (it keeps the other half), so the matrix shrinks as the lanes combine:
+// N = 24: 12 + 6 + 3 exchanges, then two plain butterfly steps on 3 columns = 27 shuffles instead of 120.
+template <int N, int MASK>
+__device__ __forceinline__ void warp_colsum_step(float (&v)[N], int lane, int base, int writers, float* __restrict__ dst) {
+  if constexpr (MASK == 0) {
+    if ((lane & writers) == 0) {
+#pragma unroll
+      for (int i = 0; i < N; ++i) dst[base + i] += v[i];
+    }
+  } else if constexpr (N % 2 == 0) {
+    const bool up = (lane & MASK) != 0;
+    float h[N / 2];
+#pragma unroll
+    for (int i = 0; i < N / 2; ++i) {
+      const float send = up ? v[i] : v[i + N / 2];
+      const float keep = up ? v[i + N / 2] : v[i];
+      h[i] = keep + __shfl_xor_sync(0xffffffffu, send, MASK);
+    }
+    warp_colsum_step<N / 2, MASK / 2>(h, lane, base + (up ? N / 2 : 0), writers, dst);
+  } else {
+#pragma unroll
+    for (int i = 0; i < N; ++i) v[i] += __shfl_xor_sync(0xffffffffu, v[i], MASK);
+    warp_colsum_step<N, MASK / 2>(v, lane, base, writers | MASK, dst);      // replicated over this lane bit
+  }
+}
+template <int N>
+__device__ __forceinline__ void warp_colsum_add(float (&v)[N], int lane, float* __restrict__ dst) {
+  warp_colsum_step<N, 16>(v, lane, 0, 0, dst);
+}
+
 // Warp-level tensor-core MMA (m16n8k8, TF32 operands, fp32 accumulate).  The node transforms of the
 // gather kernel are [32 nodes] x [HP] x [2HP] per warp: far too small to stage for tcgen05, but as
 // 3xTF32 mma.sync they cost ~110 instructions per warp where the FMA form costs ~1400.
@@ -1558,11 +1590,7 @@ __global__ void __launch_bounds__(kGbThreads, 4) gnn_bwd_gather_kernel(const Gnn
 #pragma unroll
           for (int c = 0; c < HP; ++c) { dbias[c] = g[c]; g[c] *= inv_deg; }
         }
-#pragma unroll
-        for (int c = 0; c < HP; ++c) {
-          const float sb = warp_sum(dbias[c]);
-          if (lane == (c & 31)) slot[HP + c] += sb;       // warp-private slot
-        }
+        warp_colsum_add<HP>(dbias, lane, slot + HP);      // warp-private slot
       }
       __syncthreads();
 
@@ -1593,7 +1621,8 @@ __global__ void __launch_bounds__(kGbThreads, 4) gnn_bwd_gather_kernel(const Gnn
             s1 = fmaf(vec[3 * HP + c + 1], fabsf(t1), s1);
             d0 = fmaf(g[c], v[c], d0);
             d1 = fmaf(g[c + 1], v[c + 1], d1);
-            bits |= ((__float_as_uint(t0) >> 31) << c) | ((__float_as_uint(t1) >> 31) << (c + 1));
+            if (t0 < 0.f) bits |= 1u << c;
+            if (t1 < 0.f) bits |= 2u << c;
           }
           const float sc_e = p_s[j] + q_i + (s0 + s1);
           es_s[e] = sc_e;
@@ -1623,24 +1652,20 @@ __global__ void __launch_bounds__(kGbThreads, 4) gnn_bwd_gather_kernel(const Gnn
           ds_sum += ds;
 #pragma unroll
           for (int c = 0; c < HP; ++c)
-            sg[c] += __uint_as_float(__float_as_uint(ds) ^ ((bits << (31 - c)) & 0x80000000u));
+            if (bits & (1u << c)) sg[c] += ds;           // sum of ds over the edges on the negative branch
         }
-        const float base = 0.6f * ds_sum;
 #pragma unroll
         for (int c = 0; c < HP; ++c) {
-          const float wv = fmaf(0.4f, sg[c], base);
+          const float wv = fmaf(-0.8f, sg[c], ds_sum);   // sum_e ds_e (0.6 + 0.4 sgn) = ds_sum - 0.8 sum_neg
           datt[c] = xr[c] * wv;
           sg[c] = vec[2 * HP + c] * wv;                  // d_xr
         }
         store_row<HP>(dxa + HP, sg);                     // read back in step 4 (registers are short at 4 CTAs per SM)
         load_row<HP>(xl_s + i * HP, vown);               // own xl row for the source pass: xl_s is free after the barrier
       }
+      warp_colsum_add<HP>(datt, lane, slot);             // target half of d_att
 #pragma unroll
-      for (int c = 0; c < HP; ++c) {                     // target half of d_att
-        const float sa = warp_sum(datt[c]);
-        if (lane == (c & 31)) slot[c] += sa;
-        datt[c] = 0.f;
-      }
+      for (int c = 0; c < HP; ++c) datt[c] = 0.f;
       __syncthreads();
 
       // ---- 3. source side: d_xl over the out-edges = this node's own CSR row of a symmetric graph; what the
@@ -1664,23 +1689,19 @@ __global__ void __launch_bounds__(kGbThreads, 4) gnn_bwd_gather_kernel(const Gnn
 #pragma unroll
           for (int c = 0; c < HP; ++c) {
             dxl[c] = fmaf(alpha, gi[c], dxl[c]);
-            sg[c] += __uint_as_float(__float_as_uint(ds) ^ ((bits << (31 - c)) & 0x80000000u));
+            if (bits & (1u << c)) sg[c] += ds;
           }
         }
-        const float base = 0.6f * ds_sum;
 #pragma unroll
         for (int c = 0; c < HP; ++c) {
-          const float wv = fmaf(0.4f, sg[c], base);
+          const float wv = fmaf(-0.8f, sg[c], ds_sum);
           datt[c] = vown[c] * wv;
           dxl[c] = fmaf(vec[2 * HP + c], wv, dxl[c]);
         }
         store_row<HP>(dxa, dxl);
       }
-#pragma unroll
-      for (int c = 0; c < HP; ++c) {
-        const float sa = warp_sum(datt[c]);
-        if (lane == (c & 31)) slot[c] += sa;
-      }
+      __syncwarp();                                      // slot[] is updated by different lanes in the two halves
+      warp_colsum_add<HP>(datt, lane, slot);
       // ---- 4. d_h_in = d_xl Wl + d_xr Wr -> d_out of application a-1: two [32 x HP] x [HP x HP] products; the
       //         operand rows are staged in this warp's slot rows of xl_s (no xl row is read after the last
       //         barrier), and the result rows return to their owners the same way ----
