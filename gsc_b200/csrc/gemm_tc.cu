@@ -516,7 +516,9 @@ gemm_tc_kernel(const __grid_constant__ TcParams p, const __grid_constant__ CUten
         mbar_wait(loempty_bar(lstage), lphase ^ 1u);             // the MMAs that read this lo slot retired
         const uint32_t src = smem_base + stage * kTcStageBytes + ct * 16;
         const uint32_t dst = lo_base + lstage * p.lo_slot + ct * 16;
-        if (kATm && a_tmem) {
+        if (kATm && a_tmem && (p.dbg & 8)) {
+          // experiment: no conversion work at all
+        } else if (kATm && a_tmem) {
           // A rows -> tensor memory.  Converter warp q may access TMEM lanes 32q..32q+31, so thread (q, lane)
           // takes row 32q + lane of the staged K-major tile (eight swizzled 16-byte chunks), writes
           // hi = trunc(x) to 32 columns and lo = x - hi to the next 32.  B: lo image into the lo ring.
@@ -640,9 +642,15 @@ gemm_tc_kernel(const __grid_constant__ TcParams p, const __grid_constant__ CUten
             }
           } else {
             float* dst = p.partial + ((int64_t)it.split * p.M + row) * p.N + col0;
+            if (col0 + 32 <= p.N && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
 #pragma unroll
-            for (int q = 0; q < 32; ++q)
-              if (col0 + q < p.N) dst[q] = v[q];
+              for (int q = 0; q < 8; ++q)
+                reinterpret_cast<float4*>(dst)[q] = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+            } else {
+#pragma unroll
+              for (int q = 0; q < 32; ++q)
+                if (col0 + q < p.N) dst[q] = v[q];
+            }
           }
         }
       }

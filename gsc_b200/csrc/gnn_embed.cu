@@ -1940,19 +1940,31 @@ __global__ void gnn_chunk_edges_kernel(const int32_t* __restrict__ rowptr, const
 
 // d_params[t] = sum of the CTA partials, in a fixed order: block = 32 parameters x 8 partial-lanes,
 // lane r adds the partials r, r + 8, ... (independent loads in flight), then the lanes are added.
+// Sums the partial rows in a fixed order.  When the gather kernel ran (same run-time condition as in
+// the kernels themselves), the W / lin-bias entries were written by gnn_wgrad_kernel, which uses
+// `rows_w` CTAs (a streaming kernel wants long node slices), the att / bias entries by the gather
+// kernel's `num_partials` CTAs.
 __global__ void __launch_bounds__(256)
-gnn_bwd_reduce_kernel(const float* __restrict__ partials, int num_partials, int64_t P, float* __restrict__ d_params) {
+gnn_bwd_reduce_kernel(const float* __restrict__ partials, int num_partials, int rows_w, int64_t P, float* __restrict__ d_params,
+                      const int32_t* __restrict__ stats, const int32_t* __restrict__ flags, int num_convs, int in_dim, int H) {
   __shared__ float red[8][33];
   const int c = threadIdx.x & 31, r = threadIdx.x >> 5;
   const int64_t t = (int64_t)blockIdx.x * 32 + c;
+  int rows = num_partials;
+  if (rows_w < num_partials && stats != nullptr && stats[3] == 0 && flags[0] == 0) {
+    for (int cv = 0; cv < num_convs; ++cv) {
+      const int64_t o = conv_param_offset(cv, in_dim, H);
+      if (t >= o + 2 * H && t < conv_param_offset(cv + 1, in_dim, H)) rows = rows_w;
+    }
+  }
   float s0 = 0.f, s1 = 0.f;
   if (t < P) {
     int b = r;
-    for (; b + 8 < num_partials; b += 16) {
+    for (; b + 8 < rows; b += 16) {
       s0 += partials[(size_t)b * P + t];
       s1 += partials[(size_t)(b + 8) * P + t];
     }
-    if (b < num_partials) s0 += partials[(size_t)b * P + t];
+    if (b < rows) s0 += partials[(size_t)b * P + t];
   }
   red[r][c] = s0 + s1;
   __syncthreads();
@@ -2097,7 +2109,7 @@ static int launch_bwd_both(GnnArgs a, int max_nodes, float* d_params, cudaStream
   int cap_t = 0, cols = 0;
   size_t smem_t = 0;
   const bool tc = gnn_use_tc() && a.stats != nullptr && plan_bwd_tc<HP>(a, max_nodes, &cap_t, &cols, &smem_t);
-  int grid = grid_f;
+  int grid = grid_f, rows_w = 0;
   GSC_CUDA_TRY(cudaMemsetAsync(const_cast<int32_t*>(a.flags), 0, sizeof(int32_t), st));
   const size_t smem_g = GbL<HP>::bytes(a.num_convs);
   const bool gather_fma = gnn_bwd_variant() != 1 && a.stats != nullptr && max_nodes <= kGbThreads &&
@@ -2118,7 +2130,9 @@ static int launch_bwd_both(GnnArgs a, int max_nodes, float* d_params, cudaStream
     GSC_LAUNCH_CHECK("gnn_bwd_gather_kernel");
     const int smem_w = WgL<HP>::kSmemFloats * 4;
     GSC_CUDA_TRY(cudaFuncSetAttribute(gnn_wgrad_kernel<HP>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_w));
-    gnn_wgrad_kernel<HP><<<grid, kGnnThreads, smem_w, st>>>(t);           // its weight gradients (same condition)
+    static const int wg_ctas = [] { const char* e = getenv("GSC_GNN_WGRAD_CTAS"); return e ? atoi(e) : 2; }();
+    rows_w = wg_ctas > 0 ? min(grid, wg_ctas * kNumSMs) : grid;
+    gnn_wgrad_kernel<HP><<<rows_w, kGnnThreads, smem_w, st>>>(t);         // its weight gradients (same condition)
     GSC_LAUNCH_CHECK("gnn_wgrad_kernel");
     a.gather_kernel_launched = 1;
   } else if (tc) {
@@ -2149,7 +2163,9 @@ static int launch_bwd_both(GnnArgs a, int max_nodes, float* d_params, cudaStream
   }
   GSC_LAUNCH_CHECK("gnn_bwd_kernel");
   const int64_t P = conv_param_offset(a.num_convs, a.in_dim, a.H);
-  gnn_bwd_reduce_kernel<<<(int)ceil_div(P, 32), 256, 0, st>>>(a.partials, grid, P, d_params);
+  if (rows_w == 0) rows_w = grid;
+  gnn_bwd_reduce_kernel<<<(int)ceil_div(P, 32), 256, 0, st>>>(a.partials, grid, rows_w, P, d_params, a.stats, a.flags,
+                                                              a.num_convs, a.in_dim, a.H);
   GSC_LAUNCH_CHECK("gnn_bwd_reduce_kernel");
   return GSC_OK;
 }
