@@ -177,7 +177,7 @@ def run_ours(args):
         upd = ddpg.DDPGUpdater(actor, qf1, ta, tq, lr=1e-3, gamma=0.99, tau=1e-4,
                                world_size=world, rank=rank, shard_optimizer=shard_opt,
                                fork_streams=args.fork, sm_reserve=args.sm_reserve,
-                               bucket_allreduce=args.bucket_allreduce)
+                               bucket_allreduce=args.bucket_allreduce, split_optimizer_step=args.split_step)
 
     def host_batch(st):
         return GraphBatch.from_states(st, pin=True, dense_mask=args.dense_mask)
@@ -673,6 +673,10 @@ def main():
                          "backward: per layer (default when given) or as one block ('mlp')")
     ap.add_argument("--sm-reserve", type=int, default=8,
                     help="N > 1: SMs the embedder backward leaves free for the concurrent NCCL kernels")
+    ap.add_argument("--split-step", dest="split_step", action="store_true",
+                    help="step the dense layers on the side stream while the embedder backward runs (measured: "
+                         "no gain, the embedder backward leaves no SM resources for it; default: one optimizer "
+                         "launch per network after its backward)")
     ap.add_argument("--no-fork", dest="fork", action="store_false",
                     help="run the three independent forward chains of the update on one stream")
     ap.add_argument("--shard-optimizer", action=argparse.BooleanOptionalAction, default=None,

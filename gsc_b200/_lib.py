@@ -71,6 +71,8 @@ _PROTOS = {
                                      c_float, c_float, c_float, c_float, c_int64, c_float, c_void_p]),
     "gsc_adam_soft_update_dev": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64,
                                          c_float, c_float, c_float, c_float, c_void_p, c_float, c_void_p]),
+    "gsc_adam_soft_update_slice": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64,
+                                           c_float, c_float, c_float, c_float, c_void_p, c_float, c_int, c_void_p]),
     "gsc_soft_update": (c_int, [c_void_p, c_void_p, c_int64, c_float, c_void_p]),
     "gsc_actor_head": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_int, c_float, c_float,
                                c_void_p, c_void_p]),

@@ -228,6 +228,25 @@ extern "C" int gsc_adam_soft_update_dev(float* p, const float* g, float* m, floa
   return GSC_OK;
 }
 
+extern "C" int gsc_adam_soft_update_slice(float* p, const float* g, float* m, float* v, float* target, int64_t n,
+                                          float lr, float beta1, float beta2, float eps, int64_t* step_dev, float tau,
+                                          int bump_step, void* stream) {
+  GSC_REQUIRE(p && g && m && v && step_dev && n >= 0, "gsc_adam_soft_update_slice: bad arguments");
+  if (n > 0) {
+    int64_t blocks = ceil_div(ceil_div(n, 4), 256);
+    const int64_t cap = 8LL * kNumSMs;
+    if (blocks > cap) blocks = cap;
+    adam_soft_dev_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(p, g, m, v, target, n, step_dev, lr, beta1, beta2,
+                                                                        eps, tau);
+    GSC_LAUNCH_CHECK("adam_soft_dev_kernel");
+  }
+  if (bump_step) {
+    adam_step_inc_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(step_dev);
+    GSC_LAUNCH_CHECK("adam_step_inc_kernel");
+  }
+  return GSC_OK;
+}
+
 extern "C" int gsc_td_mse(const float* rewards, const float* dones, const float* q_next, const float* q,
                           float gamma, float loss_scale, int64_t B, float* y, float* dq, float* loss,
                           void* stream) {

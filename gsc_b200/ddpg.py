@@ -33,7 +33,7 @@ class DDPGUpdater:
                  lr: float = 1e-3, gamma: float = 0.99, tau: float = 1e-4, betas=(0.9, 0.999),
                  eps: float = 1e-8, process_group=None, world_size: int = 1, rank: int = 0,
                  shard_optimizer: bool = False, global_batch: Optional[int] = None, fork_streams: bool = False,
-                 sm_reserve: int = 8, bucket_allreduce: bool = False):
+                 sm_reserve: int = 8, bucket_allreduce: bool = False, split_optimizer_step: bool = False):
         self.actor, self.qf1, self.target_actor, self.qf1_target = actor, qf1, target_actor, qf1_target
         self.lr, self.gamma, self.tau, self.betas, self.eps = lr, gamma, tau, betas, eps
         self.pg, self.world_size = process_group, int(world_size)
@@ -56,6 +56,7 @@ class DDPGUpdater:
         self.step_actor = 0
         self.step_critic = 0
         self.fork_streams = bool(fork_streams)
+        self.split_optimizer_step = bool(split_optimizer_step)
         self._side = None
         # Per-layer all-reduces behind the embedder backward (see _bucketed) pay on 2 GPUs (1.92 -> 1.85 ms)
         # but not on 8 (2.04 -> 2.10 ms: six collectives instead of two, and they compete with the
@@ -88,8 +89,32 @@ class DDPGUpdater:
             return lambda i: allreduce_flat(g[layers[0][0]:layers[-1][1]], self.pg) if i == 0 else None
         return lambda i: allreduce_flat(g[layers[i][0]:layers[i][1]], self.pg)
 
+    def _split_step(self) -> bool:
+        """Step the dense layers on the side stream while the embedder backward runs?  Needs their
+        gradients complete there: a single GPU, or the bucketed all-reduce on that stream."""
+        return self.fork_streams and self.split_optimizer_step and not self.shard and \
+            (self.world_size == 1 or self._bucketed())
+
+    def _mlp_step(self, net, target, g, m, v, step_dev):
+        """Adam + soft update of everything behind the embedder block (called on the side stream by
+        ``net_backward`` once the dense gradients are complete and the dense weights no longer read)."""
+        if not self._split_step():
+            return None
+        lo = net.grad_regions()[0][1]
+
+        def step():
+            ops.adam_soft_update_slice(net.flat[lo:], g[lo:], m[lo:], v[lo:], target.flat[lo:], self.lr,
+                                       self.betas[0], self.betas[1], self.eps, step_dev, self.tau, bump_step=False)
+        return step
+
     def _optimizer_step(self, net, target, g, gs, m, v, step_dev) -> None:
         """Gradient exchange + fused Adam + soft target update of one network."""
+        if self._split_step():                       # the dense layers were stepped by ``_mlp_step``
+            lo, hi = net.grad_regions()[0]
+            self._allreduce(g[lo:hi])
+            ops.adam_soft_update_slice(net.flat[:hi], g[:hi], m[:hi], v[:hi], target.flat[:hi], self.lr,
+                                       self.betas[0], self.betas[1], self.eps, step_dev, self.tau, bump_step=True)
+            return
         if not self.shard:
             if self._bucketed():
                 lo, hi = net.grad_regions()[0]
@@ -205,7 +230,8 @@ class DDPGUpdater:
         # ---- critic update (reference _update_critic, simple_ddpg.py:204-219) ----
         _, dq, q_loss = ops.td_mse(rewards, dones, q2, qv, self.gamma, scale)
         net_backward(q, q.flat, cur, ctx, dq.view(B, 1), self.g_critic, side=self._side[0],
-                     after_layer=self._layer_allreduce(q, self.g_critic))
+                     after_layer=self._layer_allreduce(q, self.g_critic),
+                     mlp_done=self._mlp_step(q, tq, self.g_critic, self.m_critic, self.v_critic, self.steps_dev[0:1]))
         self.step_critic += 1
         self._optimizer_step(q, tq, self.g_critic, self.gs_critic, self.m_critic, self.v_critic, self.steps_dev[0:1])
         # ---- actor update (reference _update_actor, :221-227) ----
@@ -222,7 +248,8 @@ class DDPGUpdater:
             self._neg_scale = scale
         dz = net_backward(q, q.flat, cur, ctx_q, self._neg, None, want_action_grad=True, action_grad_masked=True)
         net_backward(ac, ac.flat, cur, ctx_a, dz, self.g_actor, side=self._side[0],
-                     after_layer=self._layer_allreduce(ac, self.g_actor))
+                     after_layer=self._layer_allreduce(ac, self.g_actor),
+                     mlp_done=self._mlp_step(ac, ta, self.g_actor, self.m_actor, self.v_actor, self.steps_dev[1:2]))
         self.step_actor += 1
         self._optimizer_step(ac, ta, self.g_actor, self.gs_actor, self.m_actor, self.v_actor, self.steps_dev[1:2])
         a_loss = ops.colsum(q_pi) * (-scale)

@@ -353,7 +353,7 @@ def net_forward(net: _FlatNet, flat: torch.Tensor, gb: GraphBatch, action: Optio
 def net_backward(net: _FlatNet, flat: torch.Tensor, gb: GraphBatch, ctx, dz: torch.Tensor,
                  grad_flat: Optional[torch.Tensor], want_action_grad: bool = False,
                  action_grad_masked: bool = False, side: Optional[torch.cuda.Stream] = None,
-                 after_layer=None):
+                 after_layer=None, mlp_done=None):
     """Back-propagate ``dz`` (gradient w.r.t. the pre-mask MLP output).
 
     Writes parameter gradients into ``grad_flat`` (same layout as ``flat``) unless it is None, and
@@ -366,7 +366,9 @@ def net_backward(net: _FlatNet, flat: torch.Tensor, gb: GraphBatch, ctx, dz: tor
     persistent kernel whose last wave leaves more than half of the SMs idle, which the side stream's
     kernels fill.  The streams are joined before returning.  ``after_layer(i)`` is called on that
     stream once layer i's weight and bias gradients are enqueued (data parallelism all-reduces them
-    there, behind the embedder backward)."""
+    there, behind the embedder backward).  ``mlp_done()`` is called on that stream once every dense
+    layer's gradients are enqueued AND the current stream has read the dense weights for the last time
+    (the optimizer step of the dense layers then overlaps the embedder backward)."""
     embp, saved, inputs, hs, st = ctx
     main = torch.cuda.current_stream()
 
@@ -413,6 +415,12 @@ def net_backward(net: _FlatNet, flat: torch.Tensor, gb: GraphBatch, ctx, dz: tor
                 d_action = ops.linear_dgrad(d, Wp, pad + H + A, A, mul=mul, smask=sm)
             if grad_flat is not None:
                 d_embp = ops.linear_dgrad(d, Wp, 0, pad + H)
+                if mlp_done is not None and side is not None:
+                    reads_done = torch.cuda.Event()
+                    reads_done.record(main)             # last read of the dense weights on this stream
+                    with torch.cuda.stream(side):
+                        side.wait_event(reads_done)
+                        mlp_done()
                 rowptr, col, gptr = gb.csr()
                 ops.gnn_embed_bwd(gb.x, rowptr, col, gptr, gb.num_graphs, gb.max_nodes, gnn, H,
                                   net.embedder.num_layers, net.embedder.num_iter, saved, d_embp[:, pad:],

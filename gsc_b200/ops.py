@@ -482,6 +482,20 @@ def adam_soft_update_dev(p, g, m, v, target, lr, beta1, beta2, eps, step_dev: to
     _count(2)
 
 
+def adam_soft_update_slice(p, g, m, v, target, lr, beta1, beta2, eps, step_dev: torch.Tensor, tau: float,
+                           bump_step: bool):
+    """``adam_soft_update_dev`` over a slice of the flat buffers (pass the sliced views); the device
+    step counter is incremented only when ``bump_step`` (the last slice of the optimizer step)."""
+    for t in (p, g, m, v, target):
+        if t is not None and not t.is_contiguous():
+            raise _lib.GscError("adam_soft_update_slice needs flat contiguous buffers")
+    with _Timed(f"adam_soft_update[{int(p.numel())}]"):
+        check(_lib.load().gsc_adam_soft_update_slice(_ptr(p), _ptr(g), _ptr(m), _ptr(v), _ptr(target),
+                                                     int(p.numel()), lr, beta1, beta2, eps, _ptr(step_dev), tau,
+                                                     1 if bump_step else 0, _stream()), "gsc_adam_soft_update_slice")
+    _count((1 if p.numel() else 0) + (1 if bump_step else 0))
+
+
 def soft_update(p: torch.Tensor, target: torch.Tensor, tau: float):
     """target <- tau * p + (1 - tau) * target over flat contiguous buffers."""
     if not (p.is_contiguous() and target.is_contiguous()) or p.numel() != target.numel():

@@ -227,6 +227,15 @@ int gsc_adam_soft_update_dev(float* p, const float* g, float* m, float* v, float
                              float lr, float beta1, float beta2, float eps, int64_t* step_dev, float tau,
                              void* stream);
 
+/* The same update over a SLICE of the flat buffers (all five pointers already offset): a network's
+ * parameter groups can then be stepped as soon as their gradients are complete -- the dense layers
+ * while the embedder backward is still running -- and in any order.  Every slice of one optimizer
+ * step reads *step_dev + 1; the counter is incremented only by the call with bump_step != 0, which
+ * the caller orders after the other slices' launches (stream order or an event). */
+int gsc_adam_soft_update_slice(float* p, const float* g, float* m, float* v, float* target, int64_t n,
+                               float lr, float beta1, float beta2, float eps, int64_t* step_dev, float tau,
+                               int bump_step, void* stream);
+
 /* The soft target update alone, target <- tau*p + (1-tau)*target (reference
  * src/rlsp/agents/simple_ddpg.py:229-234), over a flat range: what a data-parallel rank with a sharded
  * optimizer applies to the parameter slices it received from the other ranks. */
