@@ -39,6 +39,7 @@ struct GnnArgs {
   const int32_t* stats;   // bwd: packer stats (stats[3] == 0 <=> symmetric graph), nullable
   const int32_t* flags;   // bwd: flags[0] != 0 <=> some chunk's edges exceed the gather kernel's shared memory
   int gather_kernel_launched;   // bwd: the out-edge gather kernel handles symmetric graphs
+  const uint16_t* prep;         // bwd gather kernel: per chunk [perm | rev] (gnn_chunk_prep_kernel)
   int64_t Nt;
   int64_t emb_ld;         // row stride of emb (fwd) / d_emb (bwd), floats
   int B, in_dim, H, num_convs, num_apps, G, cap;
@@ -1318,10 +1319,14 @@ template <int HP>
 struct GbL {
   static constexpr int kConvFloats = 2 * HP * HP + 4 * HP;     // Wl[c][k], Wr[c][k], bl, br, att, 0.4 att
   static constexpr int kSlotFloats = (kGbThreads / 32) * 2 * HP;   // per-warp d_att | d_bias sums, per conv
+  // Row stride of the two gathered row arrays: HP + 4 floats.  An odd number of 16-byte units spreads the
+  // rows of a random gather over all eight 16-byte bank groups (HP = 24 alone reaches only four of them),
+  // makes the MMA fragment loads conflict-free, and the pad of an xl row holds its score scalar p_j.
+  static constexpr int kRS = HP + 4;
   __host__ __device__ static constexpr size_t bytes(int num_convs) {
-    return (size_t)num_convs * (kConvFloats + kSlotFloats) * 4 + 2 * (size_t)kGbThreads * HP * 4 /*xl, g rows*/ +
-           (size_t)kGbThreads * 4 /*p*/ + ((size_t)kGbThreads + 4) * 4 /*rp*/ +
-           (size_t)kGbEdgesPerNode * kGbThreads * (4 + 4 + 4 + 2 + 2) + (size_t)kGbThreads * 2 /*perm*/ + 64 * 4;
+    return (size_t)num_convs * (kConvFloats + kSlotFloats) * 4 + 2 * (size_t)kGbThreads * kRS * 4 /*xl, g rows*/ +
+           ((size_t)kGbThreads + 4) * 4 /*rp*/ +
+           (size_t)kGbEdgesPerNode * kGbThreads * (4 + 4 + 4 + 2 + 2) + (size_t)kGbThreads * 2 /*perm*/;
   }
 };
 
@@ -1410,17 +1415,16 @@ __global__ void __launch_bounds__(kGbThreads, 4) gnn_bwd_gather_kernel(const Gnn
   extern __shared__ float4 smem4[];
   float* wsm = reinterpret_cast<float*>(smem4);                     // [num_convs][kConvFloats]
   float* slot_s = wsm + p.num_convs * L::kConvFloats;               // [num_convs][warps][2HP]
-  float* xl_s = slot_s + p.num_convs * L::kSlotFloats;              // [cap][HP] xl rows by node; step 4: MMA staging by slot
-  float* g_s = xl_s + cap * HP;                                     // [cap][HP] g rows by node; step 1: MMA staging by slot
-  float* p_s = g_s + cap * HP;                                      // [cap] 0.6 att.xl_j
-  int* rp_s = reinterpret_cast<int*>(p_s + cap);                    // [cap + 4]
+  constexpr int kRS = L::kRS;
+  float* xl_s = slot_s + p.num_convs * L::kSlotFloats;              // [cap][kRS] xl rows by node (+ 0.6 att.xl_j in the pad); step 4: MMA staging by slot
+  float* g_s = xl_s + cap * kRS;                                    // [cap][kRS] g rows by node; step 1: MMA staging by slot
+  int* rp_s = reinterpret_cast<int*>(g_s + cap * kRS);              // [cap + 4]
   float* es_s = reinterpret_cast<float*>(rp_s + cap + 4);           // [emax] score, then alpha
   float* eda_s = es_s + emax;                                       // [emax] g_i.xl_j, then d_score
   uint32_t* sb_s = reinterpret_cast<uint32_t*>(eda_s + emax);       // [emax] bit c: sign of xl_j,c + xr_i,c (LeakyReLU branch)
   uint16_t* col_s = reinterpret_cast<uint16_t*>(sb_s + emax);       // [emax]
   uint16_t* rev_s = col_s + emax;                                   // [emax]
   uint16_t* perm_s = rev_s + emax;                                  // [cap]
-  int* hist_s = reinterpret_cast<int*>(perm_s + cap);               // [64]
   if (p.stats == nullptr || p.stats[3] != 0 || p.flags[0] != 0) return;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int gid = lane >> 2, tig = lane & 3;
@@ -1456,40 +1460,16 @@ __global__ void __launch_bounds__(kGbThreads, 4) gnn_bwd_gather_kernel(const Gnn
     const int nbase = p.graph_ptr[g0];
     const int nc = p.graph_ptr[g1] - nbase;
     if (nc > cap) __trap();     // a graph larger than the max_nodes the launch was sized for: fail loudly
-    // chunk CSR -> shared memory, degree-sorted node order, reverse-edge index (see gnn_bwd_tc_kernel)
+    // chunk CSR -> shared memory; degree-sorted node order and reverse-edge index from gnn_chunk_prep_kernel
     const int ebase = p.rowptr[nbase];
-    const int ne = p.rowptr[nbase + nc] - ebase;            // <= emax (checked by gnn_chunk_edges_kernel)
+    const int ne = p.rowptr[nbase + nc] - ebase;            // <= emax (checked by gnn_chunk_prep_kernel)
+    const uint16_t* prep = p.prep + (size_t)chunk * (cap + emax);
     for (int i = tid; i <= nc; i += kGbThreads) rp_s[i] = p.rowptr[nbase + i] - ebase;
-    for (int e = tid; e < ne; e += kGbThreads) col_s[e] = (uint16_t)(p.col[ebase + e] - nbase);
-    if (tid < 64) hist_s[tid] = 0;
-    __syncthreads();
-    if (tid < nc) atomicAdd(hist_s + 63 - min(rp_s[tid + 1] - rp_s[tid], 63), 1);
-    __syncthreads();
-    if (warp == 0) {                                   // exclusive scan of the 64 buckets
-      int a0 = hist_s[2 * lane], a1 = hist_s[2 * lane + 1];
-      int incl = a0 + a1;
-#pragma unroll
-      for (int o = 1; o < 32; o <<= 1) {
-        const int t = __shfl_up_sync(0xffffffffu, incl, o);
-        if (lane >= o) incl += t;
-      }
-      hist_s[2 * lane] = incl - a0 - a1;
-      hist_s[2 * lane + 1] = incl - a1;
+    for (int e = tid; e < ne; e += kGbThreads) {
+      col_s[e] = (uint16_t)(p.col[ebase + e] - nbase);
+      rev_s[e] = prep[cap + e];
     }
-    __syncthreads();
-    if (tid < nc) perm_s[atomicAdd(hist_s + 63 - min(rp_s[tid + 1] - rp_s[tid], 63), 1)] = (uint16_t)tid;
-    if (tid < nc) {
-      const int e0 = rp_s[tid], e1 = rp_s[tid + 1];
-      for (int e = e0; e < e1; ++e) {
-        const int j = col_s[e];
-        int k = 0;
-        for (int q = e0; q < e; ++q) k += (col_s[q] == j);
-        int r = e;
-        for (int q = rp_s[j]; q < rp_s[j + 1]; ++q)
-          if (col_s[q] == tid && k-- == 0) { r = q; break; }
-        rev_s[e] = (uint16_t)r;
-      }
-    }
+    if (tid < nc) perm_s[tid] = prep[tid];
     __syncthreads();
 
     // this thread's node for the whole chunk (rows of similar length share a warp)
@@ -1521,7 +1501,7 @@ __global__ void __launch_bounds__(kGbThreads, 4) gnn_bwd_gather_kernel(const Gnn
       //         through the same slot rows ----
       float xr[HP];
       {
-        float* stage_rows = g_s + warp * 32 * HP;
+        float* stage_rows = g_s + warp * 32 * kRS;
         {
           float hin[HP];
 #pragma unroll
@@ -1534,7 +1514,7 @@ __global__ void __launch_bounds__(kGbThreads, 4) gnn_bwd_gather_kernel(const Gnn
               load_row<HP>(p.saved + ((size_t)(a - 1) * p.Nt + node) * HP, hin);
             }
           }
-          store_row<HP>(stage_rows + lane * HP, hin);
+          store_row<HP>(stage_rows + lane * kRS, hin);
         }
         __syncwarp();
         float acc[2][2 * HP / 8][4];
@@ -1544,8 +1524,8 @@ __global__ void __launch_bounds__(kGbThreads, 4) gnn_bwd_gather_kernel(const Gnn
           for (int nt = 0; nt < 2 * HP / 8; ++nt)
 #pragma unroll
             for (int q = 0; q < 4; ++q) acc[mt][nt][q] = 0.f;
-        if (a == 0 && p.in_dim <= 8) warp_gemm_3xtf32<1, 2 * HP / 8, HP>(acc, stage_rows, w, HP, 1, lane);
-        else warp_gemm_3xtf32<HP / 8, 2 * HP / 8, HP>(acc, stage_rows, w, HP, 1, lane);
+        if (a == 0 && p.in_dim <= 8) warp_gemm_3xtf32<1, 2 * HP / 8, kRS>(acc, stage_rows, w, HP, 1, lane);
+        else warp_gemm_3xtf32<HP / 8, 2 * HP / 8, kRS>(acc, stage_rows, w, HP, 1, lane);
         __syncwarp();                                    // every lane is done reading the staged rows
         // rows (16 mt + gid) and (+ 8), channels 8 nt + 2 tig (+ 1): nt < HP/8 is xl, the rest xr
 #pragma unroll
@@ -1564,18 +1544,18 @@ __global__ void __launch_bounds__(kGbThreads, 4) gnn_bwd_gather_kernel(const Gnn
               const float v0 = acc[mt][nt][2 * hrow] + vec[(is_r ? HP : 0) + ch];
               const float v1 = acc[mt][nt][2 * hrow + 1] + vec[(is_r ? HP : 0) + ch + 1];
               if (is_r) {
-                *reinterpret_cast<float2*>(stage_rows + sl * HP + ch) = make_float2(v0, v1);
+                *reinterpret_cast<float2*>(stage_rows + sl * kRS + ch) = make_float2(v0, v1);
               } else {
                 pl = fmaf(vec[2 * HP + ch], v0, fmaf(vec[2 * HP + ch + 1], v1, pl));
-                if (live) *reinterpret_cast<float2*>(xl_s + ni * HP + ch) = make_float2(v0, v1);
+                if (live) *reinterpret_cast<float2*>(xl_s + ni * kRS + ch) = make_float2(v0, v1);
               }
             }
             pl += __shfl_xor_sync(0xffffffffu, pl, 1);
             pl += __shfl_xor_sync(0xffffffffu, pl, 2);
-            if (live && tig == 0) p_s[ni] = 0.6f * pl;                  // score scalar p_j
+            if (live && tig == 0) xl_s[ni * kRS + HP] = 0.6f * pl;                  // score scalar p_j
           }
         __syncwarp();
-        load_row<HP>(stage_rows + lane * HP, xr);
+        load_row<HP>(stage_rows + lane * kRS, xr);
         // g = relu'(out) d_out / deg of the own node; conv-bias gradient
         float dbias[HP];
 #pragma unroll
@@ -1603,7 +1583,7 @@ __global__ void __launch_bounds__(kGbThreads, 4) gnn_bwd_gather_kernel(const Gnn
 #pragma unroll
       for (int c = 0; c < HP; ++c) { datt[c] = 0.f; vown[c] = 0.f; }
       if (active) {
-        store_row<HP>(g_s + i * HP, g);                  // read by the neighbours' source passes (after the next barrier)
+        store_row<HP>(g_s + i * kRS, g);                  // read by the neighbours' source passes (after the next barrier)
         float sg[HP];
         const float q_i = 0.6f * dot4<HP>(*reinterpret_cast<const float(*)[HP]>(vec + 2 * HP), xr);
         float m = -INFINITY;
@@ -1611,7 +1591,7 @@ __global__ void __launch_bounds__(kGbThreads, 4) gnn_bwd_gather_kernel(const Gnn
         for (int e = e0; e < e1; ++e) {
           const int j = col_s[e];
           float v[HP];
-          load_row<HP>(xl_s + j * HP, v);
+          load_row<HP>(xl_s + j * kRS, v);
           float s0 = 0.f, s1 = 0.f, d0 = 0.f, d1 = 0.f;
           uint32_t bits = 0;
 #pragma unroll
@@ -1624,7 +1604,7 @@ __global__ void __launch_bounds__(kGbThreads, 4) gnn_bwd_gather_kernel(const Gnn
             if (t0 < 0.f) bits |= 1u << c;
             if (t1 < 0.f) bits |= 2u << c;
           }
-          const float sc_e = p_s[j] + q_i + (s0 + s1);
+          const float sc_e = xl_s[j * kRS + HP] + q_i + (s0 + s1);
           es_s[e] = sc_e;
           eda_s[e] = d0 + d1;
           sb_s[e] = bits;
@@ -1661,7 +1641,7 @@ __global__ void __launch_bounds__(kGbThreads, 4) gnn_bwd_gather_kernel(const Gnn
           sg[c] = vec[2 * HP + c] * wv;                  // d_xr
         }
         store_row<HP>(dxa + HP, sg);                     // read back in step 4 (registers are short at 4 CTAs per SM)
-        load_row<HP>(xl_s + i * HP, vown);               // own xl row for the source pass: xl_s is free after the barrier
+        load_row<HP>(xl_s + i * kRS, vown);               // own xl row for the source pass: xl_s is free after the barrier
       }
       warp_colsum_add<HP>(datt, lane, slot);             // target half of d_att
 #pragma unroll
@@ -1684,7 +1664,7 @@ __global__ void __launch_bounds__(kGbThreads, 4) gnn_bwd_gather_kernel(const Gnn
           const float alpha = es_s[r], ds = eda_s[r];
           const uint32_t bits = sb_s[r];
           float gi[HP];
-          load_row<HP>(g_s + ti * HP, gi);
+          load_row<HP>(g_s + ti * kRS, gi);
           ds_sum += ds;
 #pragma unroll
           for (int c = 0; c < HP; ++c) {
@@ -1706,7 +1686,7 @@ __global__ void __launch_bounds__(kGbThreads, 4) gnn_bwd_gather_kernel(const Gnn
       //         operand rows are staged in this warp's slot rows of xl_s (no xl row is read after the last
       //         barrier), and the result rows return to their owners the same way ----
       if (a > 0) {
-        float* stage_rows = xl_s + warp * 32 * HP;
+        float* stage_rows = xl_s + warp * 32 * kRS;
         float acc[2][HP / 8][4];
 #pragma unroll
         for (int mt = 0; mt < 2; ++mt)
@@ -1714,9 +1694,9 @@ __global__ void __launch_bounds__(kGbThreads, 4) gnn_bwd_gather_kernel(const Gnn
           for (int nt = 0; nt < HP / 8; ++nt)
 #pragma unroll
             for (int q = 0; q < 4; ++q) acc[mt][nt][q] = 0.f;
-        store_row<HP>(stage_rows + lane * HP, dxl);
+        store_row<HP>(stage_rows + lane * kRS, dxl);
         __syncwarp();
-        warp_gemm_3xtf32<HP / 8, HP / 8, HP>(acc, stage_rows, w, 1, HP, lane);               // B(k = c, n) = Wl[c][n]
+        warp_gemm_3xtf32<HP / 8, HP / 8, kRS>(acc, stage_rows, w, 1, HP, lane);               // B(k = c, n) = Wl[c][n]
         __syncwarp();
         {
           float dxr[HP];
@@ -1729,20 +1709,20 @@ __global__ void __launch_bounds__(kGbThreads, 4) gnn_bwd_gather_kernel(const Gnn
               dxr[4 * c4] = t4.x; dxr[4 * c4 + 1] = t4.y; dxr[4 * c4 + 2] = t4.z; dxr[4 * c4 + 3] = t4.w;
             }
           }
-          store_row<HP>(stage_rows + lane * HP, dxr);
+          store_row<HP>(stage_rows + lane * kRS, dxr);
         }
         __syncwarp();
-        warp_gemm_3xtf32<HP / 8, HP / 8, HP>(acc, stage_rows, w + HP * HP, 1, HP, lane);     // ... + d_xr Wr
+        warp_gemm_3xtf32<HP / 8, HP / 8, kRS>(acc, stage_rows, w + HP * HP, 1, HP, lane);     // ... + d_xr Wr
         __syncwarp();
 #pragma unroll
         for (int mt = 0; mt < 2; ++mt)
 #pragma unroll
           for (int nt = 0; nt < HP / 8; ++nt) {
-            *reinterpret_cast<float2*>(stage_rows + (16 * mt + gid) * HP + 8 * nt + 2 * tig) = make_float2(acc[mt][nt][0], acc[mt][nt][1]);
-            *reinterpret_cast<float2*>(stage_rows + (16 * mt + 8 + gid) * HP + 8 * nt + 2 * tig) = make_float2(acc[mt][nt][2], acc[mt][nt][3]);
+            *reinterpret_cast<float2*>(stage_rows + (16 * mt + gid) * kRS + 8 * nt + 2 * tig) = make_float2(acc[mt][nt][0], acc[mt][nt][1]);
+            *reinterpret_cast<float2*>(stage_rows + (16 * mt + 8 + gid) * kRS + 8 * nt + 2 * tig) = make_float2(acc[mt][nt][2], acc[mt][nt][3]);
           }
         __syncwarp();
-        load_row<HP>(stage_rows + lane * HP, g);
+        load_row<HP>(stage_rows + lane * kRS, g);
       }
       __syncthreads();        // the rows are rewritten by the next application / chunk
     }
@@ -1938,6 +1918,80 @@ __global__ void gnn_chunk_edges_kernel(const int32_t* __restrict__ rowptr, const
   }
 }
 
+// Per-chunk index work of the gather backward, which depends on the topology only, done once per launch
+// instead of once per resident CTA pass: for every chunk of G graphs
+//   perm[slot] : the chunk's nodes by descending degree (stable: ties by node index, so the slot of a
+//                node -- and with it every fp32 summation order in the gather kernel -- is deterministic);
+//   rev[e]     : for CSR entry e = (j -> i) of row i, the entry of row j that holds (i -> j) (the k-th
+//                duplicate maps to the k-th duplicate), i.e. where the target pass of i leaves what the
+//                source pass of j needs.
+// Layout: prep[chunk][kGbThreads + emax] uint16.  flags[0] := 1 if a chunk does not fit (the scatter
+// kernel then handles the batch).
+__global__ void __launch_bounds__(128)
+gnn_chunk_prep_kernel(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col,
+                      const int32_t* __restrict__ graph_ptr, int B, int G, int cap, int emax,
+                      int32_t* __restrict__ flags, uint16_t* __restrict__ prep) {
+  extern __shared__ int prep_smem[];
+  int* rp_s = prep_smem;                                           // [cap + 1]
+  int* cnt_s = rp_s + cap + 1;                                     // [4 warps][65] nodes per degree bucket
+  int* start_s = cnt_s + 4 * 65;                                   // [64]
+  uint16_t* col_s = reinterpret_cast<uint16_t*>(start_s + 64);     // [emax]
+  const int tid = threadIdx.x;
+  const int num_chunks = (B + G - 1) / G;
+  for (int chunk = blockIdx.x; chunk < num_chunks; chunk += gridDim.x) {
+    const int g0 = chunk * G, g1 = min(B, g0 + G);
+    const int nbase = graph_ptr[g0], nc = graph_ptr[g1] - nbase;
+    const int ebase = rowptr[nbase], ne = rowptr[nbase + nc] - ebase;
+    if (nc > cap || ne > emax) {                                   // uniform per CTA
+      if (tid == 0) flags[0] = 1;
+      continue;
+    }
+    uint16_t* out = prep + (size_t)chunk * (cap + emax);
+    for (int i = tid; i <= nc; i += blockDim.x) rp_s[i] = rowptr[nbase + i] - ebase;
+    for (int e = tid; e < ne; e += blockDim.x) col_s[e] = (uint16_t)(col[ebase + e] - nbase);
+    __syncthreads();
+    // stable counting sort by descending degree (bucket 63 - min(deg, 63)): per-warp bucket counts from
+    // match.any, bucket starts from a scan over the 64 buckets, position = start + earlier warps + earlier lanes
+    const int warp = tid >> 5, lane = tid & 31;
+    const int i = tid;                                             // cap == blockDim.x: one node per thread
+    const int bkt = i < nc ? 63 - min(rp_s[i + 1] - rp_s[i], 63) : 64;
+    for (int t = tid; t < 4 * 65; t += blockDim.x) cnt_s[t] = 0;
+    __syncthreads();
+    const uint32_t same = __match_any_sync(0xffffffffu, bkt);
+    if ((same & ((1u << lane) - 1u)) == 0) cnt_s[warp * 65 + bkt] = __popc(same);     // first lane of its group
+    __syncthreads();
+    if (warp == 0) {                                               // exclusive scan of the bucket totals (2 per lane)
+      int t0 = 0, t1 = 0;
+      for (int w = 0; w < 4; ++w) { t0 += cnt_s[w * 65 + 2 * lane]; t1 += cnt_s[w * 65 + 2 * lane + 1]; }
+      int incl = t0 + t1;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += t;
+      }
+      start_s[2 * lane] = incl - t0 - t1;
+      start_s[2 * lane + 1] = incl - t1;
+    }
+    __syncthreads();
+    if (i < nc) {
+      int pos = start_s[bkt] + __popc(same & ((1u << lane) - 1u));
+      for (int w = 0; w < warp; ++w) pos += cnt_s[w * 65 + bkt];
+      out[pos] = (uint16_t)i;
+      const int e0 = rp_s[i], e1 = rp_s[i + 1];
+      for (int e = e0; e < e1; ++e) {
+        const int j = col_s[e];
+        int k = 0;
+        for (int q = e0; q < e; ++q) k += (col_s[q] == j);
+        int r = e;
+        for (int q = rp_s[j]; q < rp_s[j + 1]; ++q)
+          if (col_s[q] == i && k-- == 0) { r = q; break; }
+        out[cap + e] = (uint16_t)r;
+      }
+    }
+    __syncthreads();
+  }
+}
+
 // d_params[t] = sum of the CTA partials, in a fixed order: block = 32 parameters x 8 partial-lanes,
 // lane r adds the partials r, r + 8, ... (independent loads in flight), then the lanes are added.
 // Sums the partial rows in a fixed order.  When the gather kernel ran (same run-time condition as in
@@ -2112,17 +2166,24 @@ static int launch_bwd_both(GnnArgs a, int max_nodes, float* d_params, cudaStream
   int grid = grid_f, rows_w = 0;
   GSC_CUDA_TRY(cudaMemsetAsync(const_cast<int32_t*>(a.flags), 0, sizeof(int32_t), st));
   const size_t smem_g = GbL<HP>::bytes(a.num_convs);
-  const bool gather_fma = gnn_bwd_variant() != 1 && a.stats != nullptr && max_nodes <= kGbThreads &&
-                          kGbCtasPerSm * (smem_g + 1024) <= 227 * 1024;
+  // resident CTAs per SM: four when the shared-memory layout allows (two convs at HP = 24), else fewer
+  int gb_ctas = (int)((227 * 1024) / (smem_g + 1024));
+  if (gb_ctas > kGbCtasPerSm) gb_ctas = kGbCtasPerSm;
+  const bool gather_fma = gnn_bwd_variant() != 1 && a.stats != nullptr && max_nodes <= kGbThreads && gb_ctas >= 1;
   if (gather_fma) {
     GnnArgs t = a;
     t.cap = kGbThreads;
-    t.G = graphs_per_cta(kGbThreads, max_nodes, t.B, kGbCtasPerSm);
+    t.G = graphs_per_cta(kGbThreads, max_nodes, t.B, gb_ctas);
     const int chunks_t = (t.B + t.G - 1) / t.G;
-    gnn_chunk_edges_kernel<<<(chunks_t + 255) / 256, 256, 0, st>>>(t.rowptr, t.graph_ptr, t.B, t.G,
-                                                                   kGbEdgesPerNode * kGbThreads, const_cast<int32_t*>(a.flags));
-    GSC_LAUNCH_CHECK("gnn_chunk_edges_kernel");
-    int grid_g = kGbCtasPerSm * (kNumSMs - sm_reserve());
+    {
+      constexpr int emax = kGbEdgesPerNode * kGbThreads;
+      const int smem_p = (kGbThreads + 1 + 4 * 65 + 64) * 4 + emax * 2;
+      gnn_chunk_prep_kernel<<<chunks_t < 8 * kNumSMs ? chunks_t : 8 * kNumSMs, 128, smem_p, st>>>(
+          t.rowptr, t.col, t.graph_ptr, t.B, t.G, kGbThreads, emax, const_cast<int32_t*>(a.flags),
+          const_cast<uint16_t*>(a.prep));
+      GSC_LAUNCH_CHECK("gnn_chunk_prep_kernel");
+    }
+    int grid_g = gb_ctas * (kNumSMs - sm_reserve());
     if (chunks_t < grid_g) grid_g = chunks_t;
     grid = grid_g > grid_f ? grid_g : grid_f;       // one partial row per CTA of either kernel
     GSC_CUDA_TRY(cudaFuncSetAttribute(gnn_bwd_gather_kernel<HP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_g));
@@ -2236,11 +2297,17 @@ static size_t bwd_dx_bytes(int64_t Nt, int H, int num_layers, int num_iter) {
   return ((size_t)num_apps_of(num_layers, num_iter) * (size_t)Nt * 2 * pick_hp(H) * 4 + 255) / 256 * 256;
 }
 
+// [perm | rev] of every chunk of the gather backward (at most one chunk per graph)
+static size_t bwd_prep_bytes(int64_t B, int max_nodes) {
+  if (max_nodes > kGbThreads) return 0;
+  return ((size_t)(B > 0 ? B : 1) * (kGbThreads + kGbEdgesPerNode * kGbThreads) * 2 + 255) / 256 * 256;
+}
+
 extern "C" size_t gsc_gnn_bwd_workspace_bytes(int64_t Nt, int64_t B, int max_nodes, int in_dim, int H, int num_layers,
                                               int num_iter) {
-  (void)B;
   if (Nt < 0 || max_nodes < 1 || H < 1 || H > GSC_MAX_HIDDEN || num_layers < 1 || num_iter < 0) return 0;
-  size_t bytes = bwd_partials_bytes(in_dim, H, num_layers) + kBwdFlagBytes + bwd_dx_bytes(Nt, H, num_layers, num_iter);
+  size_t bytes = bwd_partials_bytes(in_dim, H, num_layers) + kBwdFlagBytes + bwd_prep_bytes(B, max_nodes) +
+                 bwd_dx_bytes(Nt, H, num_layers, num_iter);
   if (bwd_rows_in_global(max_nodes, H, num_layers)) {
     const size_t cap = ((size_t)max_nodes + 31) / 32 * 32;
     bytes += (size_t)kNumSMs * 5 * cap * pick_hp(H) * 4;
@@ -2264,7 +2331,9 @@ extern "C" int gsc_gnn_embed_bwd(const float* x, int64_t Nt, int in_dim, const i
                 gsc_gnn_bwd_workspace_bytes(Nt, B, max_nodes, in_dim, H, num_layers, num_iter));
   a.saved = const_cast<float*>(saved); a.d_emb = d_emb; a.partials = (float*)workspace;
   a.flags = reinterpret_cast<const int32_t*>(static_cast<uint8_t*>(workspace) + bwd_partials_bytes(in_dim, H, num_layers));
-  a.dx = reinterpret_cast<float*>(static_cast<uint8_t*>(workspace) + bwd_partials_bytes(in_dim, H, num_layers) + kBwdFlagBytes);
+  a.prep = reinterpret_cast<const uint16_t*>(static_cast<uint8_t*>(workspace) + bwd_partials_bytes(in_dim, H, num_layers) + kBwdFlagBytes);
+  a.dx = reinterpret_cast<float*>(static_cast<uint8_t*>(workspace) + bwd_partials_bytes(in_dim, H, num_layers) + kBwdFlagBytes +
+                                  bwd_prep_bytes(B, max_nodes));
   a.rows_ws = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(a.dx) + bwd_dx_bytes(Nt, H, num_layers, num_iter));
   a.dbg = g_gnn_debug;
   a.stats = pack_stats;
