@@ -283,6 +283,28 @@ def test_adam_soft_update_matches_torch_adam():
     np.testing.assert_allclose(p2.cpu().numpy(), p0.float().numpy() - 1e-3, rtol=0, atol=2e-6)
 
 
+def test_adam_soft_update_slices_equal_one_launch():
+    """Two slices of one optimizer step (the second bumps the device step counter) == one launch over
+    the whole buffer, bit for bit, over several steps."""
+    gen = torch.Generator().manual_seed(5)
+    n, cut = 70001, 1280
+    p0, t0 = torch.randn(n, generator=gen).to(DEV), torch.randn(n, generator=gen).to(DEV)
+    state = lambda: [p0.clone(), torch.zeros(n, device=DEV), torch.zeros(n, device=DEV), t0.clone(),
+                     torch.zeros(1, dtype=torch.int64, device=DEV)]
+    pa, ma, va, ta, sa = state()
+    pb, mb, vb, tb, sb = state()
+    for step in range(3):
+        g = torch.randn(n, generator=gen).to(DEV)
+        ops.adam_soft_update_dev(pa, g, ma, va, ta, 1e-3, 0.9, 0.999, 1e-8, sa, 1e-2)
+        ops.adam_soft_update_slice(pb[cut:], g[cut:], mb[cut:], vb[cut:], tb[cut:], 1e-3, 0.9, 0.999, 1e-8, sb, 1e-2,
+                                   bump_step=False)
+        ops.adam_soft_update_slice(pb[:cut], g[:cut], mb[:cut], vb[:cut], tb[:cut], 1e-3, 0.9, 0.999, 1e-8, sb, 1e-2,
+                                   bump_step=True)
+    assert int(sa.item()) == int(sb.item()) == 3
+    for a, b in ((pa, pb), (ma, mb), (va, vb), (ta, tb)):
+        assert torch.equal(a, b)
+
+
 def test_td_mse():
     gen = torch.Generator().manual_seed(4)
     B = 1500
