@@ -74,6 +74,10 @@ _PROTOS = {
     "gsc_adam_soft_update_slice": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64,
                                            c_float, c_float, c_float, c_float, c_void_p, c_float, c_int, c_void_p]),
     "gsc_soft_update": (c_int, [c_void_p, c_void_p, c_int64, c_float, c_void_p]),
+    "gsc_linear_n1_fwd": (c_int, [c_void_p, c_int64, c_int64, c_int, c_void_p, c_void_p, c_void_p, c_int64, c_void_p]),
+    "gsc_linear_n1_bwd_workspace_bytes": (c_size_t, [c_int]),
+    "gsc_linear_n1_bwd": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_int64, c_int, c_void_p, c_int, c_void_p,
+                                  c_int64, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
     "gsc_actor_head": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_int, c_float, c_float,
                                c_void_p, c_void_p]),
 }

@@ -8,7 +8,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libgsc_b200.so")
-SOURCES = ["common.cu", "pack_csr.cu", "gnn_embed.cu", "gemm.cu", "gemm_tc.cu", "optim.cu", "actor_head.cu", "replay.cu", "smask.cu", "observe.cu"]
+SOURCES = ["common.cu", "pack_csr.cu", "gnn_embed.cu", "gemm.cu", "gemm_tc.cu", "linear_n1.cu", "optim.cu", "actor_head.cu", "replay.cu", "smask.cu", "observe.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "--fmad=true"]
 

@@ -16,15 +16,39 @@ constexpr int kScanThreads = 256;
 constexpr int kScanItems = 4;
 constexpr int kScanTile = kScanThreads * kScanItems;  // 1024 rows per scan block
 
+__device__ __forceinline__ void pack_graph_ptr_body(const int64_t* __restrict__ batch, int64_t Nt, int64_t B,
+                                                    int32_t* __restrict__ graph_ptr, int32_t* __restrict__ stats) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (batch == nullptr) {
+    if (i == 0) { graph_ptr[0] = 0; for (int64_t g = 1; g <= B; ++g) graph_ptr[g] = (int32_t)Nt; }
+    return;
+  }
+  if (Nt == 0) {
+    for (; i <= B; i += (int64_t)gridDim.x * blockDim.x) graph_ptr[i] = 0;
+    return;
+  }
+  for (; i < Nt; i += (int64_t)gridDim.x * blockDim.x) {
+    int64_t b = batch[i];
+    int64_t prev = (i > 0) ? batch[i - 1] : -1;
+    if (b < 0 || b >= B) { atomicOr(stats + 2, 2); continue; }
+    if (b < prev) { atomicOr(stats + 2, 4); continue; }
+    for (int64_t g = prev + 1; g <= b; ++g) graph_ptr[g] = (int32_t)i;  // empty graphs too
+    if (i == Nt - 1)
+      for (int64_t g = b + 1; g <= B; ++g) graph_ptr[g] = (int32_t)Nt;
+  }
+}
 __global__ void pack_init_kernel(int32_t* __restrict__ deg, int64_t Nt, int32_t* __restrict__ stats) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i == 0) { stats[0] = 0; stats[1] = 0; stats[2] = 0; stats[3] = 0; }
   for (; i < Nt; i += (int64_t)gridDim.x * blockDim.x) deg[i] = 1;  // the self-loop
 }
 
+// In-degrees; the same launch derives graph_ptr from the (sorted) batch vector -- both only need the
+// stats words zeroed by pack_init_kernel.
 __global__ void pack_count_kernel(const int64_t* __restrict__ ei, int64_t E, int64_t Nt,
                                   const int64_t* __restrict__ batch, int32_t* __restrict__ deg,
-                                  int32_t* __restrict__ stats) {
+                                  int32_t* __restrict__ stats, int64_t B, int32_t* __restrict__ graph_ptr) {
+  pack_graph_ptr_body(batch, Nt, B, graph_ptr, stats);
   for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < E;
        e += (int64_t)gridDim.x * blockDim.x) {
     int64_t s = ei[e], d = ei[E + e];
@@ -96,6 +120,48 @@ __global__ void __launch_bounds__(1024) pack_scan_blocks_kernel(int32_t* __restr
   if (threadIdx.x == 0) blocksum[nb] = carry_s;
 }
 
+// Small batches (nb <= kFusedScanBlocks scan tiles): one launch instead of three.  Block b adds up the tile
+// totals in front of it itself (nb loads per block), finishes its tile of rowptr, zeroes the cursors;
+// block 0 also writes the grand total, and every block folds its share of the graphs into max_nodes.
+constexpr int kFusedScanBlocks = 2048;
+__global__ void __launch_bounds__(kScanThreads)
+pack_scan_finish_kernel(int32_t* __restrict__ rowptr, int32_t* __restrict__ cursor, const int32_t* __restrict__ blocksum,
+                        int64_t Nt, int nb, int32_t* __restrict__ stats, const int32_t* __restrict__ graph_ptr, int64_t B) {
+  __shared__ int32_t red[kScanThreads / 32];
+  __shared__ int32_t offs_s[2];
+  int32_t before = 0, all = 0;
+  for (int j = threadIdx.x; j < nb; j += kScanThreads) {
+    const int32_t v = blocksum[j];
+    all += v;
+    if (j < (int)blockIdx.x) before += v;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    before += __shfl_xor_sync(0xffffffffu, before, o);
+    all += __shfl_xor_sync(0xffffffffu, all, o);
+  }
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (lane == 0) red[warp] = before;
+  __syncthreads();
+  if (threadIdx.x == 0) { int32_t t = 0; for (int w = 0; w < kScanThreads / 32; ++w) t += red[w]; offs_s[0] = t; }
+  __syncthreads();
+  if (lane == 0) red[warp] = all;
+  __syncthreads();
+  if (threadIdx.x == 0) { int32_t t = 0; for (int w = 0; w < kScanThreads / 32; ++w) t += red[w]; offs_s[1] = t; }
+  __syncthreads();
+  const int32_t off = offs_s[0];
+  if (blockIdx.x == 0 && threadIdx.x == 0) { rowptr[Nt] = offs_s[1]; stats[0] = offs_s[1]; }
+  const int64_t base = (int64_t)blockIdx.x * kScanTile;
+  for (int k = threadIdx.x; k < kScanTile; k += kScanThreads)
+    if (base + k < Nt) { rowptr[base + k] += off; cursor[base + k] = 0; }
+  int32_t m = 0;
+  for (int64_t g = (int64_t)blockIdx.x * kScanThreads + threadIdx.x; g < B; g += (int64_t)gridDim.x * kScanThreads)
+    m = max(m, graph_ptr[g + 1] - graph_ptr[g]);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
+  if (lane == 0 && m > 0) atomicMax(stats + 1, m);
+}
+
 // rowptr += block offset; cursor (the deg array) := 0; rowptr[Nt] and stats[0] := total.
 __global__ void pack_scan_add_kernel(int32_t* __restrict__ rowptr, int32_t* __restrict__ cursor,
                                      const int32_t* __restrict__ blocksum, int64_t Nt, int nb,
@@ -121,65 +187,74 @@ __global__ void pack_fill_kernel(const int64_t* __restrict__ ei, int64_t E, int6
   }
 }
 
-// One thread per row: sort the neighbour sources ascending, put the self-loop last.
+// One thread per row: sort the neighbour sources ascending, put the self-loop last.  Rows of up to 16
+// neighbours are sorted in registers (two dependent global round trips per row instead of one per
+// compare/swap: this kernel is pure latency).
 __global__ void pack_rows_kernel(const int32_t* __restrict__ rowptr, int32_t* __restrict__ col, int64_t Nt) {
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < Nt;
        i += (int64_t)gridDim.x * blockDim.x) {
-    int lo = rowptr[i], hi = rowptr[i + 1] - 1;
-    for (int a = lo + 1; a < hi; ++a) {
-      int32_t key = col[a];
-      int b = a - 1;
-      while (b >= lo && col[b] > key) { col[b + 1] = col[b]; --b; }
-      col[b + 1] = key;
+    const int lo = rowptr[i], hi = rowptr[i + 1] - 1;
+    const int n = hi - lo;
+    if (n <= 16) {
+      int32_t v[16];
+#pragma unroll
+      for (int k = 0; k < 16; ++k) v[k] = k < n ? col[lo + k] : INT32_MAX;
+#pragma unroll
+      for (int pass = 0; pass < 16; ++pass) {            // odd-even transposition sort, fully unrolled
+        if (pass >= n) break;
+#pragma unroll
+        for (int k = pass & 1; k + 1 < 16; k += 2) {
+          const int32_t a = v[k], b = v[k + 1];
+          v[k] = min(a, b);
+          v[k + 1] = max(a, b);
+        }
+      }
+#pragma unroll
+      for (int k = 0; k < 16; ++k)
+        if (k < n) col[lo + k] = v[k];
+    } else {
+      for (int a = lo + 1; a < hi; ++a) {
+        int32_t key = col[a];
+        int b = a - 1;
+        while (b >= lo && col[b] > key) { col[b + 1] = col[b]; --b; }
+        col[b + 1] = key;
+      }
     }
     col[hi] = (int32_t)i;
   }
 }
 
 // stats[3] := 1 unless the packed graph is symmetric (every edge s->d has as many reverse edges
-// d->s).  Rows are sorted, so the reverse edge is found by binary search.  The embedder backward
-// uses the flag to read a node's out-edges from the same CSR instead of scattering with atomics.
-__global__ void pack_symmetry_kernel(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col,
-                                     int64_t Nt, int32_t* __restrict__ stats) {
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < Nt;
-       i += (int64_t)gridDim.x * blockDim.x) {
-    const int lo = rowptr[i], hi = rowptr[i + 1] - 1;            // neighbours, self-loop excluded
-    int a = lo;
-    while (a < hi) {
-      const int32_t s = col[a];
-      int b = a + 1;
-      while (b < hi && col[b] == s) ++b;                          // multiplicity of s in row i
-      const int slo = rowptr[s], shi = rowptr[s + 1] - 1;
-      int l = slo, r = shi;                                       // lower bound of i in row s
-      while (l < r) { const int m = (l + r) >> 1; if (col[m] < (int32_t)i) l = m + 1; else r = m; }
-      int cnt = 0;
-      while (l + cnt < shi && col[l + cnt] == (int32_t)i) ++cnt;
-      if (cnt != b - a) { atomicOr(stats + 3, 1); return; }
-      a = b;
-    }
+// d->s).  The embedder backward uses the flag to read a node's out-edges from the same CSR instead of
+// scattering with atomics.  One thread per INPUT edge (s, d): with the rows sorted, the multiplicity of
+// s in row d and of d in row s are two short binary searches -- a chain of ~8 dependent loads per
+// thread, where one thread per row walked all its neighbours one after the other.
+__device__ __forceinline__ int pack_count_in_row(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col,
+                                                 int64_t row, int32_t key) {
+  int l = rowptr[row];
+  const int hi = rowptr[row + 1] - 1;                             // self-loop excluded
+  int r = hi;
+  while (l < r) { const int m = (l + r) >> 1; if (col[m] < key) l = m + 1; else r = m; }
+  int cnt = 0;
+  while (l + cnt < hi && col[l + cnt] == key) ++cnt;
+  return cnt;
+}
+__global__ void pack_symmetry_kernel(const int64_t* __restrict__ ei, int64_t E, int64_t Nt,
+                                     const int64_t* __restrict__ batch, const int32_t* __restrict__ rowptr,
+                                     const int32_t* __restrict__ col, int32_t* __restrict__ stats) {
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < E;
+       e += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t s = ei[e], d = ei[E + e];
+    if (s < 0 || s >= Nt || d < 0 || d >= Nt || s == d) continue;           // dropped by the packer
+    if (batch != nullptr && batch[s] != batch[d]) continue;
+    if (pack_count_in_row(rowptr, col, d, (int32_t)s) != pack_count_in_row(rowptr, col, s, (int32_t)d))
+      atomicOr(stats + 3, 1);
   }
 }
 
 __global__ void pack_graph_ptr_kernel(const int64_t* __restrict__ batch, int64_t Nt, int64_t B,
                                       int32_t* __restrict__ graph_ptr, int32_t* __restrict__ stats) {
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (batch == nullptr) {
-    if (i == 0) { graph_ptr[0] = 0; for (int64_t g = 1; g <= B; ++g) graph_ptr[g] = (int32_t)Nt; }
-    return;
-  }
-  if (Nt == 0) {
-    for (; i <= B; i += (int64_t)gridDim.x * blockDim.x) graph_ptr[i] = 0;
-    return;
-  }
-  for (; i < Nt; i += (int64_t)gridDim.x * blockDim.x) {
-    int64_t b = batch[i];
-    int64_t prev = (i > 0) ? batch[i - 1] : -1;
-    if (b < 0 || b >= B) { atomicOr(stats + 2, 2); continue; }
-    if (b < prev) { atomicOr(stats + 2, 4); continue; }
-    for (int64_t g = prev + 1; g <= b; ++g) graph_ptr[g] = (int32_t)i;  // empty graphs too
-    if (i == Nt - 1)
-      for (int64_t g = b + 1; g <= B; ++g) graph_ptr[g] = (int32_t)Nt;
-  }
+  pack_graph_ptr_body(batch, Nt, B, graph_ptr, stats);
 }
 
 __global__ void pack_max_nodes_kernel(const int32_t* __restrict__ graph_ptr, int64_t B,
@@ -226,18 +301,32 @@ extern "C" int gsc_pack_csr(const int64_t* edge_index, int64_t E, const int64_t*
   int nb = (int)ceil_div(Nt > 0 ? Nt : 1, kScanTile);
   int32_t* blocksum = (int32_t*)((char*)workspace + align_up((size_t)(Nt > 0 ? Nt : 1) * 4, 256));
 
+  // 7 launches for batches of up to kFusedScanBlocks * 1024 nodes (10 beyond): init | in-degrees + graph_ptr |
+  // tile scan | offsets + cursors + max_nodes | fill | row sort | symmetry
   pack_init_kernel<<<flat_grid(Nt, 256), 256, 0, st>>>(deg, Nt, stats);
   GSC_LAUNCH_CHECK("pack_init_kernel");
   if (E > 0) {
-    pack_count_kernel<<<flat_grid(E, 256), 256, 0, st>>>(edge_index, E, Nt, batch, deg, stats);
+    const int64_t work = E > Nt ? E : Nt;
+    pack_count_kernel<<<flat_grid(work, 256), 256, 0, st>>>(edge_index, E, Nt, batch, deg, stats, B, graph_ptr);
     GSC_LAUNCH_CHECK("pack_count_kernel");
+  } else {
+    int64_t gp_n = (batch == nullptr) ? 1 : (Nt > 0 ? Nt : B + 1);
+    pack_graph_ptr_kernel<<<flat_grid(gp_n, 256), 256, 0, st>>>(batch, Nt, B, graph_ptr, stats);
+    GSC_LAUNCH_CHECK("pack_graph_ptr_kernel");
   }
   pack_scan_local_kernel<<<nb, kScanThreads, 0, st>>>(deg, Nt, rowptr, blocksum);
   GSC_LAUNCH_CHECK("pack_scan_local_kernel");
-  pack_scan_blocks_kernel<<<1, 1024, 0, st>>>(blocksum, nb);
-  GSC_LAUNCH_CHECK("pack_scan_blocks_kernel");
-  pack_scan_add_kernel<<<flat_grid(Nt, 256), 256, 0, st>>>(rowptr, deg, blocksum, Nt, nb, stats);
-  GSC_LAUNCH_CHECK("pack_scan_add_kernel");
+  if (nb <= kFusedScanBlocks) {
+    pack_scan_finish_kernel<<<nb, kScanThreads, 0, st>>>(rowptr, deg, blocksum, Nt, nb, stats, graph_ptr, B);
+    GSC_LAUNCH_CHECK("pack_scan_finish_kernel");
+  } else {
+    pack_scan_blocks_kernel<<<1, 1024, 0, st>>>(blocksum, nb);
+    GSC_LAUNCH_CHECK("pack_scan_blocks_kernel");
+    pack_scan_add_kernel<<<flat_grid(Nt, 256), 256, 0, st>>>(rowptr, deg, blocksum, Nt, nb, stats);
+    GSC_LAUNCH_CHECK("pack_scan_add_kernel");
+    pack_max_nodes_kernel<<<flat_grid(B, 256), 256, 0, st>>>(graph_ptr, B, stats);
+    GSC_LAUNCH_CHECK("pack_max_nodes_kernel");
+  }
   if (E > 0) {
     pack_fill_kernel<<<flat_grid(E, 256), 256, 0, st>>>(edge_index, E, Nt, batch, rowptr, deg, col);
     GSC_LAUNCH_CHECK("pack_fill_kernel");
@@ -246,15 +335,10 @@ extern "C" int gsc_pack_csr(const int64_t* edge_index, int64_t E, const int64_t*
     pack_rows_kernel<<<flat_grid(Nt, 128), 128, 0, st>>>(rowptr, col, Nt);
     GSC_LAUNCH_CHECK("pack_rows_kernel");
   }
-  if (Nt > 0) {
-    pack_symmetry_kernel<<<flat_grid(Nt, 128), 128, 0, st>>>(rowptr, col, Nt, stats);
+  if (E > 0) {
+    pack_symmetry_kernel<<<flat_grid(E, 256), 256, 0, st>>>(edge_index, E, Nt, batch, rowptr, col, stats);
     GSC_LAUNCH_CHECK("pack_symmetry_kernel");
   }
-  int64_t gp_n = (batch == nullptr) ? 1 : (Nt > 0 ? Nt : B + 1);
-  pack_graph_ptr_kernel<<<flat_grid(gp_n, 256), 256, 0, st>>>(batch, Nt, B, graph_ptr, stats);
-  GSC_LAUNCH_CHECK("pack_graph_ptr_kernel");
-  pack_max_nodes_kernel<<<flat_grid(B, 256), 256, 0, st>>>(graph_ptr, B, stats);
-  GSC_LAUNCH_CHECK("pack_max_nodes_kernel");
   return GSC_OK;
 }
 

@@ -299,6 +299,11 @@ def first_layer_table(net: _FlatNet, flat: torch.Tensor, gb: GraphBatch) -> Opti
     return ops.mask_table(Wp[:, pad + H:pad + H + A], gb.n_max, gb.groups)
 
 
+def _single_unit(W: torch.Tensor) -> bool:
+    """A dense layer with one output unit and a K the fused head kernels take (ops.linear_n1_*)."""
+    return ops.fuse_head and int(W.shape[0]) == 1 and int(W.shape[1]) <= 1024 and W.stride(1) == 1
+
+
 def net_forward(net: _FlatNet, flat: torch.Tensor, gb: GraphBatch, action: Optional[torch.Tensor],
                 save: bool, mask_output: bool = False, clamp1: bool = False,
                 save_gnn: Optional[bool] = None, table: Optional[torch.Tensor] = None,
@@ -341,6 +346,8 @@ def net_forward(net: _FlatNet, flat: torch.Tensor, gb: GraphBatch, action: Optio
             offs = [0] + ([pad + H + A] if action is not None else [])
             h = ops.linear_fwd(ins, Wp, b, relu=not last, mul=out_mul, clamp1=clamp1 and last,
                                col_offsets=offs, row_table=(table, gb.n_nodes), smask=out_smask)
+        elif last and i > 0 and _single_unit(W) and out_mul is None and out_smask is None and not clamp1:
+            h = ops.linear_n1_fwd(h, W, b)             # the critic's head: one launch, no GEMM machinery
         else:
             h = ops.linear_fwd(inputs if i == 0 else [h], Wp if i == 0 else W, b, relu=not last,
                                mul=out_mul, clamp1=clamp1 and last, smask=out_smask)
@@ -392,6 +399,15 @@ def net_backward(net: _FlatNet, flat: torch.Tensor, gb: GraphBatch, ctx, dz: tor
     for i in range(len(lins) - 1, -1, -1):
         W, _, Wp, pad = lins[i]
         keep.append(d)
+        if i == len(lins) - 1 and i > 0 and _single_unit(W):
+            # head with one output unit: input gradient (through the ReLU below), weight and bias gradient
+            # in one launch on this stream
+            d = ops.linear_n1_bwd(d, hs[i - 1], W, relu_input=True,
+                                  dW=g_lins[i][0] if grad_flat is not None else None,
+                                  db=g_lins[i][1] if grad_flat is not None else None)
+            if grad_flat is not None and after_layer is not None:
+                weight_grads(lambda i=i: after_layer(i))
+            continue
         if grad_flat is not None:
             def layer_grads(i=i, d=d, pad=pad):
                 if i == 0 and st:

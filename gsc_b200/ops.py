@@ -28,6 +28,9 @@ EPI_TF32 = 32
 EPI_TF32X3 = 256
 # Use the node counts instead of the dense mask whenever a batch carries them (GraphBatch.structured).
 use_structured_mask = True
+# Layers with one output unit (the critic's head) through the fused one-launch kernels (linear_n1.cu)
+# instead of gsc_gemm; False restores the GEMM route (tests compare the two).
+fuse_head = True
 
 
 class use_precision:
@@ -63,8 +66,10 @@ def _need_cuda(*ts):
             raise _lib.GscError("gsc_b200 ops need CUDA tensors (there is no CPU fallback)")
 
 
-def workspace(nbytes: int, device, tag: str = "main") -> Tuple[Optional[torch.Tensor], int]:
-    """Grow-only scratch buffer per (device, tag, stream); the library itself never allocates."""
+def workspace(nbytes: int, device, tag: str = "main", zeroed: bool = False) -> Tuple[Optional[torch.Tensor], int]:
+    """Grow-only scratch buffer per (device, tag, stream); the library itself never allocates.
+    ``zeroed``: allocated as zeros (for kernels that keep a self-resetting counter in it; the tag must
+    then be theirs alone)."""
     if nbytes <= 0:
         return None, 0
     # one buffer per stream: launches on different streams may run concurrently (DDPGUpdater forks the
@@ -72,9 +77,18 @@ def workspace(nbytes: int, device, tag: str = "main") -> Tuple[Optional[torch.Te
     key = (torch.device(device).index, tag, _stream())
     ws = _workspaces.get(key)
     if ws is None or ws.numel() < nbytes:
-        ws = torch.empty(int(nbytes * 1.25) + 256, dtype=torch.uint8, device=device)
+        ws = (torch.zeros if zeroed else torch.empty)(int(nbytes * 1.25) + 256, dtype=torch.uint8, device=device)
         _workspaces[key] = ws
     return ws, ws.numel()
+
+
+def _pack_launches(num_nodes: int, E: int) -> int:
+    """Kernels one gsc_pack_csr call launches (pack_csr.cu: fused scan finish up to 2048 scan tiles)."""
+    small = (max(int(num_nodes), 1) + 1023) // 1024 <= 2048
+    scan = 2 if small else 4                    # tile scan + (finish | block scan, add, max_nodes)
+    if E > 0:
+        return 1 + 1 + scan + 3                 # init, count(+graph_ptr), scan, fill, rows, symmetry
+    return 1 + 1 + scan + (1 if num_nodes > 0 else 0)
 
 
 def _count(n: int):
@@ -142,7 +156,7 @@ def pack_csr(edge_index: torch.Tensor, batch: Optional[torch.Tensor], num_nodes:
         check(lib.gsc_pack_csr(_ptr(edge_index), E, _ptr(batch), num_nodes, num_graphs, _ptr(rowptr),
                                _ptr(col), _ptr(graph_ptr), _ptr(stats), _ptr(ws), wsn, _stream()),
               "gsc_pack_csr")
-    _count(10 if E > 0 else 8)
+    _count(_pack_launches(num_nodes, E))
     return rowptr, col, graph_ptr, stats
 
 
@@ -173,7 +187,7 @@ def pack_csr_noalloc(edge_index: torch.Tensor, batch: Optional[torch.Tensor], nu
         check(lib.gsc_pack_csr_noalloc(_ptr(edge_index), E, _ptr(batch), num_nodes, num_graphs, _ptr(rowptr),
                                        _ptr(col), _ptr(graph_ptr), _ptr(stats), _stream()),
               "gsc_pack_csr_noalloc")
-    _count(10 if E > 0 else 8)
+    _count(_pack_launches(num_nodes, E))
     return rowptr, col, graph_ptr, stats
 
 
@@ -395,6 +409,41 @@ def linear_wgrad(dY: torch.Tensor, inputs: List[torch.Tensor], dW: torch.Tensor)
         gemm_raw([seg], N, K, dW[:, off:off + K], 0, tag="linear_wgrad")
         off += K
     return dW
+
+
+def linear_n1_fwd(h: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor]) -> torch.Tensor:
+    """h @ weight.T + bias for a layer with ONE output unit (weight [1, K]): one launch, one warp per row."""
+    h = _row_major(h, "linear_n1_fwd h")
+    M, K = int(h.shape[0]), int(h.shape[1])
+    if tuple(weight.shape) != (1, K) or weight.stride(1) != 1:
+        raise _lib.GscError(f"linear_n1_fwd: weight must be [1, {K}] with unit column stride")
+    out = torch.empty(M, 1, dtype=torch.float32, device=h.device)
+    with _Timed(f"linear_n1_fwd[{M}x1x{K}]"):
+        check(_lib.load().gsc_linear_n1_fwd(_ptr(h), _ld(h), M, K, _ptr(weight), _ptr(bias), _ptr(out), 1, _stream()),
+              "gsc_linear_n1_fwd")
+    _count(1)
+    return out
+
+
+def linear_n1_bwd(dq: torch.Tensor, h: torch.Tensor, weight: torch.Tensor, relu_input: bool,
+                  want_dh: bool = True, dW: Optional[torch.Tensor] = None, db: Optional[torch.Tensor] = None):
+    """Backward of ``linear_n1_fwd`` in one launch: returns d_h [M, K] (gated by h > 0 if ``relu_input``)
+    or None, and writes dW [1, K] / db [1] in place when given."""
+    h = _row_major(h, "linear_n1_bwd h")
+    M, K = int(h.shape[0]), int(h.shape[1])
+    if dq.numel() != M:
+        raise _lib.GscError("linear_n1_bwd: dq must hold one value per row")
+    lib = _lib.load()
+    d_h = torch.empty(M, K, dtype=torch.float32, device=h.device) if want_dh else None
+    ws, wsn = (None, 0)
+    if dW is not None or db is not None:
+        ws, wsn = workspace(lib.gsc_linear_n1_bwd_workspace_bytes(K), h.device, "linear_n1", zeroed=True)
+    ld_dq = int(dq.stride(0)) if dq.dim() >= 1 and dq.shape[0] > 1 else 1
+    with _Timed(f"linear_n1_bwd[{M}x{K}x1]"):
+        check(lib.gsc_linear_n1_bwd(_ptr(dq), ld_dq, _ptr(h), _ld(h), M, K, _ptr(weight), 1 if relu_input else 0,
+                                    _ptr(d_h), K, _ptr(dW), _ptr(db), _ptr(ws), wsn, _stream()), "gsc_linear_n1_bwd")
+    _count(1)
+    return d_h
 
 
 def mul_gate(x: torch.Tensor, mul: Optional[torch.Tensor] = None, gate: Optional[torch.Tensor] = None):

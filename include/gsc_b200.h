@@ -212,6 +212,23 @@ int gsc_td_mse(const float* rewards, const float* dones, const float* q_next, co
                float gamma, float loss_scale, int64_t B, float* y, float* dq, float* loss,
                void* stream);
 
+/* ---- dense layer with one output unit (the critic's head) -------------------------------------
+ * reference src/rlsp/agents/models.py:119-122 with critic_hidden_layer_nodes = [64]: Linear(64, 1).
+ * forward : out[i * ld_out] = sum_k h[i, k] w[k] + bias[0]                  (bias may be NULL)
+ * backward: d_h[i, k] = dq[i * ld_dq] * w[k], zeroed where h[i, k] <= 0 if relu_input (h is the ReLU
+ *           output of the layer below); dW[k] = sum_i dq[i] h[i, k]; db[0] = sum_i dq[i].
+ *           d_h, dW and db may each be NULL.  One launch; the row-block partials of dW / db are added
+ *           in block order by the block that finishes last, so the sums are deterministic.
+ * Workspace of the backward (needed for dW / db): gsc_linear_n1_bwd_workspace_bytes(K) bytes whose
+ * first 4 bytes are ZERO before the first call and which no other work touches in between (the
+ * kernel leaves them zero again): keep one such buffer per stream.  K <= 1024. */
+int gsc_linear_n1_fwd(const float* h, int64_t ld_h, int64_t M, int K, const float* w, const float* bias,
+                      float* out, int64_t ld_out, void* stream);
+size_t gsc_linear_n1_bwd_workspace_bytes(int K);
+int gsc_linear_n1_bwd(const float* dq, int64_t ld_dq, const float* h, int64_t ld_h, int64_t M, int K,
+                      const float* w, int relu_input, float* d_h, int64_t ld_dh, float* dW, float* db,
+                      void* workspace, size_t workspace_bytes, void* stream);
+
 /* ---- fused Adam + soft target update ------------------------------------------------------
  * torch 1.13 Adam (reference src/rlsp/agents/simple_ddpg.py:162-163,217,225) followed by
  * target <- tau*p + (1-tau)*target (reference :229-234) over one flat parameter buffer.

@@ -283,6 +283,32 @@ def test_adam_soft_update_matches_torch_adam():
     np.testing.assert_allclose(p2.cpu().numpy(), p0.float().numpy() - 1e-3, rtol=0, atol=2e-6)
 
 
+def test_linear_n1_head_matches_fp64_and_gemm_route():
+    """The fused one-output-unit layer (critic head) against an fp64 reference and against the GEMM
+    route it replaces; repeated calls reuse the self-resetting counter."""
+    gen = torch.Generator().manual_seed(11)
+    for M, K in ((1024, 64), (37, 64), (1, 5), (300, 1000)):
+        h = torch.relu(torch.randn(M, K, generator=gen)).to(DEV)
+        W = (torch.randn(1, K, generator=gen) / 8).to(DEV)
+        b = torch.randn(1, generator=gen).to(DEV)
+        dq = torch.randn(M, 1, generator=gen).to(DEV)
+        q = ops.linear_n1_fwd(h, W, b)
+        q_ref = h.double() @ W.double().t() + b.double()
+        assert rel_err(q.cpu().numpy(), q_ref.cpu().numpy()) < 2e-6
+        q_gemm = ops.linear_fwd([h], W, b)
+        assert rel_err(q.cpu().numpy(), q_gemm.cpu().numpy()) < 2e-6
+        for rep in range(3):
+            dW, db = torch.full((1, K), 7.0, device=DEV), torch.full((1,), 7.0, device=DEV)
+            d_h = ops.linear_n1_bwd(dq, h, W, relu_input=True, dW=dW, db=db)
+            dh_ref = torch.where(h > 0, dq.double() @ W.double(), torch.zeros((), dtype=torch.float64, device=DEV))
+            assert rel_err(d_h.cpu().numpy(), dh_ref.cpu().numpy()) < 1e-6
+            assert rel_err(dW.cpu().numpy(), (dq.double().t() @ h.double()).cpu().numpy()) < 2e-6
+            assert rel_err(db.cpu().numpy(), dq.double().sum().reshape(1).cpu().numpy()) < 2e-6
+        assert torch.equal(d_h, ops.linear_dgrad(dq, W, 0, K, gate=h))       # same products, same gate
+        only = ops.linear_n1_bwd(dq, h, W, relu_input=False, want_dh=True)
+        assert rel_err(only.cpu().numpy(), (dq.double() @ W.double()).cpu().numpy()) < 1e-6
+
+
 def test_adam_soft_update_slices_equal_one_launch():
     """Two slices of one optimizer step (the second bumps the device step counter) == one launch over
     the whole buffer, bit for bit, over several steps."""

@@ -20,7 +20,7 @@ python bench.py --no-graph --steps 2 --warmup 3 > $O/plain_c3.log 2>&1 && \
     python bench.py --no-graph --steps 2 --warmup 3 > $O/ncu_c3.log 2>&1
 # full capture of the hot kernels of one c3 step (after the three warm-up steps)
 timeout 1200 ncu --set full --clock-control none --import-source on \
-  -k regex:"gemm_tc_kernel|gnn_bwd_gather_kernel|gnn_wgrad_kernel|gnn_fwd_tc_kernel|adam_soft_dev|mask_table|mask_wgrad|colsum" -s 150 -c 60 \
+  -k regex:"gemm_tc_kernel|gnn_bwd_gather_kernel|gnn_wgrad_kernel|gnn_fwd_tc_kernel|adam_soft_dev|mask_table|mask_wgrad|colsum" -s 108 -c 72 \
   -o $O/r2_full_c3 -f python bench.py --no-graph --steps 2 --warmup 3 > $O/ncu_full_c3.log 2>&1
 # the report itself is too large to travel back (64 MiB limit): keep its CSV pages and the summary
 ncu -i $O/r2_full_c3.ncu-rep --page raw --csv > $O/r2_ncu_full_c3_raw.csv 2>/dev/null
@@ -28,4 +28,6 @@ python tools/ncu_traffic.py $O/r2_ncu_full_c3_raw.csv c3_b1024_tf32x3 > $O/r2_fu
 cp profiles/r2_traffic.json $O/r2_traffic.json
 ncu -i $O/r2_full_c3.ncu-rep --page source --csv -k regex:gnn_bwd_gather_kernel -c 1 > $O/r2_src_gnn_bwd_gather.csv 2>/dev/null
 rm -f $O/r2_full_c3.ncu-rep
+python tools/gemm_probe.py none > $O/r2_gemm_roles.log 2>&1
+python tools/gnn_bwd_only.py > $O/r2_gnn_entry.log 2>&1
 ls -la $O | tail -24
