@@ -55,6 +55,12 @@ _PROTOS = {
     "gsc_gnn_embed_bwd": (c_int, [c_void_p, c_int64, c_int, c_void_p, c_void_p, c_void_p, c_int64,
                                   c_int, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_int64, c_void_p,
                                   c_void_p, c_void_p, c_size_t, c_void_p]),
+    "gsc_gnn_embed_bwd_prepared": (c_int, [c_void_p, c_int64, c_int, c_void_p, c_void_p, c_void_p, c_int64,
+                                           c_int, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_int64, c_void_p,
+                                           c_void_p, c_void_p, c_size_t, c_void_p, c_void_p]),
+    "gsc_gnn_bwd_prep_bytes": (c_size_t, [c_int64, c_int]),
+    "gsc_gnn_bwd_prep": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_void_p, c_size_t,
+                                 c_void_p]),
     "gsc_gemm_workspace_bytes": (c_size_t, [c_int64, c_int64, c_int64]),
     "gsc_gemm": (c_int, [POINTER(GemmArgs), c_int64, c_int64, c_void_p, c_int64, c_void_p, c_size_t,
                          c_void_p]),

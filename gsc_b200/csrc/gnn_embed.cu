@@ -1313,6 +1313,7 @@ __global__ void __launch_bounds__(kGnnThreads, 1) gnn_bwd_tc_kernel(const GnnArg
 constexpr int kGbEdgeUnroll = GSC_EDGE_UNROLL;   // edge loops of the gather kernel
 constexpr int kGbThreads = 128;
 constexpr int kGbEdgesPerNode = 6;       // per-edge arrays per node slot (self-loops included)
+constexpr size_t kBwdFlagBytes = 256;    // kernel-selection flags, between the partials and the node-row scratch
 constexpr int kGbCtasPerSm = 4;          // resident CTAs per SM the shared-memory layout and register budget are sized for
 
 template <int HP>
@@ -2154,7 +2155,7 @@ static bool plan_bwd_tc(const GnnArgs& a, int max_nodes, int* cap, int* cols, si
 }
 
 template <int HP>
-static int launch_bwd_both(GnnArgs a, int max_nodes, float* d_params, cudaStream_t st) {
+static int launch_bwd_both(GnnArgs a, int max_nodes, float* d_params, const void* prep_ext, cudaStream_t st) {
   // atomic (any graph) kernel geometry
   size_t smem_f = (2 * (size_t)a.num_convs * ConvLayout<HP>::kFloats + 5 * (size_t)a.cap * HP) * 4;
   const bool global_rows = smem_f > 227 * 1024;
@@ -2164,18 +2165,25 @@ static int launch_bwd_both(GnnArgs a, int max_nodes, float* d_params, cudaStream
   size_t smem_t = 0;
   const bool tc = gnn_use_tc() && a.stats != nullptr && plan_bwd_tc<HP>(a, max_nodes, &cap_t, &cols, &smem_t);
   int grid = grid_f, rows_w = 0;
-  GSC_CUDA_TRY(cudaMemsetAsync(const_cast<int32_t*>(a.flags), 0, sizeof(int32_t), st));
   const size_t smem_g = GbL<HP>::bytes(a.num_convs);
   // resident CTAs per SM: four when the shared-memory layout allows (two convs at HP = 24), else fewer
   int gb_ctas = (int)((227 * 1024) / (smem_g + 1024));
   if (gb_ctas > kGbCtasPerSm) gb_ctas = kGbCtasPerSm;
   const bool gather_fma = gnn_bwd_variant() != 1 && a.stats != nullptr && max_nodes <= kGbThreads && gb_ctas >= 1;
+  // the chunk index work (gsc_gnn_bwd_prep) may come with the batch: [flag word, 256 B][perm | rev per chunk]
+  const bool ext = prep_ext != nullptr && gather_fma;
+  if (ext) {
+    a.flags = static_cast<const int32_t*>(prep_ext);
+    a.prep = reinterpret_cast<const uint16_t*>(static_cast<const uint8_t*>(prep_ext) + kBwdFlagBytes);
+  } else {
+    GSC_CUDA_TRY(cudaMemsetAsync(const_cast<int32_t*>(a.flags), 0, sizeof(int32_t), st));
+  }
   if (gather_fma) {
     GnnArgs t = a;
     t.cap = kGbThreads;
     t.G = graphs_per_cta(kGbThreads, max_nodes, t.B, gb_ctas);
     const int chunks_t = (t.B + t.G - 1) / t.G;
-    {
+    if (!ext) {
       constexpr int emax = kGbEdgesPerNode * kGbThreads;
       const int smem_p = (kGbThreads + 1 + 4 * 65 + 64) * 4 + emax * 2;
       gnn_chunk_prep_kernel<<<chunks_t < 8 * kNumSMs ? chunks_t : 8 * kNumSMs, 128, smem_p, st>>>(
@@ -2282,7 +2290,6 @@ extern "C" int gsc_gnn_embed_fwd(const float* x, int64_t Nt, int in_dim, const i
 static size_t bwd_partials_bytes(int in_dim, int H, int num_layers) {   // one row per CTA, up to 4 CTAs per SM
   return ((size_t)4 * kNumSMs * (size_t)conv_param_offset(num_layers, in_dim, H) * 4 + 255) / 256 * 256;
 }
-constexpr size_t kBwdFlagBytes = 256;    // kernel-selection flags, between the partials and the node-row scratch
 static bool bwd_rows_in_global(int max_nodes, int H, int num_layers) {
   const int hp = pick_hp(H);
   const size_t cap = max_nodes <= kGnnThreads ? kGnnThreads : ((size_t)max_nodes + 31) / 32 * 32;
@@ -2315,12 +2322,12 @@ extern "C" size_t gsc_gnn_bwd_workspace_bytes(int64_t Nt, int64_t B, int max_nod
   return bytes;
 }
 
-extern "C" int gsc_gnn_embed_bwd(const float* x, int64_t Nt, int in_dim, const int32_t* rowptr,
-                                 const int32_t* col, const int32_t* graph_ptr, int64_t B, int max_nodes,
-                                 const float* params, int H, int num_layers, int num_iter,
-                                 const float* saved, const float* d_emb, int64_t d_emb_ld, float* d_params,
-                                 const int32_t* pack_stats, void* workspace, size_t workspace_bytes,
-                                 void* stream) {
+static int gnn_bwd_impl(const float* x, int64_t Nt, int in_dim, const int32_t* rowptr,
+                        const int32_t* col, const int32_t* graph_ptr, int64_t B, int max_nodes,
+                        const float* params, int H, int num_layers, int num_iter,
+                        const float* saved, const float* d_emb, int64_t d_emb_ld, float* d_params,
+                        const int32_t* pack_stats, void* workspace, size_t workspace_bytes,
+                        const void* prep_ext, void* stream) {
   GnnArgs a{};
   int rc = build_args(a, x, Nt, in_dim, rowptr, col, graph_ptr, B, max_nodes, params, H, num_layers, num_iter);
   if (rc) return rc;
@@ -2339,9 +2346,67 @@ extern "C" int gsc_gnn_embed_bwd(const float* x, int64_t Nt, int in_dim, const i
   a.stats = pack_stats;
   cudaStream_t st = (cudaStream_t)stream;
   switch (pick_hp(H)) {
-    case 8: return launch_bwd_both<8>(a, max_nodes, d_params, st);
-    case 16: return launch_bwd_both<16>(a, max_nodes, d_params, st);
-    case 24: return launch_bwd_both<24>(a, max_nodes, d_params, st);
-    default: return launch_bwd_both<32>(a, max_nodes, d_params, st);
+    case 8: return launch_bwd_both<8>(a, max_nodes, d_params, prep_ext, st);
+    case 16: return launch_bwd_both<16>(a, max_nodes, d_params, prep_ext, st);
+    case 24: return launch_bwd_both<24>(a, max_nodes, d_params, prep_ext, st);
+    default: return launch_bwd_both<32>(a, max_nodes, d_params, prep_ext, st);
   }
+}
+
+extern "C" int gsc_gnn_embed_bwd(const float* x, int64_t Nt, int in_dim, const int32_t* rowptr,
+                                 const int32_t* col, const int32_t* graph_ptr, int64_t B, int max_nodes,
+                                 const float* params, int H, int num_layers, int num_iter,
+                                 const float* saved, const float* d_emb, int64_t d_emb_ld, float* d_params,
+                                 const int32_t* pack_stats, void* workspace, size_t workspace_bytes,
+                                 void* stream) {
+  return gnn_bwd_impl(x, Nt, in_dim, rowptr, col, graph_ptr, B, max_nodes, params, H, num_layers, num_iter, saved,
+                      d_emb, d_emb_ld, d_params, pack_stats, workspace, workspace_bytes, nullptr, stream);
+}
+
+extern "C" int gsc_gnn_embed_bwd_prepared(const float* x, int64_t Nt, int in_dim, const int32_t* rowptr,
+                                          const int32_t* col, const int32_t* graph_ptr, int64_t B, int max_nodes,
+                                          const float* params, int H, int num_layers, int num_iter,
+                                          const float* saved, const float* d_emb, int64_t d_emb_ld, float* d_params,
+                                          const int32_t* pack_stats, void* workspace, size_t workspace_bytes,
+                                          const void* prep, void* stream) {
+  return gnn_bwd_impl(x, Nt, in_dim, rowptr, col, graph_ptr, B, max_nodes, params, H, num_layers, num_iter, saved,
+                      d_emb, d_emb_ld, d_params, pack_stats, workspace, workspace_bytes, prep, stream);
+}
+
+// Geometry of the gather backward for (hidden, num_layers, max_nodes, B): resident CTAs per SM and graphs per chunk
+static bool gather_geometry(int H, int num_layers, int max_nodes, int64_t B, int* G) {
+  if (max_nodes > kGbThreads || max_nodes < 1 || num_layers < 1 || H < 1 || H > GSC_MAX_HIDDEN) return false;
+  const int hp = pick_hp(H);
+  const size_t smem_g = hp == 8 ? GbL<8>::bytes(num_layers) : hp == 16 ? GbL<16>::bytes(num_layers)
+                      : hp == 24 ? GbL<24>::bytes(num_layers) : GbL<32>::bytes(num_layers);
+  int ctas = (int)((227 * 1024) / (smem_g + 1024));
+  if (ctas > kGbCtasPerSm) ctas = kGbCtasPerSm;
+  if (ctas < 1) return false;
+  *G = graphs_per_cta(kGbThreads, max_nodes, (int)B, ctas);
+  return true;
+}
+
+extern "C" size_t gsc_gnn_bwd_prep_bytes(int64_t B, int max_nodes) {
+  const size_t body = bwd_prep_bytes(B, max_nodes);
+  return body ? kBwdFlagBytes + body : 0;
+}
+
+extern "C" int gsc_gnn_bwd_prep(const int32_t* rowptr, const int32_t* col, const int32_t* graph_ptr, int64_t B,
+                                int max_nodes, int H, int num_layers, void* prep, size_t prep_bytes, void* stream) {
+  GSC_REQUIRE(rowptr && col && graph_ptr && prep && B >= 1 && B < INT32_MAX, "gsc_gnn_bwd_prep: bad arguments");
+  int G = 1;
+  GSC_REQUIRE(gather_geometry(H, num_layers, max_nodes, B, &G),
+              "gsc_gnn_bwd_prep: no gather backward for max_nodes=%d hidden=%d layers=%d", max_nodes, H, num_layers);
+  if (prep_bytes < gsc_gnn_bwd_prep_bytes(B, max_nodes))
+    return fail(GSC_EWORKSPACE, "gsc_gnn_bwd_prep: buffer %zu < %zu", prep_bytes, gsc_gnn_bwd_prep_bytes(B, max_nodes));
+  cudaStream_t st = (cudaStream_t)stream;
+  GSC_CUDA_TRY(cudaMemsetAsync(prep, 0, sizeof(int32_t), st));
+  constexpr int emax = kGbEdgesPerNode * kGbThreads;
+  const int smem_p = (kGbThreads + 1 + 4 * 65 + 64) * 4 + emax * 2;
+  const int chunks = (int)((B + G - 1) / G);
+  gnn_chunk_prep_kernel<<<chunks < 8 * kNumSMs ? chunks : 8 * kNumSMs, 128, smem_p, st>>>(
+      rowptr, col, graph_ptr, (int)B, G, kGbThreads, emax, static_cast<int32_t*>(prep),
+      reinterpret_cast<uint16_t*>(static_cast<uint8_t*>(prep) + kBwdFlagBytes));
+  GSC_LAUNCH_CHECK("gnn_chunk_prep_kernel");
+  return GSC_OK;
 }

@@ -220,6 +220,8 @@ class DDPGUpdater:
             ev = torch.cuda.Event(); ev.record(self._side[0]); joins.append(ev)
         with torch.cuda.stream(self._side[1]):
             self._side[1].wait_event(fork)
+            # index work of the two embedder backward passes over `cur`: off the critical path, here
+            cur.bwd_prep(ac.embedder.hidden_dim, ac.embedder.num_layers)
             a, ctx_a = net_forward(ac, ac.flat, cur.view_shared(), None, save=True, mask_output=True, table=tab[id(ac)])
             ev = torch.cuda.Event(); ev.record(self._side[1]); joins.append(ev)
         a2, _ = net_forward(ta, ta.flat, nxt, None, save=False, mask_output=True, clamp1=True, table=tab[id(ta)],

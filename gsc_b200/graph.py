@@ -87,6 +87,7 @@ class GraphBatch:
         self.n_max = None if n_max is None else int(n_max)
         self.groups = None if groups is None else int(groups)
         self._csr = None
+        self._prep = {}                   # (hidden, num_layers) -> (buffer, event): see bwd_prep
 
     @property
     def structured(self) -> bool:
@@ -114,6 +115,7 @@ class GraphBatch:
         lazily generated dense mask, if any, is then not shared half-built)."""
         gb = self.view()
         gb._csr = self._csr
+        gb._prep = self._prep
         return gb
 
     # ---- construction -----------------------------------------------------------------------
@@ -215,6 +217,23 @@ class GraphBatch:
             self._csr = (rowptr, col, graph_ptr, stats)
         return self._csr[:3]
 
+    def bwd_prep(self, hidden: int, num_layers: int):
+        """The topology-only index work of the embedder backward (``ops.gnn_bwd_prep``), computed once per
+        packed batch on the stream of the first caller and shared by every backward pass over the batch
+        (an update runs two); later callers on other streams wait for its event.  None if not applicable."""
+        key = (int(hidden), int(num_layers))
+        hit = self._prep.get(key)
+        if hit is None:
+            from . import ops
+            rowptr, col, gptr = self.csr()
+            buf = ops.gnn_bwd_prep(rowptr, col, gptr, self.num_graphs, self.max_nodes, hidden, num_layers)
+            ev = torch.cuda.Event()
+            ev.record()
+            hit = self._prep[key] = (buf, ev)
+        else:
+            torch.cuda.current_stream().wait_event(hit[1])
+        return hit[0]
+
     def pack_stats(self):
         """The packer's device-side stats array [Et, max_nodes, error flags, asymmetry flag]."""
         self.csr()
@@ -224,4 +243,5 @@ class GraphBatch:
         """Reuse another batch's packed CSR (a transition's next state has the same network)."""
         if other._csr is not None and other.edge_index is self.edge_index:
             self._csr = other._csr
+            self._prep = other._prep
             self.max_nodes = other.max_nodes

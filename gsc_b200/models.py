@@ -440,7 +440,8 @@ def net_backward(net: _FlatNet, flat: torch.Tensor, gb: GraphBatch, ctx, dz: tor
                 rowptr, col, gptr = gb.csr()
                 ops.gnn_embed_bwd(gb.x, rowptr, col, gptr, gb.num_graphs, gb.max_nodes, gnn, H,
                                   net.embedder.num_layers, net.embedder.num_iter, saved, d_embp[:, pad:],
-                                  d_params=g_gnn, pack_stats=gb.pack_stats())
+                                  d_params=g_gnn, pack_stats=gb.pack_stats(),
+                                  prep=gb.bwd_prep(H, net.embedder.num_layers))
     if side is not None and grad_flat is not None:
         done = torch.cuda.Event()
         done.record(side)

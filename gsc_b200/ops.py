@@ -289,7 +289,8 @@ def gnn_embed_fwd(x, rowptr, col, graph_ptr, num_graphs: int, max_nodes: int, pa
 
 def gnn_embed_bwd(x, rowptr, col, graph_ptr, num_graphs: int, max_nodes: int, params, hidden: int,
                   num_layers: int, num_iter: int, saved, d_emb, d_params: Optional[torch.Tensor] = None,
-                  pack_stats: Optional[torch.Tensor] = None):
+                  pack_stats: Optional[torch.Tensor] = None, prep: Optional[torch.Tensor] = None):
+    """``prep``: the buffer of ``gnn_bwd_prep`` for this batch and embedder shape (optional)."""
     _need_cuda(x, params, saved, d_emb)
     lib = _lib.load()
     x = x.contiguous()
@@ -301,13 +302,28 @@ def gnn_embed_bwd(x, rowptr, col, graph_ptr, num_graphs: int, max_nodes: int, pa
     ws, wsn = workspace(lib.gsc_gnn_bwd_workspace_bytes(Nt, num_graphs, max_nodes, in_dim, hidden, num_layers,
                                                         num_iter), x.device, "gnn_bwd")
     with _Timed("gnn_bwd"):
-        check(lib.gsc_gnn_embed_bwd(_ptr(x), Nt, in_dim, _ptr(rowptr), _ptr(col), _ptr(graph_ptr),
-                                    num_graphs, max_nodes, _ptr(params), hidden, num_layers, num_iter,
-                                    _ptr(saved), _ptr(d_emb), _ld(d_emb), _ptr(d_params), _ptr(pack_stats),
-                                    _ptr(ws), wsn, _stream()),
+        check(lib.gsc_gnn_embed_bwd_prepared(_ptr(x), Nt, in_dim, _ptr(rowptr), _ptr(col), _ptr(graph_ptr),
+                                             num_graphs, max_nodes, _ptr(params), hidden, num_layers, num_iter,
+                                             _ptr(saved), _ptr(d_emb), _ld(d_emb), _ptr(d_params), _ptr(pack_stats),
+                                             _ptr(ws), wsn, _ptr(prep), _stream()),
               "gsc_gnn_embed_bwd")
-    _count(5)
+    _count(4 if prep is not None else 5)
     return d_params
+
+
+def gnn_bwd_prep(rowptr, col, graph_ptr, num_graphs: int, max_nodes: int, hidden: int, num_layers: int):
+    """Topology-only index work of the embedder backward for one packed batch (None if the batch has no
+    such part: graphs of more than 128 nodes).  Pass the result to every ``gnn_embed_bwd`` over the batch."""
+    lib = _lib.load()
+    n = int(lib.gsc_gnn_bwd_prep_bytes(num_graphs, max_nodes))
+    if n == 0:
+        return None
+    prep = torch.empty(n, dtype=torch.uint8, device=rowptr.device)
+    with _Timed("gnn_bwd_prep"):
+        check(lib.gsc_gnn_bwd_prep(_ptr(rowptr), _ptr(col), _ptr(graph_ptr), num_graphs, max_nodes, hidden, num_layers,
+                                   _ptr(prep), n, _stream()), "gsc_gnn_bwd_prep")
+    _count(1)
+    return prep
 
 
 # ---------------------------------------------------------------------------------------------

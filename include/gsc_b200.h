@@ -155,6 +155,24 @@ int gsc_gnn_embed_bwd(const float* x, int64_t num_nodes, int in_dim, const int32
                       const float* saved, const float* d_emb, int64_t d_emb_ld, float* d_params,
                       const int32_t* pack_stats, void* workspace, size_t workspace_bytes, void* stream);
 
+/* The topology-only part of the backward (per chunk of graphs: nodes by descending degree and the
+ * reverse-edge index; graphs of up to 128 nodes) can be computed once per packed batch and shared by
+ * every backward pass over it -- an update runs two, the critic's and the actor's:
+ *   gsc_gnn_bwd_prep_bytes(num_graphs, max_nodes)   buffer size, 0 if this batch has no such part;
+ *   gsc_gnn_bwd_prep(...)                           fills the buffer (same hidden / num_layers /
+ *                                                   num_graphs / max_nodes as the backward calls);
+ *   gsc_gnn_embed_bwd_prepared(..., prep, stream)   gsc_gnn_embed_bwd reading it (prep may be NULL:
+ *                                                   then identical to gsc_gnn_embed_bwd). */
+size_t gsc_gnn_bwd_prep_bytes(int64_t num_graphs, int max_nodes);
+int gsc_gnn_bwd_prep(const int32_t* rowptr, const int32_t* col, const int32_t* graph_ptr, int64_t num_graphs,
+                     int max_nodes, int hidden, int num_layers, void* prep, size_t prep_bytes, void* stream);
+int gsc_gnn_embed_bwd_prepared(const float* x, int64_t num_nodes, int in_dim, const int32_t* rowptr,
+                               const int32_t* col, const int32_t* graph_ptr, int64_t num_graphs,
+                               int max_nodes, const float* params, int hidden, int num_layers, int num_iter,
+                               const float* saved, const float* d_emb, int64_t d_emb_ld, float* d_params,
+                               const int32_t* pack_stats, void* workspace, size_t workspace_bytes,
+                               const void* prep, void* stream);
+
 /* ---- dense layers (PyG MLP: reference src/rlsp/agents/models.py:80-83,119-122) -------------
  * One strided GEMM, C[M,N] = epilogue( sum_s A_s * B_s ), with up to three K-segments so that
  * th.cat([emb, mask, a], 1) (reference models.py:90-91,150) is never materialised:
