@@ -1999,10 +1999,11 @@ gnn_chunk_prep_kernel(const int32_t* __restrict__ rowptr, const int32_t* __restr
 // the kernels themselves), the W / lin-bias entries were written by gnn_wgrad_kernel, which uses
 // `rows_w` CTAs (a streaming kernel wants long node slices), the att / bias entries by the gather
 // kernel's `num_partials` CTAs.
-__global__ void __launch_bounds__(256)
+constexpr int kRedLanes = 32;     // partial-row lanes per parameter: 32 parameters x 32 lanes per block
+__global__ void __launch_bounds__(32 * kRedLanes)
 gnn_bwd_reduce_kernel(const float* __restrict__ partials, int num_partials, int rows_w, int64_t P, float* __restrict__ d_params,
                       const int32_t* __restrict__ stats, const int32_t* __restrict__ flags, int num_convs, int in_dim, int H) {
-  __shared__ float red[8][33];
+  __shared__ float red[kRedLanes][33];
   const int c = threadIdx.x & 31, r = threadIdx.x >> 5;
   const int64_t t = (int64_t)blockIdx.x * 32 + c;
   int rows = num_partials;
@@ -2012,12 +2013,13 @@ gnn_bwd_reduce_kernel(const float* __restrict__ partials, int num_partials, int 
       if (t >= o + 2 * H && t < conv_param_offset(cv + 1, in_dim, H)) rows = rows_w;
     }
   }
+  // lane r adds the rows r, r + 32, ... (two independent chains); the lanes are then added in lane order
   float s0 = 0.f, s1 = 0.f;
   if (t < P) {
     int b = r;
-    for (; b + 8 < rows; b += 16) {
+    for (; b + kRedLanes < rows; b += 2 * kRedLanes) {
       s0 += partials[(size_t)b * P + t];
-      s1 += partials[(size_t)(b + 8) * P + t];
+      s1 += partials[(size_t)(b + kRedLanes) * P + t];
     }
     if (b < rows) s0 += partials[(size_t)b * P + t];
   }
@@ -2026,7 +2028,7 @@ gnn_bwd_reduce_kernel(const float* __restrict__ partials, int num_partials, int 
   if (r == 0 && t < P) {
     float tot = 0.f;
 #pragma unroll
-    for (int k = 0; k < 8; ++k) tot += red[k][c];
+    for (int k = 0; k < kRedLanes; ++k) tot += red[k][c];
     d_params[t] = tot;
   }
 }
@@ -2233,7 +2235,7 @@ static int launch_bwd_both(GnnArgs a, int max_nodes, float* d_params, const void
   GSC_LAUNCH_CHECK("gnn_bwd_kernel");
   const int64_t P = conv_param_offset(a.num_convs, a.in_dim, a.H);
   if (rows_w == 0) rows_w = grid;
-  gnn_bwd_reduce_kernel<<<(int)ceil_div(P, 32), 256, 0, st>>>(a.partials, grid, rows_w, P, d_params, a.stats, a.flags,
+  gnn_bwd_reduce_kernel<<<(int)ceil_div(P, 32), 32 * kRedLanes, 0, st>>>(a.partials, grid, rows_w, P, d_params, a.stats, a.flags,
                                                               a.num_convs, a.in_dim, a.H);
   GSC_LAUNCH_CHECK("gnn_bwd_reduce_kernel");
   return GSC_OK;
