@@ -245,6 +245,13 @@ class DDPGUpdater:
             tab_q_ready = torch.cuda.Event()
             tab_q_ready.record(self._side[1])
         q_pi, ctx_q = net_forward(q, q.flat, cur, a, save=True, save_gnn=False, table=tab_q, table_ready=tab_q_ready)
+        qpi_ev = torch.cuda.Event()
+        qpi_ev.record(main)
+        with torch.cuda.stream(self._side[1]):                # the reported actor loss: not part of the dependent chain
+            self._side[1].wait_event(qpi_ev)
+            a_loss = ops.colsum(q_pi) * (-scale)
+            loss_ev = torch.cuda.Event()
+            loss_ev.record(self._side[1])
         if self._neg is None or self._neg.shape[0] != B or float(self._neg_scale) != scale:
             self._neg = torch.full((B, 1), -scale, dtype=torch.float32, device=a.device)
             self._neg_scale = scale
@@ -254,7 +261,7 @@ class DDPGUpdater:
                      mlp_done=self._mlp_step(ac, ta, self.g_actor, self.m_actor, self.v_actor, self.steps_dev[1:2]))
         self.step_actor += 1
         self._optimizer_step(ac, ta, self.g_actor, self.gs_actor, self.m_actor, self.v_actor, self.steps_dev[1:2])
-        a_loss = ops.colsum(q_pi) * (-scale)
+        main.wait_event(loss_ev)
         return qv.view(-1), q_loss, a_loss
 
 
