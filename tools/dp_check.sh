@@ -5,8 +5,10 @@ O=gpurun_out; mkdir -p $O
 timeout 240 python -m pytest tests/test_gpu_dp.py -x -q 2>&1 | tail -3
 run() { tag=$1; shift; timeout 400 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus 2 "$@" > $O/r2_bench_${tag}_dp2.json 2> $O/r2_bench_${tag}_dp2.err; echo "$tag rc=$?"; }
 run c3
-run c3_mlp --bucket-allreduce mlp
-run c3_shard --shard-optimizer
+if [ "${DP_ALL:-0}" = "1" ]; then
+  run c3_mlp --bucket-allreduce mlp
+  run c3_shard --shard-optimizer
+fi
 run c4 --workload c4 --steps 10
 python - <<'PY'
 import json
