@@ -62,6 +62,24 @@ def test_pack_csr_single_graph_no_batch_and_empty_graphs():
     assert ops.pack_csr(bad, batch, 5, 5)[3].tolist()[2] != 0
 
 
+def test_pack_csr_long_rows_duplicates_and_symmetry_flag():
+    """A star with 40 leaves (row longer than the register sort takes), duplicate edges, and the
+    symmetry flag: set when a reverse edge (or one copy of a duplicated one) is missing."""
+    leaves = np.arange(1, 41)
+    und = np.concatenate([np.stack([np.zeros(40, dtype=np.int64), leaves]), np.stack([leaves, np.zeros(40, dtype=np.int64)])], axis=1)
+    rng = np.random.default_rng(0)
+    und = und[:, rng.permutation(und.shape[1])]
+    dup = np.array([[3, 0, 3, 0], [0, 3, 0, 3]])                # edge 0-3 three times in both directions
+    for ei, sym in ((und, 0), (np.concatenate([und, dup], axis=1), 0), (np.concatenate([und, dup[:, :3]], axis=1), 1),
+                    (und[:, 1:], 1)):
+        rowptr, col, gptr, stats = ops.pack_csr(torch.from_numpy(np.ascontiguousarray(ei)).to(DEV), None, 41, 1)
+        want_rp, want_col = _csr_reference(ei, 41)
+        np.testing.assert_array_equal(rowptr.cpu().numpy(), want_rp)
+        np.testing.assert_array_equal(col.cpu().numpy()[:len(want_col)], want_col)
+        st_h = stats.tolist()
+        assert st_h[1] == 41 and st_h[2] == 0 and st_h[3] == sym, (st_h, sym)
+
+
 def test_pack_csr_large_scan():
     st = synth.make_states(20000, 24, 16, 24, seed=9, num_topologies=64)      # ~400k rows: multi-block scan
     rowptr, col, gptr, stats = ops.pack_csr(torch.from_numpy(st.edge_index).to(DEV),
@@ -151,6 +169,28 @@ def test_gnn_embed_bwd_matches_autograd_of_oracle(B, n_max, lo, hi, H, F, num_la
     d3 = ops.gnn_embed_bwd(gb.x, rowptr, col, gptr, B, gb.max_nodes, flat, H, num_layers, num_iter, saved,
                            d_emb.float().to(DEV))
     assert rel_err(d3.cpu().numpy(), want) < 1e-4
+
+
+def test_gnn_embed_bwd_prepared_is_bit_identical_and_shared_per_batch():
+    """gsc_gnn_bwd_prep + gsc_gnn_embed_bwd_prepared == gsc_gnn_embed_bwd bit for bit (the slot order is a
+    stable sort, so the summation orders are fixed), and GraphBatch hands every backward the same buffer."""
+    B, H, F = 300, 22, 3
+    st, sd = _embed_case(B, 24, 16, 24, H, F, 2, 2, seed=5)
+    gb = GraphBatch.from_states(st).to(DEV)
+    rowptr, col, gptr = gb.csr()
+    flat = _flat(sd, 2)
+    emb, saved = ops.gnn_embed_fwd(gb.x, rowptr, col, gptr, B, gb.max_nodes, flat, H, 2, 2, save=True)
+    d_emb = torch.randn(B, H, generator=torch.Generator().manual_seed(3)).to(DEV)
+    plain = ops.gnn_embed_bwd(gb.x, rowptr, col, gptr, B, gb.max_nodes, flat, H, 2, 2, saved, d_emb,
+                              pack_stats=gb.pack_stats())
+    prep = gb.bwd_prep(H, 2)
+    assert prep is not None and gb.bwd_prep(H, 2) is prep and gb.view_shared().bwd_prep(H, 2) is prep
+    for _ in range(2):
+        got = ops.gnn_embed_bwd(gb.x, rowptr, col, gptr, B, gb.max_nodes, flat, H, 2, 2, saved, d_emb,
+                                pack_stats=gb.pack_stats(), prep=prep)
+        assert torch.equal(got, plain)
+    big = GraphBatch.from_states(synth.make_states(2, 300, 200, 300, seed=1)).to(DEV)
+    assert big.bwd_prep(H, 2) is None                          # graphs beyond 128 nodes have no such part
 
 
 def test_gnn_embed_bwd_directed_graph_uses_scatter_kernel():
