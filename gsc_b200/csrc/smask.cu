@@ -31,6 +31,7 @@ mask_table_kernel(const float* __restrict__ W, int64_t ldw, int n_max, int group
   const float* w = W + (int64_t)blockIdx.x * ldw;
   float* mycol = colpart + (size_t)warp * n_max;
   for (int j = lane; j < n_max; j += 32) mycol[j] = 0.f;
+#pragma unroll 2                                            // two rows' loads in flight: the kernel is latency-bound
   for (int i = warp; i < n_max; i += kWarps) {
     const float* wi = w + (int64_t)i * groups * n_max;
     float rowsum = 0.f;

@@ -205,9 +205,11 @@ class DDPGUpdater:
         start.record(main)
         with torch.cuda.stream(self._side[1]):
             self._side[1].wait_event(start)
-            tab = {id(net): first_layer_table(net, net.flat, cur) for net in (ta, tq, q, ac)}
-            tables_ready = torch.cuda.Event()
-            tables_ready.record(self._side[1])
+            tab, tab_ready = {}, {}                           # in the order they are needed; one event each
+            for net in (ta, tq, q, ac):
+                tab[id(net)] = first_layer_table(net, net.flat, cur)
+                tab_ready[id(net)] = torch.cuda.Event()
+                tab_ready[id(net)].record(self._side[1])
         cur.csr()
         nxt.share_topology_from(cur)
         fork = torch.cuda.Event()
@@ -216,7 +218,7 @@ class DDPGUpdater:
         with torch.cuda.stream(self._side[0]):
             self._side[0].wait_event(fork)
             qv, ctx = net_forward(q, q.flat, cur.view_shared(), actions, save=True, table=tab[id(q)],
-                                  table_ready=tables_ready)
+                                  table_ready=tab_ready[id(q)])
             ev = torch.cuda.Event(); ev.record(self._side[0]); joins.append(ev)
         with torch.cuda.stream(self._side[1]):
             self._side[1].wait_event(fork)
@@ -225,8 +227,8 @@ class DDPGUpdater:
             a, ctx_a = net_forward(ac, ac.flat, cur.view_shared(), None, save=True, mask_output=True, table=tab[id(ac)])
             ev = torch.cuda.Event(); ev.record(self._side[1]); joins.append(ev)
         a2, _ = net_forward(ta, ta.flat, nxt, None, save=False, mask_output=True, clamp1=True, table=tab[id(ta)],
-                            table_ready=tables_ready)
-        q2, _ = net_forward(tq, tq.flat, nxt, a2, save=False, table=tab[id(tq)])
+                            table_ready=tab_ready[id(ta)])
+        q2, _ = net_forward(tq, tq.flat, nxt, a2, save=False, table=tab[id(tq)], table_ready=tab_ready[id(tq)])
         for ev in joins:
             main.wait_event(ev)
         # ---- critic update (reference _update_critic, simple_ddpg.py:204-219) ----
