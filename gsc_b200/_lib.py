@@ -26,7 +26,7 @@ class GemmArgs(Structure):
                 ("b_cs", c_int64 * 3), ("num_seg", c_int), ("flags", c_int), ("bias", c_void_p),
                 ("mul", c_void_p), ("ld_mul", c_int64), ("gate", c_void_p), ("ld_gate", c_int64),
                 ("row_table", c_void_p), ("ld_table", c_int64), ("row_n", c_void_p), ("n_max", c_int32),
-                ("groups", c_int32)]
+                ("groups", c_int32), ("dot_w", c_void_p), ("dot_bias", c_void_p), ("dot_out", c_void_p)]
 
 
 class GscError(RuntimeError):

@@ -37,6 +37,9 @@ struct GemmDev {
   float* C;
   float* partial;        // [splits][M][N] when splits > 1
   int tiles_total, tiles_per_split, splits;
+  const float* dot_w;    // optional one-unit head on the finished rows (gsc_gemm_args::dot_*)
+  const float* dot_bias;
+  float* dot_out;
 };
 
 __device__ __forceinline__ float apply_epilogue(const GemmDev& g, float v, int64_t i, int64_t j) {
@@ -173,6 +176,30 @@ __global__ void gemm_finalize_kernel(const GemmDev g) {
   }
 }
 
+// Split-K finalize with a one-unit head on top: one warp per row adds the partials of the row, applies the
+// epilogue, stores C and folds the finished values into dot_out[i] = sum_j C[i, j] dot_w[j] + dot_bias[0]
+// (same summation order as gemm_finalize_kernel followed by linear_n1_fwd_kernel: lane-strided FMA chain,
+// then the shuffle tree).
+__global__ void __launch_bounds__(256) gemm_finalize_rowdot_kernel(const GemmDev g) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5, warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  const int64_t total = g.M * g.N;
+  const float b = g.dot_bias ? g.dot_bias[0] : 0.f;
+  for (int64_t i = warp; i < g.M; i += warps) {
+    float dot = 0.f;
+    for (int64_t j = lane; j < g.N; j += 32) {
+      const int64_t t = i * g.N + j;
+      float s = 0.f;
+      for (int z = 0; z < g.splits; ++z) s += g.partial[(int64_t)z * total + t];
+      const float v = apply_epilogue(g, s, i, j);
+      g.C[i * g.ldc + j] = v;
+      dot = fmaf(v, g.dot_w[j], dot);
+    }
+    dot = warp_sum(dot);
+    if (lane == 0) g.dot_out[i] = dot + b;
+  }
+}
+
 __global__ void __launch_bounds__(1024) colsum_kernel(const float* __restrict__ X, int64_t ld, int64_t M, int64_t N,
                                                       float* __restrict__ out) {
   // block = 32 columns x 32 row-lanes; every thread keeps four independent partial sums (the loop is
@@ -263,6 +290,27 @@ extern "C" int gsc_gemm(const gsc_gemm_args* a, int64_t M, int64_t N, float* C, 
   GSC_REQUIRE(!(g.flags & GSC_EPI_MUL) || g.mul, "gsc_gemm: GSC_EPI_MUL without mul");
   GSC_REQUIRE(!(g.flags & GSC_EPI_GATE) || g.gate, "gsc_gemm: GSC_EPI_GATE without gate");
   g.M = M; g.N = N; g.ldc = ldc; g.C = C;
+  g.dot_w = a->dot_w; g.dot_bias = a->dot_bias; g.dot_out = a->dot_out;
+  GSC_REQUIRE(!g.dot_out || (g.dot_w && N <= 1024), "gsc_gemm: dot_out needs dot_w and N <= 1024");
+  // the reduction of split-K partials (with the optional head), or the head alone behind an unsplit GEMM
+  auto finish = [&](int splits) -> int {
+    if (splits > 1) {
+      if (g.dot_out) {
+        int64_t blocks = ceil_div(M, 8);
+        if (blocks > 8 * kNumSMs) blocks = 8 * kNumSMs;
+        gemm_finalize_rowdot_kernel<<<(int)blocks, 256, 0, st>>>(g);
+        GSC_LAUNCH_CHECK("gemm_finalize_rowdot_kernel");
+      } else {
+        int64_t blocks = ceil_div(M * N, 256);
+        if (blocks > 8 * kNumSMs) blocks = 8 * kNumSMs;
+        gemm_finalize_kernel<<<(int)blocks, 256, 0, st>>>(g);
+        GSC_LAUNCH_CHECK("gemm_finalize_kernel");
+      }
+    } else if (g.dot_out) {
+      return gsc_linear_n1_fwd(C, ldc, M, (int)N, g.dot_w, g.dot_bias, g.dot_out, 1, (void*)st);
+    }
+    return GSC_OK;
+  };
   if (a->flags & (GSC_EPI_TF32 | GSC_EPI_TF32X3)) {
     bool a_mn = false, b_mn = false;
     // tiny problems stay on the exact path: the tensor-core pipeline has a fixed fill cost
@@ -271,15 +319,9 @@ extern "C" int gsc_gemm(const gsc_gemm_args* a, int64_t M, int64_t N, float* C, 
       int rc = gemm_tc_launch(a, M, N, C, ldc, workspace, workspace_bytes, a_mn, b_mn,
                               (a->flags & GSC_EPI_TF32X3) != 0, st, &splits);
       if (rc) return rc;
-      if (splits > 1) {
-        g.splits = splits;
-        g.partial = (float*)workspace;
-        int64_t blocks = ceil_div(M * N, 256);
-        if (blocks > 8 * kNumSMs) blocks = 8 * kNumSMs;
-        gemm_finalize_kernel<<<(int)blocks, 256, 0, st>>>(g);
-        GSC_LAUNCH_CHECK("gemm_finalize_kernel");
-      }
-      return GSC_OK;
+      g.splits = splits;
+      g.partial = (float*)workspace;
+      return finish(splits);
     }
   }
   g.tiles_total = tiles;
@@ -294,13 +336,7 @@ extern "C" int gsc_gemm(const gsc_gemm_args* a, int64_t M, int64_t N, float* C, 
   dim3 grid((unsigned)ceil_div(N, kBN), (unsigned)ceil_div(M, kBM), (unsigned)g.splits);
   gemm_simt_kernel<<<grid, kGemmThreads, 0, st>>>(g);
   GSC_LAUNCH_CHECK("gemm_simt_kernel");
-  if (g.splits > 1) {
-    int64_t blocks = ceil_div(M * N, 256);
-    if (blocks > 8 * kNumSMs) blocks = 8 * kNumSMs;
-    gemm_finalize_kernel<<<(int)blocks, 256, 0, st>>>(g);
-    GSC_LAUNCH_CHECK("gemm_finalize_kernel");
-  }
-  return GSC_OK;
+  return finish(g.splits);
 }
 
 extern "C" int gsc_colsum(const float* X, int64_t ld, int64_t M, int64_t N, float* out, void* stream) {

@@ -333,8 +333,15 @@ def net_forward(net: _FlatNet, flat: torch.Tensor, gb: GraphBatch, action: Optio
     hs = []
     h = None
     n = len(lins)
+    q_head = None
     for i, (W, b, Wp, pad) in enumerate(lins):
         last = i == n - 1
+        if last and q_head is not None:               # the one-unit head came with the layer below
+            h = q_head
+            break
+        # a one-unit last layer (the critic's head) rides on this layer's call
+        head = (lins[i + 1][0], lins[i + 1][1]) if (i == n - 2 and _single_unit(lins[i + 1][0]) and not mask_output
+                                                    and not clamp1) else None
         out_mul = gb.mask if (mask_output and last and not st) else None
         out_smask = smask if (mask_output and last and st) else None
         if i == 0 and st:
@@ -345,12 +352,16 @@ def net_forward(net: _FlatNet, flat: torch.Tensor, gb: GraphBatch, action: Optio
             ins = [embp] + ([action] if action is not None else [])
             offs = [0] + ([pad + H + A] if action is not None else [])
             h = ops.linear_fwd(ins, Wp, b, relu=not last, mul=out_mul, clamp1=clamp1 and last,
-                               col_offsets=offs, row_table=(table, gb.n_nodes), smask=out_smask)
+                               col_offsets=offs, row_table=(table, gb.n_nodes), smask=out_smask, head=head)
+            if head is not None:
+                h, q_head = h
         elif last and i > 0 and _single_unit(W) and out_mul is None and out_smask is None and not clamp1:
             h = ops.linear_n1_fwd(h, W, b)             # the critic's head: one launch, no GEMM machinery
         else:
             h = ops.linear_fwd(inputs if i == 0 else [h], Wp if i == 0 else W, b, relu=not last,
-                               mul=out_mul, clamp1=clamp1 and last, smask=out_smask)
+                               mul=out_mul, clamp1=clamp1 and last, smask=out_smask, head=head)
+            if head is not None:
+                h, q_head = h
         if not last:
             hs.append(h)
     ctx = (embp, saved, inputs, hs, st) if save else None

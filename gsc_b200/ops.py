@@ -328,7 +328,7 @@ def gnn_bwd_prep(rowptr, col, graph_ptr, num_graphs: int, max_nodes: int, hidden
 
 # ---------------------------------------------------------------------------------------------
 def gemm_raw(segs: Sequence[tuple], M: int, N: int, out: torch.Tensor, flags: int = 0,
-             bias=None, mul=None, gate=None, tag: str = "gemm", row_table=None, smask=None):
+             bias=None, mul=None, gate=None, tag: str = "gemm", row_table=None, smask=None, dot=None):
     """segs: (A_tensor, a_rs, a_cs, B_tensor, b_rs, b_cs, K) with A/B giving the base pointers.
     ``row_table``: (table [n_max+1, N], row_n int32 [M]) adds table[row_n[i]] to row i;
     ``smask``: (row_n, n_max, groups) zeroes the columns outside the structured mask of row i."""
@@ -360,20 +360,25 @@ def gemm_raw(segs: Sequence[tuple], M: int, N: int, out: torch.Tensor, flags: in
         row_n, n_max, groups = smask
         args.row_n, args.n_max, args.groups = row_n.data_ptr(), n_max, groups
         args.flags |= _lib.EPI_SMASK
+    if dot is not None:
+        args.dot_w, args.dot_bias, args.dot_out = dot[0].data_ptr(), _ptr(dot[1]), dot[2].data_ptr()
     need = lib.gsc_gemm_workspace_bytes(M, N, ktot)
     ws, wsn = workspace(need, out.device, "gemm")
     with _Timed(f"{tag}[{M}x{N}x{ktot}{'+m' if mul is not None else ''}{'+g' if gate is not None else ''}]"
                 + ("T" if row_table is not None else "") + ("S" if smask is not None else "")):
         check(lib.gsc_gemm(args, M, N, out.data_ptr(), _ld(out), _ptr(ws), wsn, _stream()), "gsc_gemm")
-    _count(2 if need else 1)
+    _count(2 if (need or dot is not None) else 1)
     return out
 
 
 def linear_fwd(inputs: List[torch.Tensor], weight: torch.Tensor, bias: Optional[torch.Tensor],
                relu: bool = False, mul: Optional[torch.Tensor] = None, clamp1: bool = False,
                out: Optional[torch.Tensor] = None, col_offsets: Optional[Sequence[int]] = None,
-               row_table=None, smask=None) -> torch.Tensor:
+               row_table=None, smask=None, head=None):
     """act(cat(inputs, 1) @ weight.T + bias) [* mul] without materialising the concatenation.
+
+    ``head=(w [1, N], b [1] or None)``: a one-unit layer on top of the result, folded into the same
+    call (into the split-K reduction when there is one); returns ``(out, q [M, 1])`` then.
 
     weight: [N, sum K_s] fp32, may be a strided row view (its row stride is used).
     ``col_offsets`` places input s at weight columns [col_offsets[s], +K_s) instead of back to back
@@ -395,7 +400,15 @@ def linear_fwd(inputs: List[torch.Tensor], weight: torch.Tensor, bias: Optional[
         out = torch.empty(M, N, dtype=torch.float32, device=weight.device)
     flags = (EPI_BIAS if bias is not None else 0) | (EPI_RELU if relu else 0) | \
             (EPI_MUL if mul is not None else 0) | (EPI_CLAMP1 if clamp1 else 0)
-    return gemm_raw(segs, M, N, out, flags, bias=bias, mul=mul, tag="linear_fwd", row_table=row_table, smask=smask)
+    if head is None:
+        return gemm_raw(segs, M, N, out, flags, bias=bias, mul=mul, tag="linear_fwd", row_table=row_table, smask=smask)
+    hw, hb = head
+    if tuple(hw.shape) != (1, N) or hw.stride(1) != 1 or N > 1024:
+        raise _lib.GscError(f"linear_fwd: head weight must be [1, {N}] with unit column stride, N <= 1024")
+    q = torch.empty(M, 1, dtype=torch.float32, device=weight.device)
+    gemm_raw(segs, M, N, out, flags, bias=bias, mul=mul, tag="linear_fwd+head", row_table=row_table, smask=smask,
+             dot=(hw, hb, q))
+    return out, q
 
 
 def linear_dgrad(dY: torch.Tensor, weight: torch.Tensor, col_off: int, K: int,

@@ -198,6 +198,12 @@ typedef struct {
   int64_t ld_table;
   const int32_t* row_n;     /* [M] node count of the state in row i (ROWTABLE, SMASK)    */
   int32_t n_max, groups;    /* scheduling shape (N_max, G, N_max) of the SMASK columns   */
+  /* optional one-unit layer on top of the finished rows (the critic: Linear(64, 1) behind its hidden
+   * layer): dot_out[i] = sum_j C[i, j] * dot_w[j] + dot_bias[0]; folded into the split-K reduction when
+   * there is one, a gsc_linear_n1_fwd launch otherwise.  dot_out == NULL: off.  N <= 1024. */
+  const float* dot_w;       /* [N]  */
+  const float* dot_bias;    /* [1] or NULL */
+  float* dot_out;           /* [M]  */
 } gsc_gemm_args;
 
 size_t gsc_gemm_workspace_bytes(int64_t M, int64_t N, int64_t K_total);

@@ -349,6 +349,20 @@ def test_linear_n1_head_matches_fp64_and_gemm_route():
         assert rel_err(only.cpu().numpy(), (dq.double() @ W.double()).cpu().numpy()) < 1e-6
 
 
+@pytest.mark.parametrize("M,N,K", [(1024, 64, 30024), (100, 64, 3480), (37, 64, 24), (300, 256, 5000)])
+def test_linear_fwd_with_fused_head_equals_two_calls(M, N, K, dense_precision):
+    """The one-unit head folded into the layer below (split-K reduction or not) == layer, then head."""
+    gen = torch.Generator().manual_seed(M + K)
+    x = torch.randn(M, K, generator=gen).to(DEV)
+    W = (torch.randn(N, K, generator=gen) / K ** 0.5).to(DEV)
+    b = torch.randn(N, generator=gen).to(DEV)
+    hw, hb = (torch.randn(1, N, generator=gen) / 8).to(DEV), torch.randn(1, generator=gen).to(DEV)
+    h_ref = ops.linear_fwd([x], W, b, relu=True)
+    q_ref = ops.linear_n1_fwd(h_ref, hw, hb)
+    h, q = ops.linear_fwd([x], W, b, relu=True, head=(hw, hb))
+    assert torch.equal(h, h_ref) and torch.equal(q, q_ref)
+
+
 def test_adam_soft_update_slices_equal_one_launch():
     """Two slices of one optimizer step (the second bumps the device step counter) == one launch over
     the whole buffer, bit for bit, over several steps."""
