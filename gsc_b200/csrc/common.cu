@@ -19,7 +19,7 @@ int fail(int code, const char* fmt, ...) {
 
 }  // namespace gsc
 
-extern "C" int gsc_version(void) { return 100; }
+extern "C" int gsc_version(void) { return 200; }   // 200: round 2 (gsc_gemm_args grew by the dot_* fields)
 
 namespace gsc {
 static std::atomic<int> g_sm_reserve{0};

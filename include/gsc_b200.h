@@ -46,7 +46,8 @@ extern "C" {
                                 product is hi*hi + hi*lo + lo*hi with fp32 accumulation (3xTF32,
                                 relative error ~2^-21 per product).  Takes precedence over TF32. */
 
-int gsc_version(void);
+int gsc_version(void);      /* 100 * round + revision; 200: gsc_gemm_args carries the dot_* fields (a host built
+                               against the 1xx header must be rebuilt before it calls gsc_gemm) */
 /* Leave `num_sms` SMs (0..74, default 0) free in the persistent embedder-backward launches, for
  * communication kernels (NCCL all-reduce of gradient blocks) that run beside them in data-parallel
  * training.  Process-wide; no counterpart in the reference (it has no multi-GPU path). */
