@@ -33,6 +33,28 @@ def test_library_exports_every_declared_symbol():
     assert lib.gsc_version() >= 100
 
 
+def test_ctypes_mirror_of_gsc_gemm_args_matches_the_header(tmp_path):
+    """The struct crosses the C-ABI by pointer: size and field offsets of the ctypes mirror must be what a
+    C compiler makes of include/gsc_b200.h."""
+    import ctypes
+    fields = [n for n, _ in _lib.GemmArgs._fields_]
+    src = tmp_path / "layout.c"
+    src.write_text('#include <stdio.h>\n#include <stddef.h>\n#include "gsc_b200.h"\nint main(void) {\n'
+                   '  printf("%zu\\n", sizeof(gsc_gemm_args));\n' +
+                   "".join(f'  printf("%zu\\n", offsetof(gsc_gemm_args, {f}));\n' for f in fields) +
+                   "  return 0;\n}\n")
+    exe = tmp_path / "layout"
+    subprocess.run(["gcc", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)], check=True)
+    out = [int(v) for v in subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.split()]
+    assert out[0] == ctypes.sizeof(_lib.GemmArgs)
+    assert out[1:] == [getattr(_lib.GemmArgs, f).offset for f in fields]
+    # the size queries added with the round-2 entry points answer without a GPU
+    lib = _lib.load()
+    assert lib.gsc_linear_n1_bwd_workspace_bytes(64) >= 256 + 65 * 4
+    assert lib.gsc_gnn_bwd_prep_bytes(1024, 100) > 1024 * 128 * 2 and lib.gsc_gnn_bwd_prep_bytes(4, 300) == 0
+    assert lib.gsc_version() >= 200
+
+
 def test_size_queries_need_no_gpu():
     lib = _lib.load()
     assert lib.gsc_gnn_param_floats(3, 22, 2) == 220 + 1056          # SURVEY.md section 8a, row a3
