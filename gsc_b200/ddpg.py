@@ -200,7 +200,7 @@ class DDPGUpdater:
         main = torch.cuda.current_stream()
         self.side_streams()
         # the four first-layer tables depend on the weights only: they are built on a side stream while
-        # the main stream packs the batch (ten small launches that leave the GPU mostly idle)
+        # the main stream packs the batch (seven small launches that leave the GPU mostly idle)
         start = torch.cuda.Event()
         start.record(main)
         with torch.cuda.stream(self._side[1]):
